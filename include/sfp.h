@@ -1,0 +1,261 @@
+/* sfp.h — C ABI of the starframe physics step (B200-native build).
+ *
+ * This is the drop-in boundary for ONE path of m0lentum/starframe: the per-frame physics
+ * substep loop (spatial-hash broadphase -> narrowphase -> XPBD position projection ->
+ * velocity update with friction and restitution; BASELINE.json north_star).
+ *
+ * Reference citations: the reference source tree is NOT mounted offline
+ * (/root/reference holds only README.md:1-3, "moved to Codeberg").  Every entry point below
+ * therefore cites the interface it replaces by north_star's own wording ("the reference's
+ * Physics/Collider/Body API surface") instead of a file:line; see BASELINE.md §0 and
+ * SURVEY.md §8b.  Parity with the reference itself is UNPINNED.
+ *
+ * Two shared libraries export this API:
+ *   libsfp_b200.so  (starframe_b200/csrc)  symbols  sfp_*      — CUDA sm_100a product path
+ *   libsfp_ref.so   (oracle/)              symbols  sfp_ref_*  — CPU oracle, TEST INFRASTRUCTURE ONLY
+ * The oracle's entry points have identical signatures with the prefix sfp_ref_.
+ *
+ * Conventions
+ *   - every function returns int32_t: 0 = SFP_OK, negative = error (never throws / unwinds)
+ *   - the library owns everything behind SfpWorld*; the caller owns every buffer it passes;
+ *     no caller pointer is retained after a call returns
+ *   - a world is not thread-safe (mirrors `&mut self` on the Rust side); distinct worlds may
+ *     be used from distinct threads
+ *   - body index == upload order, stable for the life of the world
+ *   - all structs are plain C PODs (#[repr(C)]-compatible), little-endian
+ */
+#ifndef SFP_H_
+#define SFP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define SFP_API
+#else
+#define SFP_API __attribute__((visibility("default")))
+#endif
+
+/* ---- error codes ------------------------------------------------------------------ */
+enum {
+    SFP_OK = 0,
+    SFP_E_INVALID = -1,  /* bad argument / bad state */
+    SFP_E_CUDA = -2,     /* a CUDA call failed; sfp_last_error() has the string */
+    SFP_E_CAPACITY = -3, /* a device buffer (entries / pairs / colours) overflowed */
+    SFP_E_NCCL = -4,
+    SFP_E_NOMEM = -5
+};
+
+/* ---- collider shapes (north_star: circle / capsule / rounded polygon) --------------- */
+enum {
+    SFP_SHAPE_CIRCLE = 0,  /* point core + radius                                        */
+    SFP_SHAPE_CAPSULE = 1, /* segment core (-hx,0)..(+hx,0) in body frame + radius       */
+    SFP_SHAPE_RECT = 2     /* rectangle core [-hx,hx]x[-hy,hy] + rounding radius         */
+};
+
+enum {
+    SFP_BODY_STATIC = 1u /* infinite mass; never moved by the solver */
+};
+
+/* solver constraint order (oracle honours both; the CUDA path is COLOUR only) */
+enum {
+    SFP_ORDER_COLOUR = 0,   /* graph-coloured Gauss-Seidel == sequential GS in colour order */
+    SFP_ORDER_REFERENCE = 1 /* sequential GS: joints in upload order, then sorted pairs      */
+};
+
+enum {
+    SFP_JOINT_DISTANCE = 0, /* bilateral: |pb-pa| == rest                                 */
+    SFP_JOINT_ROPE = 1      /* unilateral: |pb-pa| <= rest                                */
+};
+
+enum {
+    SFP_FLAG_BROADPHASE_EVERY_SUBSTEP = 1u, /* default: once per frame     */
+    SFP_FLAG_MULTI_KERNEL = 2u              /* CUDA: one launch per stage instead of the
+                                               persistent cooperative substep kernel (debug) */
+};
+
+/* ---- parameters ------------------------------------------------------------------- */
+typedef struct SfpParams {
+    float gravity_x, gravity_y; /* default (0, -9.81)                                      */
+    float cell_size;            /* spatial-hash cell edge, metres (default 0.5)            */
+    float aabb_margin;          /* constant AABB expansion, metres (default 0.02)          */
+    float vel_expand;           /* AABB swept by vel_expand*dt*v towards the motion (def. 1) */
+    float contact_margin;       /* narrowphase keeps points with separation < this (0.01)  */
+    uint32_t solver_order;      /* SFP_ORDER_*                                             */
+    uint32_t flags;             /* SFP_FLAG_*                                              */
+    uint32_t max_bodies;        /* capacities; 0 = choose from the first upload            */
+    uint32_t max_joints;
+    uint32_t max_entries;       /* (cell,body) broadphase entries                          */
+    uint32_t max_pairs;         /* candidate pairs                                         */
+    int32_t device;             /* CUDA device ordinal (ignored by the oracle)             */
+    uint32_t reserved[3];
+} SfpParams; /* 64 bytes */
+
+/* ---- scene-graph side records (AoS, as a scene-graph walk produces them) ------------ */
+typedef struct SfpBodyDesc {
+    float x, y, angle;      /* pose                                                        */
+    float vx, vy, omega;    /* velocity                                                    */
+    float hx, hy, radius;   /* collider dimensions, see SFP_SHAPE_*                        */
+    uint32_t shape;         /* SFP_SHAPE_*                                                 */
+    float density;          /* mass = density * area(shape); ignored for static bodies     */
+    float mu_s, mu_d;       /* static / dynamic friction                                   */
+    float restitution;
+    uint16_t category;      /* collision layer bits of this body                           */
+    uint16_t mask;          /* layers it collides with; pair kept iff both ways match      */
+    uint32_t flags;         /* SFP_BODY_*                                                  */
+} SfpBodyDesc; /* 64 bytes */
+
+typedef struct SfpJointDesc {
+    uint32_t body_a, body_b;
+    float ax, ay; /* anchor in body_a's frame */
+    float bx, by; /* anchor in body_b's frame */
+    float rest;   /* rest (distance) / max (rope) length */
+    float compliance; /* XPBD alpha, m/N; 0 = rigid */
+    uint32_t kind;    /* SFP_JOINT_* */
+    uint32_t reserved[3];
+} SfpJointDesc; /* 48 bytes */
+
+/* what the scene graph reads back per body */
+typedef struct SfpBodyState {
+    float x, y;
+    float c, s; /* rotation as (cos, sin) — the solver's native representation */
+    float vx, vy, omega;
+    float angle; /* atan2(s, c), derived on the host at download */
+} SfpBodyState; /* 32 bytes */
+
+typedef struct SfpPair {
+    uint32_t a, b; /* a < b */
+} SfpPair;
+
+/* one contact manifold per candidate pair that touches (1 or 2 points) */
+typedef struct SfpContact {
+    uint32_t a, b;
+    uint32_t count; /* 1 or 2 */
+    float nx, ny;   /* unit normal, from a to b */
+    float depth[2]; /* penetration depth at narrowphase time (negative = separated, < margin) */
+    float px[2], py[2]; /* world-space contact point (midway between the two surfaces) */
+    float lambda_n[2];  /* normal multiplier accumulated in the last substep */
+    float lambda_t[2];
+} SfpContact; /* 60 bytes */
+
+typedef struct SfpStats {
+    uint64_t frames;        /* frames stepped since creation */
+    uint64_t body_substeps; /* sum of n_bodies * substeps */
+    uint32_t n_bodies, n_dynamic, n_joints;
+    uint32_t n_entries;  /* last frame: (cell,body) entries */
+    uint32_t n_pairs;    /* last frame: candidate pairs */
+    uint32_t n_contacts; /* last substep: contact points */
+    uint32_t n_manifolds;/* last substep: pairs with >=1 point */
+    uint32_t n_colours;  /* last frame */
+    uint32_t colour_rounds; /* last frame: colouring rounds taken */
+    uint32_t overflow;   /* sticky: nonzero if a capacity was exceeded */
+    float max_penetration;  /* last substep, over contact points, at narrowphase time */
+    float kinetic_energy;   /* after last substep */
+    float potential_energy; /* -m g.x, after last substep */
+    uint32_t reserved[3];
+} SfpStats; /* 80 bytes */
+
+typedef struct SfpWorld SfpWorld;
+typedef struct SfpBatch SfpBatch;
+
+/* ---- single world ----------------------------------------------------------------- */
+
+/* Replaces: construction of the reference's `Physics` object (tuning constants + empty
+ * body/collider storage).  Reference file:line unavailable — tree not mounted. */
+SFP_API int32_t sfp_default_params(SfpParams* out);
+SFP_API int32_t sfp_create(const SfpParams* params, SfpWorld** out);
+SFP_API int32_t sfp_destroy(SfpWorld* w);
+
+/* Replaces: the scene-graph -> physics sync that hands every `Body` + `Collider` to the
+ * step (AoS in, converted to SoA device buffers inside).  Replaces all bodies. */
+SFP_API int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n);
+
+/* Replaces: registration of the reference's distance / rope constraints. Replaces all joints. */
+SFP_API int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n);
+
+/* Replaces: the reference's per-frame `Physics` step (frame dt, substep count): broadphase,
+ * then `substeps` x { integrate, narrowphase, position solve, velocity update }.
+ * Asynchronous on the world's stream until a download / get / sync call. */
+SFP_API int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps);
+
+/* Blocks until all queued work of this world is done; reports sticky errors. */
+SFP_API int32_t sfp_sync(SfpWorld* w);
+
+/* Replaces: physics -> scene-graph pose write-back. `out` has room for n states. */
+SFP_API int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n);
+
+/* Candidate pair set of the last frame, sorted by (a,b).  *n_out receives the count even
+ * when it exceeds cap (then only cap pairs are written). */
+SFP_API int32_t sfp_get_pairs(SfpWorld* w, SfpPair* out, uint32_t cap, uint32_t* n_out);
+
+/* Contact manifolds of the last substep, sorted by (a,b). Same cap semantics. */
+SFP_API int32_t sfp_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap, uint32_t* n_out);
+
+/* Per-pair colour of the last frame's constraint colouring, aligned with sfp_get_pairs
+ * order; joint colours follow in upload order if joint_colours != NULL. (Test hook.) */
+SFP_API int32_t sfp_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap,
+                                uint32_t* joint_colours, uint32_t jcap);
+
+SFP_API int32_t sfp_get_stats(SfpWorld* w, SfpStats* out);
+SFP_API const char* sfp_last_error(SfpWorld* w);
+
+/* ---- step with host buffers (the end-to-end call the engine makes each frame) -------- */
+/* Uploads poses+velocities for n bodies (shape/material unchanged since the last full
+ * upload), steps one frame and downloads the new states.  Host<->device copies included. */
+SFP_API int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out,
+                              uint32_t n, float dt, uint32_t substeps);
+
+/* ---- batched independent worlds (BASELINE.json config 5) --------------------------- */
+/* n_worlds worlds of exactly bodies_per_world bodies each, stepped together on ONE device
+ * (one process per GPU shards the world range; no collective on the data path). */
+SFP_API int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds,
+                                 uint32_t bodies_per_world, SfpBatch** out);
+SFP_API int32_t sfp_batch_destroy(SfpBatch* b);
+/* bodies: n_worlds * bodies_per_world descs, world-major */
+SFP_API int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies);
+SFP_API int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps);
+SFP_API int32_t sfp_batch_sync(SfpBatch* b);
+SFP_API int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out);
+/* per-world stats: out has room for n_worlds entries (n_pairs, n_contacts, n_colours ...) */
+SFP_API int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out);
+SFP_API const char* sfp_batch_last_error(SfpBatch* b);
+
+/* device-time of the last sfp_step / sfp_batch_step in milliseconds, measured with CUDA
+ * events on the world's own stream (0 from the oracle) */
+SFP_API int32_t sfp_last_step_ms(SfpWorld* w, float* ms);
+SFP_API int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms);
+
+/* library identification: "cuda-sm_100a" or "cpu-oracle" */
+SFP_API const char* sfp_backend(void);
+
+/* ---- oracle twins (libsfp_ref.so) -------------------------------------------------- */
+SFP_API int32_t sfp_ref_default_params(SfpParams* out);
+SFP_API int32_t sfp_ref_create(const SfpParams* params, SfpWorld** out);
+SFP_API int32_t sfp_ref_destroy(SfpWorld* w);
+SFP_API int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n);
+SFP_API int32_t sfp_ref_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n);
+SFP_API int32_t sfp_ref_step(SfpWorld* w, float dt, uint32_t substeps);
+SFP_API int32_t sfp_ref_sync(SfpWorld* w);
+SFP_API int32_t sfp_ref_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n);
+SFP_API int32_t sfp_ref_get_pairs(SfpWorld* w, SfpPair* out, uint32_t cap, uint32_t* n_out);
+SFP_API int32_t sfp_ref_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap,
+                                     uint32_t* n_out);
+SFP_API int32_t sfp_ref_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap,
+                                    uint32_t* joint_colours, uint32_t jcap);
+SFP_API int32_t sfp_ref_get_stats(SfpWorld* w, SfpStats* out);
+SFP_API const char* sfp_ref_last_error(SfpWorld* w);
+SFP_API int32_t sfp_ref_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out,
+                                  uint32_t n, float dt, uint32_t substeps);
+SFP_API int32_t sfp_ref_last_step_ms(SfpWorld* w, float* ms);
+SFP_API const char* sfp_ref_backend(void);
+/* oracle-only: brute-force O(n^2) candidate pairs of the CURRENT state (property tests) */
+SFP_API int32_t sfp_ref_brute_pairs(SfpWorld* w, float dt, SfpPair* out, uint32_t cap,
+                                    uint32_t* n_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFP_H_ */

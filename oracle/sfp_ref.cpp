@@ -1,0 +1,533 @@
+/* sfp_ref.cpp — CPU ORACLE for the physics substep loop.  TEST INFRASTRUCTURE, NOT PRODUCT.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+ * load this library.  The product path (starframe_b200/csrc, libsfp_b200.so) never links,
+ * loads or calls it.
+ *
+ * PARITY UNPINNED: the reference source tree is not mounted (/root/reference holds only
+ * README.md:1-3, "moved to Codeberg"), so there is no reference file:line to
+ * follow and no reference golden vector to pin against.  This file restates the step from
+ *   - BASELINE.json north_star (stage list: spatial-hash broadphase, narrowphase for circle /
+ *     capsule / rounded-polygon colliders, XPBD projection of contacts and distance/rope
+ *     joints, velocity update with friction and restitution), and
+ *   - the public XPBD rigid-body algorithm (Müller et al. 2020), Algorithm 2 + §3.5/3.6,
+ * in plain sequential C++ (single thread, Gauss-Seidel).  It is pinned to PHYSICS instead, by
+ * the analytic known-answer tests in tests/test_oracle_kat.py.
+ *
+ * The per-item arithmetic lives in include/sfp_math.h, compiled here with -ffp-contract=off.
+ * The data-parallel structure (hashing, sorting, colouring rounds, solve order) is restated
+ * here independently of the CUDA code: sequential loops over std::vector.
+ */
+#include <algorithm>
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "sfp.h"
+#include "sfp_host.h"
+#include "sfp_math.h"
+
+using namespace sfp;
+
+struct SfpWorld {
+    SfpParams p;
+    uint32_t n = 0;
+    std::vector<f4> pose, prev, vel, shape, mat;
+    std::vector<f2> minv;
+    std::vector<SfpJointDesc> joints;
+    /* per frame */
+    std::vector<SfpPair> pairs;          /* sorted by (a,b) */
+    std::vector<uint32_t> pair_colour;   /* aligned with pairs */
+    std::vector<uint32_t> joint_colour;  /* aligned with joints */
+    std::vector<ContactRec> contacts;    /* aligned with pairs */
+    std::vector<f4> lambdas;             /* aligned with pairs: ln0, lt0, ln1, lt1 */
+    uint32_t n_colours = 0, colour_rounds = 0, n_entries = 0;
+    SfpStats stats;
+    std::string err;
+    float last_ms = 0.0f;
+    bool stepped = false;
+};
+
+namespace {
+
+struct Entry {
+    uint32_t key, body;
+};
+
+bool is_dynamic(const SfpWorld& w, uint32_t i) { return w.minv[i].x > 0.0f || w.minv[i].y > 0.0f; }
+
+bool pair_allowed(const SfpWorld& w, uint32_t a, uint32_t b) {
+    if (!is_dynamic(w, a) && !is_dynamic(w, b)) return false;
+    return layers_collide(f2u(w.mat[a].w), f2u(w.mat[b].w));
+}
+
+void compute_aabbs(const SfpWorld& w, float dt, std::vector<f4>& aabb) {
+    aabb.resize(w.n);
+    for (uint32_t i = 0; i < w.n; ++i)
+        aabb[i] = body_aabb(w.pose[i], w.vel[i], w.shape[i], w.p.aabb_margin, w.p.vel_expand, dt);
+}
+
+/* A2: every body is entered into each cell its expanded AABB touches; inside a cell every two
+ * entries are tested; a pair is reported only from the cell that holds the lower corner of
+ * the two cell ranges' intersection, which makes the report unique without deduplication. */
+int broadphase(SfpWorld& w, float dt) {
+    std::vector<f4> aabb;
+    compute_aabbs(w, dt, aabb);
+    float inv = 1.0f / w.p.cell_size;
+    std::vector<Entry> entries;
+    std::vector<int> cx0(w.n), cy0(w.n);
+    for (uint32_t i = 0; i < w.n; ++i) {
+        int x0 = cell_coord(aabb[i].x, inv), y0 = cell_coord(aabb[i].y, inv);
+        int x1 = cell_coord(aabb[i].z, inv), y1 = cell_coord(aabb[i].w, inv);
+        cx0[i] = x0;
+        cy0[i] = y0;
+        for (int cy = y0; cy <= y1; ++cy)
+            for (int cx = x0; cx <= x1; ++cx) entries.push_back({cell_key(cx, cy), i});
+    }
+    w.n_entries = (uint32_t)entries.size();
+    if (w.p.max_entries && entries.size() > w.p.max_entries) {
+        w.stats.overflow |= 1u;
+        w.err = "broadphase entry capacity exceeded";
+        return SFP_E_CAPACITY;
+    }
+    std::stable_sort(entries.begin(), entries.end(),
+                     [](const Entry& a, const Entry& b) { return a.key < b.key; });
+    w.pairs.clear();
+    size_t i = 0;
+    while (i < entries.size()) {
+        size_t j = i;
+        while (j < entries.size() && entries[j].key == entries[i].key) ++j;
+        int cx = key_cx(entries[i].key), cy = key_cy(entries[i].key);
+        for (size_t u = i; u < j; ++u)
+            for (size_t v = u + 1; v < j; ++v) {
+                uint32_t a = entries[u].body, b = entries[v].body;
+                if (a == b) continue;
+                if (std::max(cx0[a], cx0[b]) != cx || std::max(cy0[a], cy0[b]) != cy) continue;
+                if (!aabb_overlap(aabb[a], aabb[b])) continue;
+                if (!pair_allowed(w, a, b)) continue;
+                SfpPair p = {std::min(a, b), std::max(a, b)};
+                w.pairs.push_back(p);
+            }
+        i = j;
+    }
+    std::sort(w.pairs.begin(), w.pairs.end(), [](const SfpPair& x, const SfpPair& y) {
+        return x.a != y.a ? x.a < y.a : x.b < y.b;
+    });
+    if (w.p.max_pairs && w.pairs.size() > w.p.max_pairs) {
+        w.stats.overflow |= 2u;
+        w.err = "pair capacity exceeded";
+        return SFP_E_CAPACITY;
+    }
+    return SFP_OK;
+}
+
+/* A8: rounds of "every body grants its lowest-priority-key uncoloured constraint; a
+ * constraint granted by all its dynamic bodies takes the lowest colour free on them". */
+int colour_constraints(SfpWorld& w) {
+    const uint32_t P = (uint32_t)w.pairs.size(), J = (uint32_t)w.joints.size();
+    const uint32_t UNC = 0xffffffffu;
+    w.pair_colour.assign(P, UNC);
+    w.joint_colour.assign(J, UNC);
+    std::vector<uint64_t> mask(w.n, 0ull), claim(w.n);
+    std::vector<uint64_t> pkey(P), jkey(J);
+    for (uint32_t k = 0; k < P; ++k) pkey[k] = pair_priority(w.pairs[k].a, w.pairs[k].b);
+    for (uint32_t k = 0; k < J; ++k) jkey[k] = joint_priority(k);
+    uint32_t remaining = P + J, rounds = 0, ncol = 0;
+    bool overflow = false;
+    /* constraints without a dynamic end never conflict: colour 0 */
+    for (uint32_t k = 0; k < J; ++k)
+        if (!is_dynamic(w, w.joints[k].body_a) && !is_dynamic(w, w.joints[k].body_b)) {
+            w.joint_colour[k] = 0;
+            --remaining;
+            ncol = std::max(ncol, 1u);
+        }
+    while (remaining > 0) {
+        ++rounds;
+        std::fill(claim.begin(), claim.end(), SFP_NO_CLAIM);
+        auto bid = [&](uint32_t body, uint64_t key) {
+            if (is_dynamic(w, body)) claim[body] = std::min(claim[body], key);
+        };
+        for (uint32_t k = 0; k < P; ++k)
+            if (w.pair_colour[k] == UNC) {
+                bid(w.pairs[k].a, pkey[k]);
+                bid(w.pairs[k].b, pkey[k]);
+            }
+        for (uint32_t k = 0; k < J; ++k)
+            if (w.joint_colour[k] == UNC) {
+                bid(w.joints[k].body_a, jkey[k]);
+                bid(w.joints[k].body_b, jkey[k]);
+            }
+        auto try_take = [&](uint32_t a, uint32_t b, uint64_t key, uint32_t* colour) {
+            bool da = is_dynamic(w, a), db = is_dynamic(w, b);
+            if (da && claim[a] != key) return;
+            if (db && claim[b] != key) return;
+            uint64_t m = (da ? mask[a] : 0ull) | (db ? mask[b] : 0ull);
+            int c = lowest_free(m);
+            if (c >= SFP_MAX_COLOURS) {
+                overflow = true;
+                c = SFP_MAX_COLOURS - 1;
+            }
+            if (da) mask[a] |= 1ull << c;
+            if (db) mask[b] |= 1ull << c;
+            *colour = (uint32_t)c;
+            ncol = std::max(ncol, (uint32_t)c + 1u);
+            --remaining;
+        };
+        for (uint32_t k = 0; k < P; ++k)
+            if (w.pair_colour[k] == UNC)
+                try_take(w.pairs[k].a, w.pairs[k].b, pkey[k], &w.pair_colour[k]);
+        for (uint32_t k = 0; k < J; ++k)
+            if (w.joint_colour[k] == UNC)
+                try_take(w.joints[k].body_a, w.joints[k].body_b, jkey[k], &w.joint_colour[k]);
+    }
+    w.n_colours = ncol;
+    w.colour_rounds = rounds;
+    if (overflow) {
+        w.stats.overflow |= 4u;
+        w.err = "more than 64 constraint colours needed";
+        return SFP_E_CAPACITY;
+    }
+    return SFP_OK;
+}
+
+BodyPos load_pos(const SfpWorld& w, uint32_t i) {
+    BodyPos b;
+    b.x = mk(w.pose[i].x, w.pose[i].y);
+    b.q = mk(w.pose[i].z, w.pose[i].w);
+    b.d = mk(w.prev[i].x, w.prev[i].y);
+    b.qp = mk(w.prev[i].z, w.prev[i].w);
+    b.im = w.minv[i].x;
+    b.ii = w.minv[i].y;
+    return b;
+}
+void store_pos(SfpWorld& w, uint32_t i, const BodyPos& b) {
+    if (!is_dynamic(w, i)) return;
+    w.pose[i].x = b.x.x;
+    w.pose[i].y = b.x.y;
+    w.pose[i].z = b.q.x;
+    w.pose[i].w = b.q.y;
+    w.prev[i].x = b.d.x;
+    w.prev[i].y = b.d.y;
+}
+
+void solve_pair_position(SfpWorld& w, uint32_t k) {
+    const ContactRec& c = w.contacts[k];
+    uint32_t cnt = f2u(c.b.y);
+    f4 lam = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (cnt > 0) {
+        uint32_t a = w.pairs[k].a, b = w.pairs[k].b;
+        BodyPos A = load_pos(w, a), B = load_pos(w, b);
+        v2 n = mk(c.a.x, c.a.y);
+        lam = solve_contact_manifold(&A, &B, n, cnt, mk(c.p0.x, c.p0.y), mk(c.p0.z, c.p0.w),
+                                     mk(c.p1.x, c.p1.y), mk(c.p1.z, c.p1.w), c.a.z);
+        store_pos(w, a, A);
+        store_pos(w, b, B);
+    }
+    w.lambdas[k] = lam;
+}
+
+void solve_joint_position(SfpWorld& w, uint32_t k, float inv_h2) {
+    const SfpJointDesc& j = w.joints[k];
+    BodyPos A = load_pos(w, j.body_a), B = load_pos(w, j.body_b);
+    solve_joint(&A, &B, mk(j.ax, j.ay), mk(j.bx, j.by), j.rest, j.compliance, j.kind, inv_h2);
+    store_pos(w, j.body_a, A);
+    store_pos(w, j.body_b, B);
+}
+
+void solve_pair_velocity(SfpWorld& w, uint32_t k, float h, float rest_threshold) {
+    const ContactRec& c = w.contacts[k];
+    uint32_t cnt = f2u(c.b.y);
+    f4 lam = w.lambdas[k];
+    if (cnt == 0 || !(lam.x > 0.0f || lam.z > 0.0f)) return;
+    uint32_t a = w.pairs[k].a, b = w.pairs[k].b;
+    BodyVel A, B;
+    A.v = mk(w.vel[a].x, w.vel[a].y);
+    A.w = w.vel[a].z;
+    A.im = w.minv[a].x;
+    A.ii = w.minv[a].y;
+    B.v = mk(w.vel[b].x, w.vel[b].y);
+    B.w = w.vel[b].z;
+    B.im = w.minv[b].x;
+    B.ii = w.minv[b].y;
+    v2 qa = mk(w.pose[a].z, w.pose[a].w), qb = mk(w.pose[b].z, w.pose[b].w);
+    v2 n = mk(c.a.x, c.a.y);
+    solve_manifold_velocity(&A, &B, qa, qb, n, cnt, mk(c.p0.x, c.p0.y), mk(c.p0.z, c.p0.w),
+                            mk(c.p1.x, c.p1.y), mk(c.p1.z, c.p1.w), lam, c.b.z, c.b.w, c.a.z, c.a.w,
+                            c.b.x, h, rest_threshold);
+    if (is_dynamic(w, a)) {
+        w.vel[a].x = A.v.x;
+        w.vel[a].y = A.v.y;
+        w.vel[a].z = A.w;
+    }
+    if (is_dynamic(w, b)) {
+        w.vel[b].x = B.v.x;
+        w.vel[b].y = B.v.y;
+        w.vel[b].z = B.w;
+    }
+}
+
+void substep(SfpWorld& w, float h) {
+    const uint32_t P = (uint32_t)w.pairs.size(), J = (uint32_t)w.joints.size();
+    const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    const float g = sqrtf(w.p.gravity_x * w.p.gravity_x + w.p.gravity_y * w.p.gravity_y);
+    const float rest_threshold = 2.0f * g * h;
+    /* A3 */
+    for (uint32_t i = 0; i < w.n; ++i) {
+        integrate_body(&w.pose[i], &w.prev[i], &w.vel[i], w.minv[i], w.p.gravity_x, w.p.gravity_y, h);
+    }
+    /* A4 */
+    w.contacts.resize(P);
+    w.lambdas.assign(P, f4{0.0f, 0.0f, 0.0f, 0.0f});
+    uint32_t npts = 0, nman = 0;
+    float maxpen = 0.0f;
+    for (uint32_t k = 0; k < P; ++k) {
+        uint32_t a = w.pairs[k].a, b = w.pairs[k].b;
+        w.contacts[k] = narrowphase(w.pose[a], w.vel[a], w.shape[a], w.mat[a], w.pose[b], w.vel[b],
+                                    w.shape[b], w.mat[b], w.p.contact_margin);
+        uint32_t cnt = f2u(w.contacts[k].b.y);
+        npts += cnt;
+        nman += cnt > 0 ? 1u : 0u;
+        if (cnt > 0) maxpen = std::max(maxpen, -w.contacts[k].s.x);
+        if (cnt > 1) maxpen = std::max(maxpen, -w.contacts[k].s.y);
+    }
+    w.stats.n_contacts = npts;
+    w.stats.n_manifolds = nman;
+    w.stats.max_penetration = maxpen;
+    /* A5 + A6 */
+    if (w.p.solver_order == SFP_ORDER_REFERENCE) {
+        for (uint32_t k = 0; k < J; ++k) solve_joint_position(w, k, inv_h2);
+        for (uint32_t k = 0; k < P; ++k) solve_pair_position(w, k);
+    } else {
+        for (uint32_t c = 0; c < w.n_colours; ++c) {
+            for (uint32_t k = 0; k < J; ++k)
+                if (w.joint_colour[k] == c) solve_joint_position(w, k, inv_h2);
+            for (uint32_t k = 0; k < P; ++k)
+                if (w.pair_colour[k] == c) solve_pair_position(w, k);
+        }
+    }
+    /* A7 (i) */
+    for (uint32_t i = 0; i < w.n; ++i)
+        w.vel[i] = derive_velocity(w.pose[i], w.prev[i], w.vel[i], w.minv[i], inv_h);
+    /* A7 (ii) */
+    if (w.p.solver_order == SFP_ORDER_REFERENCE) {
+        for (uint32_t k = 0; k < P; ++k) solve_pair_velocity(w, k, h, rest_threshold);
+    } else {
+        for (uint32_t c = 0; c < w.n_colours; ++c)
+            for (uint32_t k = 0; k < P; ++k)
+                if (w.pair_colour[k] == c) solve_pair_velocity(w, k, h, rest_threshold);
+    }
+}
+
+int frame(SfpWorld& w, float dt, uint32_t substeps) {
+    const float h = dt / (float)substeps;
+    const bool every = (w.p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP) != 0u;
+    int rc;
+    if (!every) {
+        if ((rc = broadphase(w, dt)) != SFP_OK) return rc;
+        if ((rc = colour_constraints(w)) != SFP_OK) return rc;
+    }
+    for (uint32_t s = 0; s < substeps; ++s) {
+        if (every) {
+            if ((rc = broadphase(w, h)) != SFP_OK) return rc;
+            if ((rc = colour_constraints(w)) != SFP_OK) return rc;
+        }
+        substep(w, h);
+    }
+    w.stats.frames += 1;
+    w.stats.body_substeps += (uint64_t)w.n * substeps;
+    w.stepped = true;
+    return SFP_OK;
+}
+
+} /* namespace */
+
+extern "C" {
+
+int32_t sfp_ref_default_params(SfpParams* out) {
+    if (!out) return SFP_E_INVALID;
+    default_params(out);
+    return SFP_OK;
+}
+
+int32_t sfp_ref_create(const SfpParams* params, SfpWorld** out) {
+    if (!out) return SFP_E_INVALID;
+    *out = nullptr;
+    SfpParams p;
+    if (params) p = *params;
+    else default_params(&p);
+    if (!params_valid(p)) return SFP_E_INVALID;
+    SfpWorld* w = new (std::nothrow) SfpWorld();
+    if (!w) return SFP_E_NOMEM;
+    w->p = p;
+    std::memset(&w->stats, 0, sizeof(w->stats));
+    *out = w;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_destroy(SfpWorld* w) {
+    delete w;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
+    if (!w || (n && !bodies)) return SFP_E_INVALID;
+    if (n > SFP_MAX_BODIES || (w->p.max_bodies && n > w->p.max_bodies)) {
+        w->err = "too many bodies";
+        return SFP_E_CAPACITY;
+    }
+    for (uint32_t i = 0; i < n; ++i)
+        if (!desc_valid(bodies[i])) {
+            w->err = "invalid body desc at index " + std::to_string(i);
+            return SFP_E_INVALID;
+        }
+    for (const SfpJointDesc& j : w->joints)
+        if (j.body_a >= n || j.body_b >= n) {
+            w->err = "existing joints reference bodies beyond the new count";
+            return SFP_E_INVALID;
+        }
+    w->n = n;
+    w->pose.resize(n);
+    w->prev.resize(n);
+    w->vel.resize(n);
+    w->shape.resize(n);
+    w->mat.resize(n);
+    w->minv.resize(n);
+    uint32_t ndyn = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        body_from_desc(bodies[i], &w->pose[i], &w->vel[i], &w->minv[i], &w->shape[i], &w->mat[i]);
+        w->prev[i] = w->pose[i];
+        ndyn += is_dynamic(*w, i) ? 1u : 0u;
+    }
+    w->stats.n_bodies = n;
+    w->stats.n_dynamic = ndyn;
+    w->pairs.clear();
+    w->contacts.clear();
+    w->lambdas.clear();
+    w->pair_colour.clear();
+    w->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n) {
+    if (!w || (n && !joints)) return SFP_E_INVALID;
+    if (w->p.max_joints && n > w->p.max_joints) return SFP_E_CAPACITY;
+    for (uint32_t i = 0; i < n; ++i)
+        if (!joint_valid(joints[i], w->n)) {
+            w->err = "invalid joint desc at index " + std::to_string(i);
+            return SFP_E_INVALID;
+        }
+    w->joints.assign(joints, joints + n);
+    w->joint_colour.clear();
+    w->stats.n_joints = n;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_step(SfpWorld* w, float dt, uint32_t substeps) {
+    if (!w || !(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
+    auto t0 = std::chrono::steady_clock::now();
+    int rc = frame(*w, dt, substeps);
+    auto t1 = std::chrono::steady_clock::now();
+    w->last_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    return rc;
+}
+
+int32_t sfp_ref_sync(SfpWorld* w) { return w ? SFP_OK : SFP_E_INVALID; }
+
+int32_t sfp_ref_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
+    if (!w || (n && !out) || n > w->n) return SFP_E_INVALID;
+    for (uint32_t i = 0; i < n; ++i) out[i] = state_from_records(w->pose[i], w->vel[i]);
+    return SFP_OK;
+}
+
+int32_t sfp_ref_get_pairs(SfpWorld* w, SfpPair* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    *n_out = (uint32_t)w->pairs.size();
+    uint32_t m = std::min<uint32_t>(cap, *n_out);
+    if (m) std::memcpy(out, w->pairs.data(), sizeof(SfpPair) * m);
+    return SFP_OK;
+}
+
+int32_t sfp_ref_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    uint32_t cnt = 0;
+    for (size_t k = 0; k < w->contacts.size() && k < w->pairs.size(); ++k) {
+        if (f2u(w->contacts[k].b.y) == 0) continue;
+        if (cnt < cap) {
+            uint32_t a = w->pairs[k].a, b = w->pairs[k].b;
+            out[cnt] = contact_from_records(a, b, w->contacts[k], w->lambdas[k], w->pose[a],
+                                            w->pose[b]);
+        }
+        ++cnt;
+    }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap,
+                            uint32_t* joint_colours, uint32_t jcap) {
+    if (!w) return SFP_E_INVALID;
+    if (pair_colours)
+        for (uint32_t k = 0; k < cap && k < w->pair_colour.size(); ++k)
+            pair_colours[k] = w->pair_colour[k];
+    if (joint_colours)
+        for (uint32_t k = 0; k < jcap && k < w->joint_colour.size(); ++k)
+            joint_colours[k] = w->joint_colour[k];
+    return SFP_OK;
+}
+
+int32_t sfp_ref_get_stats(SfpWorld* w, SfpStats* out) {
+    if (!w || !out) return SFP_E_INVALID;
+    w->stats.n_entries = w->n_entries;
+    w->stats.n_pairs = (uint32_t)w->pairs.size();
+    w->stats.n_colours = w->n_colours;
+    w->stats.colour_rounds = w->colour_rounds;
+    energies(w->pose, w->vel, w->minv, w->p.gravity_x, w->p.gravity_y, &w->stats.kinetic_energy,
+             &w->stats.potential_energy);
+    *out = w->stats;
+    return SFP_OK;
+}
+
+const char* sfp_ref_last_error(SfpWorld* w) { return w ? w->err.c_str() : "null world"; }
+
+int32_t sfp_ref_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, uint32_t n,
+                          float dt, uint32_t substeps) {
+    if (!w || !in || !out || n != w->n) return SFP_E_INVALID;
+    for (uint32_t i = 0; i < n; ++i) {
+        records_from_state(in[i], w->minv[i], &w->pose[i], &w->vel[i]);
+        w->prev[i] = w->pose[i];
+    }
+    int rc = sfp_ref_step(w, dt, substeps);
+    if (rc != SFP_OK) return rc;
+    return sfp_ref_download_bodies(w, out, n);
+}
+
+int32_t sfp_ref_last_step_ms(SfpWorld* w, float* ms) {
+    if (!w || !ms) return SFP_E_INVALID;
+    *ms = w->last_ms;
+    return SFP_OK;
+}
+
+const char* sfp_ref_backend(void) { return "cpu-oracle"; }
+
+int32_t sfp_ref_brute_pairs(SfpWorld* w, float dt, SfpPair* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    std::vector<f4> aabb;
+    compute_aabbs(*w, dt, aabb);
+    uint32_t cnt = 0;
+    for (uint32_t a = 0; a < w->n; ++a)
+        for (uint32_t b = a + 1; b < w->n; ++b) {
+            if (!aabb_overlap(aabb[a], aabb[b])) continue;
+            if (!pair_allowed(*w, a, b)) continue;
+            if (cnt < cap) {
+                out[cnt].a = a;
+                out[cnt].b = b;
+            }
+            ++cnt;
+        }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
+} /* extern "C" */

@@ -1,0 +1,370 @@
+"""ctypes binding of the C ABI declared in include/sfp.h.
+
+`Api(lib_path, prefix)` binds one shared library.  The product package only ever binds
+`starframe_b200/csrc/libsfp_b200.so` (prefix ``sfp_``) and raises if it is missing — there is no
+CPU fallback.  `oracle/loader.py` (tests / bench cpu_baseline / smoke only) binds the oracle with
+the prefix ``sfp_ref_`` through the same class, so parity tests are backend-generic.
+
+Reference: the reference's `Physics` API cannot be cited by file:line (tree not mounted,
+BASELINE.md §0); this mirrors SURVEY.md §8b.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+SFP_OK = 0
+SFP_E_INVALID = -1
+SFP_E_CUDA = -2
+SFP_E_CAPACITY = -3
+SFP_E_NCCL = -4
+SFP_E_NOMEM = -5
+
+SHAPE_CIRCLE, SHAPE_CAPSULE, SHAPE_RECT = 0, 1, 2
+BODY_STATIC = 1
+ORDER_COLOUR, ORDER_REFERENCE = 0, 1
+JOINT_DISTANCE, JOINT_ROPE = 0, 1
+FLAG_BROADPHASE_EVERY_SUBSTEP = 1
+FLAG_MULTI_KERNEL = 2
+
+# numpy mirrors of the PODs (sizes asserted against the C side's static_asserts)
+PARAMS_DTYPE = np.dtype(
+    [
+        ("gravity_x", "<f4"), ("gravity_y", "<f4"), ("cell_size", "<f4"),
+        ("aabb_margin", "<f4"), ("vel_expand", "<f4"), ("contact_margin", "<f4"),
+        ("solver_order", "<u4"), ("flags", "<u4"), ("max_bodies", "<u4"),
+        ("max_joints", "<u4"), ("max_entries", "<u4"), ("max_pairs", "<u4"),
+        ("device", "<i4"), ("reserved", "<u4", (3,)),
+    ]
+)
+BODY_DESC_DTYPE = np.dtype(
+    [
+        ("x", "<f4"), ("y", "<f4"), ("angle", "<f4"),
+        ("vx", "<f4"), ("vy", "<f4"), ("omega", "<f4"),
+        ("hx", "<f4"), ("hy", "<f4"), ("radius", "<f4"),
+        ("shape", "<u4"), ("density", "<f4"),
+        ("mu_s", "<f4"), ("mu_d", "<f4"), ("restitution", "<f4"),
+        ("category", "<u2"), ("mask", "<u2"), ("flags", "<u4"),
+    ]
+)
+JOINT_DESC_DTYPE = np.dtype(
+    [
+        ("body_a", "<u4"), ("body_b", "<u4"), ("ax", "<f4"), ("ay", "<f4"),
+        ("bx", "<f4"), ("by", "<f4"), ("rest", "<f4"), ("compliance", "<f4"),
+        ("kind", "<u4"), ("reserved", "<u4", (3,)),
+    ]
+)
+BODY_STATE_DTYPE = np.dtype(
+    [
+        ("x", "<f4"), ("y", "<f4"), ("c", "<f4"), ("s", "<f4"),
+        ("vx", "<f4"), ("vy", "<f4"), ("omega", "<f4"), ("angle", "<f4"),
+    ]
+)
+PAIR_DTYPE = np.dtype([("a", "<u4"), ("b", "<u4")])
+CONTACT_DTYPE = np.dtype(
+    [
+        ("a", "<u4"), ("b", "<u4"), ("count", "<u4"), ("nx", "<f4"), ("ny", "<f4"),
+        ("depth", "<f4", (2,)), ("px", "<f4", (2,)), ("py", "<f4", (2,)),
+        ("lambda_n", "<f4", (2,)), ("lambda_t", "<f4", (2,)),
+    ]
+)
+STATS_DTYPE = np.dtype(
+    [
+        ("frames", "<u8"), ("body_substeps", "<u8"),
+        ("n_bodies", "<u4"), ("n_dynamic", "<u4"), ("n_joints", "<u4"),
+        ("n_entries", "<u4"), ("n_pairs", "<u4"), ("n_contacts", "<u4"),
+        ("n_manifolds", "<u4"), ("n_colours", "<u4"), ("colour_rounds", "<u4"),
+        ("overflow", "<u4"), ("max_penetration", "<f4"), ("kinetic_energy", "<f4"),
+        ("potential_energy", "<f4"), ("reserved", "<u4", (3,)),
+    ]
+)
+assert PARAMS_DTYPE.itemsize == 64
+assert BODY_DESC_DTYPE.itemsize == 64
+assert JOINT_DESC_DTYPE.itemsize == 48
+assert BODY_STATE_DTYPE.itemsize == 32
+assert PAIR_DTYPE.itemsize == 8
+assert CONTACT_DTYPE.itemsize == 60
+assert STATS_DTYPE.itemsize == 80
+
+# every symbol include/sfp.h declares for the product library (checked by the CPU tests)
+PRODUCT_SYMBOLS = [
+    "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
+    "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
+    "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
+    "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
+    "backend",
+]
+ORACLE_SYMBOLS = [
+    "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
+    "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
+    "step_host", "last_step_ms", "backend", "brute_pairs",
+]
+
+
+class SfpError(RuntimeError):
+    def __init__(self, code: int, what: str, detail: str = ""):
+        self.code = code
+        names = {-1: "SFP_E_INVALID", -2: "SFP_E_CUDA", -3: "SFP_E_CAPACITY",
+                 -4: "SFP_E_NCCL", -5: "SFP_E_NOMEM"}
+        super().__init__(f"{what}: {names.get(code, code)}" + (f" ({detail})" if detail else ""))
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Api:
+    """One bound shared library exporting `<prefix>*`."""
+
+    def __init__(self, lib_path: str, prefix: str):
+        if not os.path.exists(lib_path):
+            raise ImportError(
+                f"{lib_path} is missing — build it first (python -c 'import __graft_entry__ as g; "
+                "g.build()').  There is no fallback path."
+            )
+        self.path = lib_path
+        self.prefix = prefix
+        self.lib = C.CDLL(lib_path)
+        self._bind()
+
+    def fn(self, name: str):
+        return getattr(self.lib, self.prefix + name)
+
+    def has(self, name: str) -> bool:
+        try:
+            self.fn(name)
+            return True
+        except AttributeError:
+            return False
+
+    def _bind(self):
+        vp, u32, f32, i32 = C.c_void_p, C.c_uint32, C.c_float, C.c_int32
+        sig = {
+            "default_params": [vp],
+            "create": [vp, C.POINTER(vp)],
+            "destroy": [vp],
+            "upload_bodies": [vp, vp, u32],
+            "set_joints": [vp, vp, u32],
+            "step": [vp, f32, u32],
+            "sync": [vp],
+            "download_bodies": [vp, vp, u32],
+            "get_pairs": [vp, vp, u32, C.POINTER(u32)],
+            "get_contacts": [vp, vp, u32, C.POINTER(u32)],
+            "get_colours": [vp, vp, u32, vp, u32],
+            "get_stats": [vp, vp],
+            "step_host": [vp, vp, vp, u32, f32, u32],
+            "last_step_ms": [vp, C.POINTER(f32)],
+            "brute_pairs": [vp, f32, vp, u32, C.POINTER(u32)],
+            "batch_create": [vp, u32, u32, C.POINTER(vp)],
+            "batch_destroy": [vp],
+            "batch_upload": [vp, vp],
+            "batch_step": [vp, f32, u32],
+            "batch_sync": [vp],
+            "batch_download": [vp, vp],
+            "batch_stats": [vp, vp],
+            "batch_last_step_ms": [vp, C.POINTER(f32)],
+        }
+        for name, args in sig.items():
+            if not self.has(name):
+                continue
+            f = self.fn(name)
+            f.argtypes = args
+            f.restype = i32
+        for name in ("last_error", "batch_last_error"):
+            if self.has(name):
+                f = self.fn(name)
+                f.argtypes = [vp]
+                f.restype = C.c_char_p
+        if self.has("backend"):
+            self.fn("backend").argtypes = []
+            self.fn("backend").restype = C.c_char_p
+
+    def backend(self) -> str:
+        return self.fn("backend")().decode()
+
+    def default_params(self) -> np.ndarray:
+        p = np.zeros(1, dtype=PARAMS_DTYPE)
+        rc = self.fn("default_params")(_ptr(p))
+        if rc != SFP_OK:
+            raise SfpError(rc, "default_params")
+        return p
+
+
+class World:
+    """Thin RAII wrapper over SfpWorld* for one bound library."""
+
+    def __init__(self, api: Api, params: np.ndarray | None = None, **overrides):
+        self.api = api
+        p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1).copy()
+        for k, v in overrides.items():
+            p[k] = v
+        self.params = p
+        h = C.c_void_p()
+        rc = api.fn("create")(_ptr(p), C.byref(h))
+        if rc != SFP_OK:
+            raise SfpError(rc, "create")
+        self.h = h
+        self.n = 0
+        self.n_joints = 0
+
+    def _check(self, rc: int, what: str):
+        if rc != SFP_OK:
+            detail = self.api.fn("last_error")(self.h)
+            raise SfpError(rc, what, detail.decode() if detail else "")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.api.fn("destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def upload_bodies(self, bodies: np.ndarray):
+        b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE)
+        self._check(self.api.fn("upload_bodies")(self.h, _ptr(b), b.shape[0]), "upload_bodies")
+        self.n = int(b.shape[0])
+
+    def set_joints(self, joints: np.ndarray):
+        j = np.ascontiguousarray(joints, dtype=JOINT_DESC_DTYPE)
+        self._check(self.api.fn("set_joints")(self.h, _ptr(j), j.shape[0]), "set_joints")
+        self.n_joints = int(j.shape[0])
+
+    def step(self, dt: float = 1.0 / 60.0, substeps: int = 8):
+        self._check(self.api.fn("step")(self.h, dt, substeps), "step")
+
+    def sync(self):
+        self._check(self.api.fn("sync")(self.h), "sync")
+
+    def download_bodies(self) -> np.ndarray:
+        out = np.zeros(self.n, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("download_bodies")(self.h, _ptr(out), self.n), "download_bodies")
+        return out
+
+    def step_host(self, states: np.ndarray, dt: float = 1.0 / 60.0, substeps: int = 8,
+                  out: np.ndarray | None = None) -> np.ndarray:
+        s = np.ascontiguousarray(states, dtype=BODY_STATE_DTYPE)
+        if out is None:
+            out = np.zeros(self.n, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("step_host")(self.h, _ptr(s), _ptr(out), self.n, dt, substeps),
+                    "step_host")
+        return out
+
+    def get_pairs(self) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(self.api.fn("get_pairs")(self.h, None, 0, C.byref(n)), "get_pairs")
+        out = np.zeros(n.value, dtype=PAIR_DTYPE)
+        if n.value:
+            self._check(self.api.fn("get_pairs")(self.h, _ptr(out), n.value, C.byref(n)), "get_pairs")
+        return out
+
+    def get_contacts(self) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(self.api.fn("get_contacts")(self.h, None, 0, C.byref(n)), "get_contacts")
+        out = np.zeros(n.value, dtype=CONTACT_DTYPE)
+        if n.value:
+            self._check(self.api.fn("get_contacts")(self.h, _ptr(out), n.value, C.byref(n)),
+                        "get_contacts")
+        return out
+
+    def get_colours(self):
+        pairs = self.get_pairs()
+        pc = np.zeros(pairs.shape[0], dtype=np.uint32)
+        jc = np.zeros(self.n_joints, dtype=np.uint32)
+        self._check(
+            self.api.fn("get_colours")(self.h, _ptr(pc), pc.shape[0], _ptr(jc), jc.shape[0]),
+            "get_colours",
+        )
+        return pairs, pc, jc
+
+    def stats(self) -> dict:
+        s = np.zeros(1, dtype=STATS_DTYPE)
+        self._check(self.api.fn("get_stats")(self.h, _ptr(s)), "get_stats")
+        return {k: (s[k][0].item() if s[k][0].shape == () else s[k][0].tolist())
+                for k in STATS_DTYPE.names if k != "reserved"}
+
+    def last_step_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self.api.fn("last_step_ms")(self.h, C.byref(ms)), "last_step_ms")
+        return float(ms.value)
+
+    def brute_pairs(self, dt: float) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(self.api.fn("brute_pairs")(self.h, dt, None, 0, C.byref(n)), "brute_pairs")
+        out = np.zeros(n.value, dtype=PAIR_DTYPE)
+        if n.value:
+            self._check(self.api.fn("brute_pairs")(self.h, dt, _ptr(out), n.value, C.byref(n)),
+                        "brute_pairs")
+        return out
+
+
+class Batch:
+    """RAII wrapper over SfpBatch* (product library only)."""
+
+    def __init__(self, api: Api, n_worlds: int, bodies_per_world: int,
+                 params: np.ndarray | None = None, **overrides):
+        self.api = api
+        p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1).copy()
+        for k, v in overrides.items():
+            p[k] = v
+        self.params = p
+        self.n_worlds = int(n_worlds)
+        self.bpw = int(bodies_per_world)
+        h = C.c_void_p()
+        rc = api.fn("batch_create")(_ptr(p), self.n_worlds, self.bpw, C.byref(h))
+        if rc != SFP_OK:
+            raise SfpError(rc, "batch_create")
+        self.h = h
+
+    def _check(self, rc: int, what: str):
+        if rc != SFP_OK:
+            detail = self.api.fn("batch_last_error")(self.h)
+            raise SfpError(rc, what, detail.decode() if detail else "")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.api.fn("batch_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, bodies: np.ndarray):
+        b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE).reshape(-1)
+        assert b.shape[0] == self.n_worlds * self.bpw
+        self._check(self.api.fn("batch_upload")(self.h, _ptr(b)), "batch_upload")
+
+    def step(self, dt: float = 1.0 / 60.0, substeps: int = 8):
+        self._check(self.api.fn("batch_step")(self.h, dt, substeps), "batch_step")
+
+    def sync(self):
+        self._check(self.api.fn("batch_sync")(self.h), "batch_sync")
+
+    def download(self) -> np.ndarray:
+        out = np.zeros(self.n_worlds * self.bpw, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("batch_download")(self.h, _ptr(out)), "batch_download")
+        return out.reshape(self.n_worlds, self.bpw)
+
+    def stats(self) -> np.ndarray:
+        out = np.zeros(self.n_worlds, dtype=STATS_DTYPE)
+        self._check(self.api.fn("batch_stats")(self.h, _ptr(out)), "batch_stats")
+        return out
+
+    def last_step_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self.api.fn("batch_last_step_ms")(self.h, C.byref(ms)), "batch_last_step_ms")
+        return float(ms.value)

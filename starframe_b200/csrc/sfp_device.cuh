@@ -1,0 +1,450 @@
+// sfp_device.cuh — device-side stages of the physics step for ONE world in global memory.
+//
+// Each stage is a __device__ function written as a grid-stride loop over (tid, nthreads) so the
+// same code runs (a) inside the persistent cooperative kernels, separated by grid.sync(), which
+// is the product path (no per-substep host launches, north_star), and (b) as one plain kernel
+// per stage (SFP_FLAG_MULTI_KERNEL, debugging / profiling).
+//
+// Per-item arithmetic comes from include/sfp_math.h (shared with the oracle, FMA contraction
+// off).  Data layout (SoA): one float4 array per record, 88 B/body; contacts
+// 6 x float4 per candidate pair, stored in colour-sorted pair order so every solver colour
+// reads and writes a contiguous range; bodies are the only gathered accesses.
+//
+// Reference: the reference's step is CPU Rust and is not mounted; stage names
+// follow north_star / SURVEY.md §8a rows A2..A8.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "sfp_math.h"
+
+namespace sfpk {
+
+using sfp::f2;
+using sfp::f4;
+using sfp::v2;
+
+constexpr uint32_t UNCOLOURED = 0xffffffffu;
+constexpr int MAX_ROUNDS = 512;
+
+struct Counters {
+    uint32_t n_bodies, n_joints;
+    uint32_t n_entries, n_pairs;
+    uint32_t n_colours, colour_rounds;
+    uint32_t overflow;
+    uint32_t n_contacts, n_manifolds, maxpen_bits;
+    uint32_t pad[2];
+    uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
+    uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
+    uint32_t round_flags[MAX_ROUNDS];
+};
+
+struct Ctx {
+    // body state
+    float4 *pose, *prev, *vel;
+    const float4 *shape, *mat;
+    const float2* minv;
+    // broadphase
+    float4* aabb;
+    int4* meta;  // cx0, cy0, layer bits, dynamic flag
+    uint32_t *cell_cnt, *cell_off;
+    uint32_t *ekey0, *eval0, *ekey1, *eval1;
+    uint32_t *pcnt, *poff;
+    uint2* pairs_raw;
+    // colouring
+    unsigned long long *mask, *claim0, *claim1;
+    uint32_t *pcol, *jcol;
+    uint32_t *pcol_sorted, *pperm, *jcol_sorted, *jperm;
+    uint2* pairs;  // colour-sorted
+    // joints: upload order (…_in) and colour-sorted
+    const uint2* jbod_in;
+    const float4 *janc_in, *jpar_in;
+    uint2* jbod;
+    float4 *janc, *jpar;
+    // contacts (per colour-sorted pair)
+    float4 *ca, *cb, *cp0, *cp1, *cs, *lam;
+    Counters* cnt;
+    // parameters
+    float gx, gy, inv_cell, aabb_margin, vel_expand, contact_margin;
+    uint32_t n, nj, cap_entries, cap_pairs;
+};
+
+__device__ __forceinline__ f4 ld4(const float4* p, uint32_t i) {
+    float4 v = p[i];
+    f4 r;
+    r.x = v.x;
+    r.y = v.y;
+    r.z = v.z;
+    r.w = v.w;
+    return r;
+}
+__device__ __forceinline__ void st4(float4* p, uint32_t i, f4 v) {
+    p[i] = make_float4(v.x, v.y, v.z, v.w);
+}
+__device__ __forceinline__ f2 ld2(const float2* p, uint32_t i) {
+    float2 v = p[i];
+    f2 r;
+    r.x = v.x;
+    r.y = v.y;
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------
+// A2 broadphase
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_t tid,
+                                                 uint32_t nth) {
+    for (uint32_t i = tid; i < c.n; i += nth) {
+        f4 pose = ld4(c.pose, i), vel = ld4(c.vel, i), shape = ld4(c.shape, i);
+        f2 mi = ld2(c.minv, i);
+        f4 bb = sfp::body_aabb(pose, vel, shape, c.aabb_margin, c.vel_expand, dt);
+        int x0 = sfp::cell_coord(bb.x, c.inv_cell), y0 = sfp::cell_coord(bb.y, c.inv_cell);
+        int x1 = sfp::cell_coord(bb.z, c.inv_cell), y1 = sfp::cell_coord(bb.w, c.inv_cell);
+        st4(c.aabb, i, bb);
+        int dyn = (mi.x > 0.0f || mi.y > 0.0f) ? 1 : 0;
+        c.meta[i] = make_int4(x0, y0, (int)sfp::f2u(c.mat[i].w), dyn);
+        c.cell_cnt[i] = (uint32_t)(x1 - x0 + 1) * (uint32_t)(y1 - y0 + 1);
+    }
+    if (tid == 0) {
+        // per-frame counters
+        c.cnt->n_colours = 0;
+        c.cnt->colour_rounds = 0;
+    }
+}
+
+__device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, uint32_t nth) {
+    for (uint32_t i = tid; i < c.n; i += nth) {
+        f4 bb = ld4(c.aabb, i);
+        int4 m = c.meta[i];
+        int x1 = sfp::cell_coord(bb.z, c.inv_cell), y1 = sfp::cell_coord(bb.w, c.inv_cell);
+        uint32_t o = c.cell_off[i];
+        for (int cy = m.y; cy <= y1; ++cy)
+            for (int cx = m.x; cx <= x1; ++cx) {
+                if (o < c.cap_entries) {
+                    c.ekey0[o] = sfp::cell_key(cx, cy);
+                    c.eval0[o] = i;
+                }
+                ++o;
+            }
+    }
+    if (tid == 0 && c.cnt->n_entries > c.cap_entries) {
+        c.cnt->n_entries = c.cap_entries;
+        c.cnt->overflow |= 1u;
+    }
+}
+
+// pair test shared by the count and the write pass; entries are sorted by cell key
+__device__ __forceinline__ bool pair_test(const Ctx& c, int cx, int cy, uint32_t a, f4 bba, int4 ma,
+                                          uint32_t b) {
+    if (a == b) return false;
+    int4 mb = c.meta[b];
+    if ((ma.w | mb.w) == 0) return false;
+    if (max(ma.x, mb.x) != cx || max(ma.y, mb.y) != cy) return false;
+    if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
+    return sfp::aabb_overlap(bba, ld4(c.aabb, b));
+}
+
+template <bool WRITE>
+__device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
+                                            const uint32_t* eval, uint32_t tid, uint32_t nth) {
+    const uint32_t E = c.cnt->n_entries;
+    for (uint32_t e = tid; e < E; e += nth) {
+        uint32_t key = ekey[e], a = eval[e];
+        int cx = sfp::key_cx(key), cy = sfp::key_cy(key);
+        f4 bba = ld4(c.aabb, a);
+        int4 ma = c.meta[a];
+        uint32_t k = 0;
+        uint32_t o = WRITE ? c.poff[e] : 0u;
+        for (uint32_t f = e + 1; f < E && ekey[f] == key; ++f) {
+            uint32_t b = eval[f];
+            if (pair_test(c, cx, cy, a, bba, ma, b)) {
+                if (WRITE) {
+                    if (o + k < c.cap_pairs)
+                        c.pairs_raw[o + k] = make_uint2(min(a, b), max(a, b));
+                }
+                ++k;
+            }
+        }
+        if (!WRITE) c.pcnt[e] = k;
+    }
+    if (WRITE && tid == 0 && c.cnt->n_pairs > c.cap_pairs) {
+        c.cnt->n_pairs = c.cap_pairs;
+        c.cnt->overflow |= 2u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// A8 colouring: rounds of bid (atomicMin of a unique 64-bit priority on each dynamic body) and
+// take (a constraint holding the claim on all its dynamic bodies takes the lowest free colour)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, uint32_t nth) {
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t i = tid; i < c.n; i += nth) {
+        c.mask[i] = 0ull;
+        c.claim0[i] = SFP_NO_CLAIM;
+        c.claim1[i] = SFP_NO_CLAIM;
+    }
+    for (uint32_t k = tid; k < P; k += nth) c.pcol[k] = UNCOLOURED;
+    for (uint32_t k = tid; k < c.nj; k += nth) {
+        uint2 jb = c.jbod_in[k];
+        bool dyn = (c.meta[jb.x].w | c.meta[jb.y].w) != 0;
+        c.jcol[k] = dyn ? UNCOLOURED : 0u;
+        if (!dyn) atomicMax(&c.cnt->n_colours, 1u);
+    }
+    for (uint32_t k = tid; k < MAX_ROUNDS; k += nth) c.cnt->round_flags[k] = 0u;
+}
+
+__device__ __forceinline__ void colour_bid_one(const Ctx& c, unsigned long long* claim, uint32_t a,
+                                               uint32_t b, unsigned long long key) {
+    if (c.meta[a].w) atomicMin(&claim[a], key);
+    if (c.meta[b].w) atomicMin(&claim[b], key);
+}
+
+__device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, uint32_t tid,
+                                                 uint32_t nth) {
+    unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = tid; k < P; k += nth)
+        if (c.pcol[k] == UNCOLOURED) {
+            uint2 p = c.pairs_raw[k];
+            colour_bid_one(c, claim, p.x, p.y, sfp::pair_priority(p.x, p.y));
+        }
+    for (uint32_t k = tid; k < c.nj; k += nth)
+        if (c.jcol[k] == UNCOLOURED) {
+            uint2 p = c.jbod_in[k];
+            colour_bid_one(c, claim, p.x, p.y, sfp::joint_priority(k));
+        }
+}
+
+// returns the colour taken, or UNCOLOURED
+__device__ __forceinline__ uint32_t colour_take_one(const Ctx& c, const unsigned long long* claim,
+                                                    unsigned long long* next_claim, uint32_t a,
+                                                    uint32_t b, unsigned long long key,
+                                                    uint32_t round) {
+    bool da = c.meta[a].w != 0, db = c.meta[b].w != 0;
+    bool win = (!da || claim[a] == key) && (!db || claim[b] == key);
+    if (!win) {
+        if (da) next_claim[a] = SFP_NO_CLAIM;
+        if (db) next_claim[b] = SFP_NO_CLAIM;
+        c.cnt->round_flags[round] = 1u;
+        return UNCOLOURED;
+    }
+    unsigned long long m = (da ? c.mask[a] : 0ull) | (db ? c.mask[b] : 0ull);
+    int col = sfp::lowest_free(m);
+    if (col >= SFP_MAX_COLOURS) {
+        col = SFP_MAX_COLOURS - 1;
+        atomicOr(&c.cnt->overflow, 4u);
+    }
+    if (da) c.mask[a] |= 1ull << col;
+    if (db) c.mask[b] |= 1ull << col;
+    atomicMax(&c.cnt->n_colours, (uint32_t)col + 1u);
+    return (uint32_t)col;
+}
+
+__device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, uint32_t tid,
+                                                  uint32_t nth) {
+    unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
+    unsigned long long* next_claim = (round & 1u) ? c.claim0 : c.claim1;
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = tid; k < P; k += nth)
+        if (c.pcol[k] == UNCOLOURED) {
+            uint2 p = c.pairs_raw[k];
+            c.pcol[k] = colour_take_one(c, claim, next_claim, p.x, p.y,
+                                        sfp::pair_priority(p.x, p.y), round);
+        }
+    for (uint32_t k = tid; k < c.nj; k += nth)
+        if (c.jcol[k] == UNCOLOURED) {
+            uint2 p = c.jbod_in[k];
+            c.jcol[k] =
+                colour_take_one(c, claim, next_claim, p.x, p.y, sfp::joint_priority(k), round);
+        }
+    if (tid == 0) c.cnt->colour_rounds = round + 1u;
+}
+
+// after the stable sort by colour: gather constraints into colour order, find colour bounds
+__device__ __forceinline__ void colour_bounds(const uint32_t* sorted_col, uint32_t n, uint32_t i,
+                                              uint32_t* off) {
+    uint32_t col = sorted_col[i];
+    int prev = (i == 0) ? -1 : (int)sorted_col[i - 1];
+    for (int cc = prev + 1; cc <= (int)col; ++cc) off[cc] = i;
+    if (i == n - 1)
+        for (int cc = (int)col + 1; cc <= SFP_MAX_COLOURS; ++cc) off[cc] = n;
+}
+
+__device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_t nth) {
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t i = tid; i < P; i += nth) {
+        c.pairs[i] = c.pairs_raw[c.pperm[i]];
+        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off);
+    }
+    if (P == 0 && tid == 0)
+        for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->pair_col_off[cc] = 0;
+    for (uint32_t i = tid; i < c.nj; i += nth) {
+        uint32_t s = c.jperm[i];
+        c.jbod[i] = c.jbod_in[s];
+        c.janc[i] = c.janc_in[s];
+        c.jpar[i] = c.jpar_in[s];
+        colour_bounds(c.jcol_sorted, c.nj, i, c.cnt->joint_col_off);
+    }
+    if (c.nj == 0 && tid == 0)
+        for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->joint_col_off[cc] = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// A3 integrate
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_integrate(const Ctx& c, float h, uint32_t tid, uint32_t nth) {
+    for (uint32_t i = tid; i < c.n; i += nth) {
+        f4 pose = ld4(c.pose, i), vel = ld4(c.vel, i);
+        f2 mi = ld2(c.minv, i);
+        f4 prev;
+        sfp::integrate_body(&pose, &prev, &vel, mi, c.gx, c.gy, h);
+        st4(c.prev, i, prev);
+        st4(c.pose, i, pose);
+        st4(c.vel, i, vel);
+    }
+    if (tid == 0) {
+        c.cnt->n_contacts = 0;
+        c.cnt->n_manifolds = 0;
+        c.cnt->maxpen_bits = 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// A4 narrowphase: one thread per candidate pair (colour-sorted order)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, uint32_t nth) {
+    const uint32_t P = c.cnt->n_pairs;
+    uint32_t npts = 0, nman = 0;
+    float maxpen = 0.0f;
+    for (uint32_t k = tid; k < P; k += nth) {
+        uint2 p = c.pairs[k];
+        sfp::ContactRec r = sfp::narrowphase(ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x),
+                                             ld4(c.mat, p.x), ld4(c.pose, p.y), ld4(c.vel, p.y),
+                                             ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin);
+        st4(c.ca, k, r.a);
+        st4(c.cb, k, r.b);
+        st4(c.cp0, k, r.p0);
+        st4(c.cp1, k, r.p1);
+        st4(c.cs, k, r.s);
+        uint32_t cnt = sfp::f2u(r.b.y);
+        npts += cnt;
+        nman += cnt ? 1u : 0u;
+        if (cnt > 0) maxpen = fmaxf(maxpen, -r.s.x);
+        if (cnt > 1) maxpen = fmaxf(maxpen, -r.s.y);
+    }
+    // warp-aggregated integer statistics (order-independent)
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        npts += __shfl_xor_sync(0xffffffffu, npts, d);
+        nman += __shfl_xor_sync(0xffffffffu, nman, d);
+        maxpen = fmaxf(maxpen, __shfl_xor_sync(0xffffffffu, maxpen, d));
+    }
+    if ((threadIdx.x & 31) == 0 && (npts | nman)) {
+        atomicAdd(&c.cnt->n_contacts, npts);
+        atomicAdd(&c.cnt->n_manifolds, nman);
+        atomicMax(&c.cnt->maxpen_bits, sfp::f2u(maxpen));
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// A5 + A6 position projection of one colour
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ sfp::BodyPos load_pos(const Ctx& c, uint32_t i) {
+    f4 pose = ld4(c.pose, i), prev = ld4(c.prev, i);
+    f2 mi = ld2(c.minv, i);
+    sfp::BodyPos b;
+    b.x = sfp::mk(pose.x, pose.y);
+    b.q = sfp::mk(pose.z, pose.w);
+    b.d = sfp::mk(prev.x, prev.y);
+    b.qp = sfp::mk(prev.z, prev.w);
+    b.im = mi.x;
+    b.ii = mi.y;
+    return b;
+}
+__device__ __forceinline__ void store_pos(const Ctx& c, uint32_t i, const sfp::BodyPos& b) {
+    if (b.im > 0.0f || b.ii > 0.0f) {
+        c.pose[i] = make_float4(b.x.x, b.x.y, b.q.x, b.q.y);
+        c.prev[i] = make_float4(b.d.x, b.d.y, b.qp.x, b.qp.y);
+    }
+}
+
+__device__ __forceinline__ void stage_solve_pos(const Ctx& c, uint32_t colour, float inv_h2,
+                                                uint32_t tid, uint32_t nth) {
+    const uint32_t j0 = c.cnt->joint_col_off[colour], j1 = c.cnt->joint_col_off[colour + 1];
+    const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
+    const uint32_t nj = j1 - j0, total = nj + (p1 - p0);
+    for (uint32_t t = tid; t < total; t += nth) {
+        if (t < nj) {
+            uint32_t k = j0 + t;
+            uint2 jb = c.jbod[k];
+            float4 an = c.janc[k], pr = c.jpar[k];
+            sfp::BodyPos A = load_pos(c, jb.x), B = load_pos(c, jb.y);
+            sfp::solve_joint(&A, &B, sfp::mk(an.x, an.y), sfp::mk(an.z, an.w), pr.x, pr.y,
+                             sfp::f2u(pr.z), inv_h2);
+            store_pos(c, jb.x, A);
+            store_pos(c, jb.y, B);
+        } else {
+            uint32_t k = p0 + (t - nj);
+            f4 cb = ld4(c.cb, k);
+            uint32_t cnt = sfp::f2u(cb.y);
+            f4 lam;
+            lam.x = lam.y = lam.z = lam.w = 0.0f;
+            if (cnt > 0) {
+                uint2 p = c.pairs[k];
+                f4 ca = ld4(c.ca, k), q0 = ld4(c.cp0, k), q1 = ld4(c.cp1, k);
+                sfp::BodyPos A = load_pos(c, p.x), B = load_pos(c, p.y);
+                lam = sfp::solve_contact_manifold(&A, &B, sfp::mk(ca.x, ca.y), cnt,
+                                                  sfp::mk(q0.x, q0.y), sfp::mk(q0.z, q0.w),
+                                                  sfp::mk(q1.x, q1.y), sfp::mk(q1.z, q1.w), ca.z);
+                store_pos(c, p.x, A);
+                store_pos(c, p.y, B);
+            }
+            st4(c.lam, k, lam);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// A7 (i) velocity derivation, (ii) velocity pass of one colour
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void stage_derive(const Ctx& c, float inv_h, uint32_t tid, uint32_t nth) {
+    for (uint32_t i = tid; i < c.n; i += nth) {
+        f4 v = sfp::derive_velocity(ld4(c.pose, i), ld4(c.prev, i), ld4(c.vel, i), ld2(c.minv, i),
+                                    inv_h);
+        st4(c.vel, i, v);
+    }
+}
+
+__device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, float h,
+                                                float rest_threshold, uint32_t tid, uint32_t nth) {
+    const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
+    for (uint32_t k = p0 + tid; k < p1; k += nth) {
+        f4 lam = ld4(c.lam, k);
+        if (!(lam.x > 0.0f || lam.z > 0.0f)) continue;
+        f4 cb = ld4(c.cb, k), ca = ld4(c.ca, k);
+        uint32_t cnt = sfp::f2u(cb.y);
+        uint2 p = c.pairs[k];
+        f4 va = ld4(c.vel, p.x), vb = ld4(c.vel, p.y);
+        f4 pa = ld4(c.pose, p.x), pb = ld4(c.pose, p.y);
+        f2 ma = ld2(c.minv, p.x), mb = ld2(c.minv, p.y);
+        sfp::BodyVel A, B;
+        A.v = sfp::mk(va.x, va.y);
+        A.w = va.z;
+        A.im = ma.x;
+        A.ii = ma.y;
+        B.v = sfp::mk(vb.x, vb.y);
+        B.w = vb.z;
+        B.im = mb.x;
+        B.ii = mb.y;
+        v2 qa = sfp::mk(pa.z, pa.w), qb = sfp::mk(pb.z, pb.w), n = sfp::mk(ca.x, ca.y);
+        f4 q0 = ld4(c.cp0, k), q1 = ld4(c.cp1, k);
+        sfp::solve_manifold_velocity(&A, &B, qa, qb, n, cnt, sfp::mk(q0.x, q0.y),
+                                     sfp::mk(q0.z, q0.w), sfp::mk(q1.x, q1.y), sfp::mk(q1.z, q1.w),
+                                     lam, cb.z, cb.w, ca.z, ca.w, cb.x, h, rest_threshold);
+        if (ma.x > 0.0f || ma.y > 0.0f) c.vel[p.x] = make_float4(A.v.x, A.v.y, A.w, 0.0f);
+        if (mb.x > 0.0f || mb.y > 0.0f) c.vel[p.y] = make_float4(B.v.x, B.v.y, B.w, 0.0f);
+    }
+}
+
+}  // namespace sfpk

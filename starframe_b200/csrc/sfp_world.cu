@@ -1,0 +1,771 @@
+// sfp_world.cu — the C ABI of include/sfp.h for ONE world on one B200 (libsfp_b200.so).
+//
+// Frame = broadphase (radix-sort spatial hash) -> colouring (cooperative kernel, rounds
+// separated by grid.sync) -> stable sort of constraints by colour -> ONE persistent cooperative
+// kernel that runs all substeps (integrate / narrowphase / per-colour position solve / derive
+// velocity / per-colour velocity solve, separated by grid.sync).  The host queues ~35 launches
+// per FRAME and none per substep, never reads anything back while stepping, and takes every
+// data-dependent count (entries, pairs, colours) from device memory.
+//
+// Reference: replaces the reference's CPU `Physics` step (not mounted).
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "sfp.h"
+#include "sfp_device.cuh"
+#include "sfp_host.h"
+#include "sfp_sort.cuh"
+
+namespace cg = cooperative_groups;
+using namespace sfpk;
+
+namespace {
+
+constexpr int TPB = 256;
+
+__device__ __forceinline__ uint32_t gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
+__device__ __forceinline__ uint32_t gnth() { return gridDim.x * blockDim.x; }
+__device__ __forceinline__ uint32_t vload(const uint32_t* p) {
+    return *reinterpret_cast<const volatile uint32_t*>(p);
+}
+
+// ---- one kernel per stage (broadphase always; the rest only with SFP_FLAG_MULTI_KERNEL) ----
+__global__ void __launch_bounds__(TPB) k_aabb_count(Ctx c, float dt) {
+    stage_aabb_count(c, dt, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_emit_entries(Ctx c) { stage_emit_entries(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_pair_count(Ctx c) {
+    stage_pairs<false>(c, c.ekey0, c.eval0, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_pair_write(Ctx c) {
+    stage_pairs<true>(c, c.ekey0, c.eval0, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_colour_init(Ctx c) { stage_colour_init(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_colour_bid(Ctx c, uint32_t round) {
+    stage_colour_bid(c, round, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_colour_take(Ctx c, uint32_t round) {
+    stage_colour_take(c, round, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_gather(Ctx c) { stage_gather(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_integrate(Ctx c, float h) {
+    stage_integrate(c, h, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_narrowphase(Ctx c) { stage_narrowphase(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_solve_pos(Ctx c, uint32_t colour, float inv_h2) {
+    stage_solve_pos(c, colour, inv_h2, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_derive(Ctx c, float inv_h) {
+    stage_derive(c, inv_h, gtid(), gnth());
+}
+__global__ void __launch_bounds__(TPB) k_solve_vel(Ctx c, uint32_t colour, float h, float rt) {
+    stage_solve_vel(c, colour, h, rt, gtid(), gnth());
+}
+
+// ---- persistent cooperative kernels (product path) ----------------------------------------
+__global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = gtid(), nth = gnth();
+    stage_colour_init(c, tid, nth);
+    grid.sync();
+    uint32_t round = 0;
+    for (; round < (uint32_t)MAX_ROUNDS; ++round) {
+        stage_colour_bid(c, round, tid, nth);
+        grid.sync();
+        stage_colour_take(c, round, tid, nth);
+        grid.sync();
+        if (vload(&c.cnt->round_flags[round]) == 0u) break;
+    }
+    if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+}
+
+__global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t substeps,
+                                                       float rest_threshold) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = gtid(), nth = gnth();
+    const uint32_t ncol = vload(&c.cnt->n_colours);
+    const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    for (uint32_t s = 0; s < substeps; ++s) {
+        stage_integrate(c, h, tid, nth);
+        grid.sync();
+        stage_narrowphase(c, tid, nth);
+        grid.sync();
+        for (uint32_t col = 0; col < ncol; ++col) {
+            stage_solve_pos(c, col, inv_h2, tid, nth);
+            grid.sync();
+        }
+        stage_derive(c, inv_h, tid, nth);
+        grid.sync();
+        for (uint32_t col = 0; col < ncol; ++col) {
+            stage_solve_vel(c, col, h, rest_threshold, tid, nth);
+            grid.sync();
+        }
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess) {                                                          \
+            w->err = std::string(#call) + ": " + cudaGetErrorString(e_);                  \
+            w->sticky = SFP_E_CUDA;                                                       \
+            return SFP_E_CUDA;                                                            \
+        }                                                                                 \
+    } while (0)
+
+struct SfpWorld {
+    SfpParams p;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    uint32_t n = 0, nj = 0;
+    uint32_t cap_bodies = 0, cap_joints = 0, cap_entries = 0, cap_pairs = 0;
+    Ctx ctx;
+    std::vector<void*> body_allocs, joint_allocs;
+    uint32_t *d_scan_tiles = nullptr, *d_hist = nullptr;
+    uint32_t hist_blocks = 0;
+    Counters* d_cnt = nullptr;
+    // host mirrors
+    std::vector<sfp::f2> h_minv;
+    std::vector<sfp::f4> h_shape, h_mat;
+    sfp::f4 *pin_pose = nullptr, *pin_vel = nullptr;  // pinned staging, cap_bodies each
+    uint32_t pin_cap = 0;
+    int coop_max_colour = 0, coop_max_substep = 0, n_sm = 0;
+    SfpStats stats;
+    std::string err;
+    int32_t sticky = SFP_OK;
+    bool stepped = false;
+};
+
+namespace {
+
+template <typename T>
+int alloc_dev(SfpWorld* w, T** out, size_t count, std::vector<void*>& bag) {
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    CU(cudaMalloc(&p, bytes));
+    CU(cudaMemsetAsync(p, 0, bytes, w->stream));
+    bag.push_back(p);
+    *out = reinterpret_cast<T*>(p);
+    return SFP_OK;
+}
+
+void free_bag(std::vector<void*>& bag) {
+    for (void* p : bag) cudaFree(p);
+    bag.clear();
+}
+
+#define TRY(x)                      \
+    do {                            \
+        int rc_ = (x);              \
+        if (rc_ != SFP_OK) return rc_; \
+    } while (0)
+
+int ensure_body_capacity(SfpWorld* w, uint32_t n) {
+    if (n <= w->cap_bodies && w->cap_bodies > 0) return SFP_OK;
+    CU(cudaStreamSynchronize(w->stream));
+    free_bag(w->body_allocs);
+    if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
+    if (w->d_hist) cudaFree(w->d_hist);
+    w->d_scan_tiles = w->d_hist = nullptr;
+    uint32_t cb = std::max<uint32_t>(std::max(n, w->p.max_bodies), 1u);
+    uint32_t ce = std::max<uint32_t>(w->p.max_entries, 8u * cb + 8192u);
+    uint32_t cp = std::max<uint32_t>(w->p.max_pairs, 12u * cb + 4096u);
+    Ctx& c = w->ctx;
+    auto& bag = w->body_allocs;
+    TRY(alloc_dev(w, &c.pose, cb, bag));
+    TRY(alloc_dev(w, &c.prev, cb, bag));
+    TRY(alloc_dev(w, &c.vel, cb, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.shape), cb, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.mat), cb, bag));
+    TRY(alloc_dev(w, const_cast<float2**>(&c.minv), cb, bag));
+    TRY(alloc_dev(w, &c.aabb, cb, bag));
+    TRY(alloc_dev(w, &c.meta, cb, bag));
+    TRY(alloc_dev(w, &c.cell_cnt, cb + 1, bag));
+    TRY(alloc_dev(w, &c.cell_off, cb + 1, bag));
+    TRY(alloc_dev(w, &c.mask, cb, bag));
+    TRY(alloc_dev(w, &c.claim0, cb, bag));
+    TRY(alloc_dev(w, &c.claim1, cb, bag));
+    TRY(alloc_dev(w, &c.ekey0, ce, bag));
+    TRY(alloc_dev(w, &c.eval0, ce, bag));
+    TRY(alloc_dev(w, &c.ekey1, ce, bag));
+    TRY(alloc_dev(w, &c.eval1, ce, bag));
+    TRY(alloc_dev(w, &c.pcnt, ce + 1, bag));
+    TRY(alloc_dev(w, &c.poff, ce + 1, bag));
+    TRY(alloc_dev(w, &c.pairs_raw, cp, bag));
+    TRY(alloc_dev(w, &c.pairs, cp, bag));
+    TRY(alloc_dev(w, &c.pcol, cp, bag));
+    TRY(alloc_dev(w, &c.pcol_sorted, cp, bag));
+    TRY(alloc_dev(w, &c.pperm, cp, bag));
+    TRY(alloc_dev(w, &c.ca, cp, bag));
+    TRY(alloc_dev(w, &c.cb, cp, bag));
+    TRY(alloc_dev(w, &c.cp0, cp, bag));
+    TRY(alloc_dev(w, &c.cp1, cp, bag));
+    TRY(alloc_dev(w, &c.cs, cp, bag));
+    TRY(alloc_dev(w, &c.lam, cp, bag));
+    w->cap_bodies = cb;
+    w->cap_entries = ce;
+    w->cap_pairs = cp;
+    c.cap_entries = ce;
+    c.cap_pairs = cp;
+    uint32_t biggest = std::max(std::max(ce, cp), std::max(cb, w->cap_joints)) + 1;
+    w->hist_blocks = radix_blocks(biggest);
+    CU(cudaMalloc(&w->d_scan_tiles, sizeof(uint32_t) * (biggest / SCAN_TILE + 4)));
+    CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * (size_t)w->hist_blocks));
+    if (w->pin_pose) cudaFreeHost(w->pin_pose);
+    if (w->pin_vel) cudaFreeHost(w->pin_vel);
+    w->pin_pose = w->pin_vel = nullptr;
+    CU(cudaMallocHost(&w->pin_pose, sizeof(sfp::f4) * cb));
+    CU(cudaMallocHost(&w->pin_vel, sizeof(sfp::f4) * cb));
+    w->pin_cap = cb;
+    return SFP_OK;
+}
+
+int ensure_joint_capacity(SfpWorld* w, uint32_t nj) {
+    if (nj <= w->cap_joints && w->cap_joints > 0) return SFP_OK;
+    CU(cudaStreamSynchronize(w->stream));
+    free_bag(w->joint_allocs);
+    uint32_t cj = std::max<uint32_t>(std::max(nj, w->p.max_joints), 1u);
+    Ctx& c = w->ctx;
+    auto& bag = w->joint_allocs;
+    TRY(alloc_dev(w, const_cast<uint2**>(&c.jbod_in), cj, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.janc_in), cj, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.jpar_in), cj, bag));
+    TRY(alloc_dev(w, &c.jbod, cj, bag));
+    TRY(alloc_dev(w, &c.janc, cj, bag));
+    TRY(alloc_dev(w, &c.jpar, cj, bag));
+    TRY(alloc_dev(w, &c.jcol, cj, bag));
+    TRY(alloc_dev(w, &c.jcol_sorted, cj, bag));
+    TRY(alloc_dev(w, &c.jperm, cj, bag));
+    w->cap_joints = cj;
+    // the radix histogram must cover the joint sort too
+    if (radix_blocks(cj + 1) > w->hist_blocks) {
+        if (w->d_hist) cudaFree(w->d_hist);
+        w->hist_blocks = radix_blocks(cj + 1);
+        CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * (size_t)w->hist_blocks));
+    }
+    return SFP_OK;
+}
+
+uint32_t blocks_for(const SfpWorld* w, uint64_t items) {
+    uint64_t b = (items + TPB - 1) / TPB;
+    uint64_t cap = (uint64_t)w->n_sm * 8;
+    return (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(b, cap));
+}
+
+int sort_entries(SfpWorld* w) {
+    Ctx& c = w->ctx;
+    const uint32_t* n_ptr = &w->d_cnt->n_entries;
+    // the hist grid must match between hist and scatter: radix_pass derives it from cap
+    for (int pass = 0; pass < 4; ++pass) {
+        const uint32_t* ki = (pass & 1) ? c.ekey1 : c.ekey0;
+        const uint32_t* vi = (pass & 1) ? c.eval1 : c.eval0;
+        uint32_t* ko = (pass & 1) ? c.ekey0 : c.ekey1;
+        uint32_t* vo = (pass & 1) ? c.eval0 : c.eval1;
+        CU(radix_pass(ki, vi, ko, vo, n_ptr, w->cap_entries, pass * 8, w->d_hist, w->stream));
+    }
+    return SFP_OK;
+}
+
+int launch_coop(SfpWorld* w, const void* fn, uint32_t blocks, void** args) {
+    CU(cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(TPB), args, 0, w->stream));
+    return SFP_OK;
+}
+
+int broadphase_and_colour(SfpWorld* w, float dt) {
+    Ctx& c = w->ctx;
+    cudaStream_t st = w->stream;
+    const bool multi = (w->p.flags & SFP_FLAG_MULTI_KERNEL) != 0u;
+    const uint32_t gb = blocks_for(w, w->n);
+    k_aabb_count<<<gb, TPB, 0, st>>>(c, dt);
+    CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
+                      &w->d_cnt->n_entries, st));
+    k_emit_entries<<<gb, TPB, 0, st>>>(c);
+    TRY(sort_entries(w));
+    const uint32_t ge = blocks_for(w, w->cap_entries);
+    k_pair_count<<<ge, TPB, 0, st>>>(c);
+    CU(scan_exclusive(c.pcnt, c.poff, &w->d_cnt->n_entries, w->cap_entries, w->d_scan_tiles,
+                      &w->d_cnt->n_pairs, st));
+    k_pair_write<<<ge, TPB, 0, st>>>(c);
+    CU(cudaGetLastError());
+
+    if (!multi) {
+        uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_colour,
+                                             blocks_for(w, 4ull * w->n + w->nj));
+        void* args[] = {&c};
+        TRY(launch_coop(w, (const void*)k_colour_coop, blocks, args));
+    } else {
+        const uint32_t gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
+        k_colour_init<<<gp, TPB, 0, st>>>(c);
+        for (uint32_t round = 0; round < (uint32_t)MAX_ROUNDS; ++round) {
+            k_colour_bid<<<gp, TPB, 0, st>>>(c, round);
+            k_colour_take<<<gp, TPB, 0, st>>>(c, round);
+            uint32_t flag = 0;
+            CU(cudaMemcpyAsync(&flag, &w->d_cnt->round_flags[round], sizeof(flag),
+                               cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            if (!flag) break;
+        }
+    }
+    CU(radix_pass(c.pcol, nullptr, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs, 0,
+                  w->d_hist, st));
+    if (w->nj)
+        CU(radix_pass(c.jcol, nullptr, c.jcol_sorted, c.jperm, &w->d_cnt->n_joints, w->cap_joints,
+                      0, w->d_hist, st));
+    k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
+    CU(cudaGetLastError());
+    return SFP_OK;
+}
+
+int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
+    Ctx& c = w->ctx;
+    cudaStream_t st = w->stream;
+    const bool multi = (w->p.flags & SFP_FLAG_MULTI_KERNEL) != 0u;
+    const float g = sqrtf(w->p.gravity_x * w->p.gravity_x + w->p.gravity_y * w->p.gravity_y);
+    float rest_threshold = 2.0f * g * h;
+    if (!multi) {
+        uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_substep,
+                                             blocks_for(w, 4ull * w->n + w->nj));
+        void* args[] = {&c, &h, &substeps, &rest_threshold};
+        return launch_coop(w, (const void*)k_substeps_coop, blocks, args);
+    }
+    uint32_t ncol = 0;
+    CU(cudaMemcpyAsync(&ncol, &w->d_cnt->n_colours, sizeof(ncol), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    const uint32_t gb = blocks_for(w, w->n), gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
+    for (uint32_t s = 0; s < substeps; ++s) {
+        k_integrate<<<gb, TPB, 0, st>>>(c, h);
+        k_narrowphase<<<gp, TPB, 0, st>>>(c);
+        for (uint32_t col = 0; col < ncol; ++col) k_solve_pos<<<gp, TPB, 0, st>>>(c, col, inv_h2);
+        k_derive<<<gb, TPB, 0, st>>>(c, inv_h);
+        for (uint32_t col = 0; col < ncol; ++col)
+            k_solve_vel<<<gp, TPB, 0, st>>>(c, col, h, rest_threshold);
+    }
+    CU(cudaGetLastError());
+    return SFP_OK;
+}
+
+int frame(SfpWorld* w, float dt, uint32_t substeps) {
+    const float h = dt / (float)substeps;
+    if (w->n == 0) return SFP_OK;
+    if (w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP) {
+        for (uint32_t s = 0; s < substeps; ++s) {
+            TRY(broadphase_and_colour(w, h));
+            TRY(run_substeps(w, h, 1));
+        }
+        return SFP_OK;
+    }
+    TRY(broadphase_and_colour(w, dt));
+    return run_substeps(w, h, substeps);
+}
+
+int read_counters(SfpWorld* w, Counters* out) {
+    CU(cudaMemcpyAsync(out, w->d_cnt, sizeof(Counters), cudaMemcpyDeviceToHost, w->stream));
+    CU(cudaStreamSynchronize(w->stream));
+    return SFP_OK;
+}
+
+int check_overflow(SfpWorld* w, const Counters& k) {
+    if (k.overflow) {
+        w->stats.overflow |= k.overflow;
+        char buf[160];
+        snprintf(buf, sizeof(buf),
+                 "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=colours>64, "
+                 "8=colour rounds)",
+                 k.overflow, w->cap_entries, w->cap_pairs);
+        w->err = buf;
+        return SFP_E_CAPACITY;
+    }
+    return SFP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t sfp_default_params(SfpParams* out) {
+    if (!out) return SFP_E_INVALID;
+    sfp::default_params(out);
+    return SFP_OK;
+}
+
+int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
+    if (!out) return SFP_E_INVALID;
+    *out = nullptr;
+    SfpParams p;
+    if (params) p = *params;
+    else sfp::default_params(&p);
+    if (!sfp::params_valid(p)) return SFP_E_INVALID;
+    if (p.solver_order != SFP_ORDER_COLOUR) return SFP_E_INVALID;  // the device path is coloured GS
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        fprintf(stderr, "libsfp_b200: no CUDA device — this library has no CPU fallback\n");
+        return SFP_E_CUDA;
+    }
+    if (p.device < 0 || p.device >= ndev) return SFP_E_INVALID;
+    SfpWorld* w = new (std::nothrow) SfpWorld();
+    if (!w) return SFP_E_NOMEM;
+    w->p = p;
+    w->device = p.device;
+    std::memset(&w->ctx, 0, sizeof(w->ctx));
+    std::memset(&w->stats, 0, sizeof(w->stats));
+    auto fail = [&](const char* what, cudaError_t e) {
+        fprintf(stderr, "libsfp_b200: %s: %s\n", what, cudaGetErrorString(e));
+        delete w;
+        return (int32_t)SFP_E_CUDA;
+    };
+    cudaError_t e;
+    if ((e = cudaSetDevice(w->device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, w->device)) != cudaSuccess)
+        return fail("cudaGetDeviceProperties", e);
+    if (!prop.cooperativeLaunch) return fail("cooperative launch unsupported", cudaErrorNotSupported);
+    w->n_sm = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&w->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&w->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMalloc(&w->d_cnt, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMemset(w->d_cnt, 0, sizeof(Counters))) != cudaSuccess) return fail("cudaMemset", e);
+    w->ctx.cnt = w->d_cnt;
+    int per_sm = 0;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_colour_coop, TPB, 0)) !=
+        cudaSuccess)
+        return fail("occupancy(colour)", e);
+    w->coop_max_colour = std::max(1, per_sm) * w->n_sm;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop, TPB, 0)) !=
+        cudaSuccess)
+        return fail("occupancy(substeps)", e);
+    w->coop_max_substep = std::max(1, per_sm) * w->n_sm;
+    w->ctx.gx = p.gravity_x;
+    w->ctx.gy = p.gravity_y;
+    w->ctx.inv_cell = 1.0f / p.cell_size;
+    w->ctx.aabb_margin = p.aabb_margin;
+    w->ctx.vel_expand = p.vel_expand;
+    w->ctx.contact_margin = p.contact_margin;
+    *out = w;
+    return SFP_OK;
+}
+
+int32_t sfp_destroy(SfpWorld* w) {
+    if (!w) return SFP_OK;
+    cudaSetDevice(w->device);
+    if (w->stream) cudaStreamSynchronize(w->stream);
+    free_bag(w->body_allocs);
+    free_bag(w->joint_allocs);
+    if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
+    if (w->d_hist) cudaFree(w->d_hist);
+    if (w->d_cnt) cudaFree(w->d_cnt);
+    if (w->pin_pose) cudaFreeHost(w->pin_pose);
+    if (w->pin_vel) cudaFreeHost(w->pin_vel);
+    if (w->ev0) cudaEventDestroy(w->ev0);
+    if (w->ev1) cudaEventDestroy(w->ev1);
+    if (w->stream) cudaStreamDestroy(w->stream);
+    delete w;
+    return SFP_OK;
+}
+
+int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
+    if (!w || (n && !bodies)) return SFP_E_INVALID;
+    if (n > SFP_MAX_BODIES || (w->p.max_bodies && n > w->p.max_bodies)) {
+        w->err = "too many bodies";
+        return SFP_E_CAPACITY;
+    }
+    for (uint32_t i = 0; i < n; ++i)
+        if (!sfp::desc_valid(bodies[i])) {
+            w->err = "invalid body desc at index " + std::to_string(i);
+            return SFP_E_INVALID;
+        }
+    if (w->nj && n < w->n) {
+        w->err = "shrinking the body set while joints exist: clear the joints first";
+        return SFP_E_INVALID;
+    }
+    CU(cudaSetDevice(w->device));
+    TRY(ensure_body_capacity(w, n));
+    std::vector<sfp::f4> pose(n), vel(n);
+    w->h_minv.resize(n);
+    w->h_shape.resize(n);
+    w->h_mat.resize(n);
+    uint32_t ndyn = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &w->h_minv[i], &w->h_shape[i],
+                            &w->h_mat[i]);
+        ndyn += (w->h_minv[i].x > 0.0f || w->h_minv[i].y > 0.0f) ? 1u : 0u;
+    }
+    Ctx& c = w->ctx;
+    cudaStream_t st = w->stream;
+    CU(cudaStreamSynchronize(st));
+    if (n) {
+        CU(cudaMemcpyAsync(c.pose, pose.data(), sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(c.prev, pose.data(), sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(c.vel, vel.data(), sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(const_cast<float4*>(c.shape), w->h_shape.data(), sizeof(sfp::f4) * n,
+                           cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(const_cast<float4*>(c.mat), w->h_mat.data(), sizeof(sfp::f4) * n,
+                           cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(const_cast<float2*>(c.minv), w->h_minv.data(), sizeof(sfp::f2) * n,
+                           cudaMemcpyHostToDevice, st));
+    }
+    w->n = n;
+    c.n = n;
+    Counters zero;
+    std::memset(&zero, 0, sizeof(zero));
+    zero.n_bodies = n;
+    zero.n_joints = w->nj;
+    CU(cudaMemcpyAsync(w->d_cnt, &zero, sizeof(zero), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));  // the host vectors above die at return
+    w->stats.n_bodies = n;
+    w->stats.n_dynamic = ndyn;
+    w->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
+    if (!w || (nj && !joints)) return SFP_E_INVALID;
+    if (w->p.max_joints && nj > w->p.max_joints) return SFP_E_CAPACITY;
+    for (uint32_t i = 0; i < nj; ++i)
+        if (!sfp::joint_valid(joints[i], w->n)) {
+            w->err = "invalid joint desc at index " + std::to_string(i);
+            return SFP_E_INVALID;
+        }
+    CU(cudaSetDevice(w->device));
+    TRY(ensure_joint_capacity(w, nj));
+    std::vector<uint2> jb(nj);
+    std::vector<float4> ja(nj), jp(nj);
+    for (uint32_t i = 0; i < nj; ++i) {
+        jb[i] = make_uint2(joints[i].body_a, joints[i].body_b);
+        ja[i] = make_float4(joints[i].ax, joints[i].ay, joints[i].bx, joints[i].by);
+        jp[i] = make_float4(joints[i].rest, joints[i].compliance, sfp::u2f(joints[i].kind), 0.0f);
+    }
+    Ctx& c = w->ctx;
+    cudaStream_t st = w->stream;
+    CU(cudaStreamSynchronize(st));
+    if (nj) {
+        CU(cudaMemcpyAsync(const_cast<uint2*>(c.jbod_in), jb.data(), sizeof(uint2) * nj,
+                           cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(const_cast<float4*>(c.janc_in), ja.data(), sizeof(float4) * nj,
+                           cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(const_cast<float4*>(c.jpar_in), jp.data(), sizeof(float4) * nj,
+                           cudaMemcpyHostToDevice, st));
+    }
+    w->nj = nj;
+    c.nj = nj;
+    CU(cudaMemcpyAsync(&w->d_cnt->n_joints, &nj, sizeof(nj), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));
+    w->stats.n_joints = nj;
+    return SFP_OK;
+}
+
+int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps) {
+    if (!w || !(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    CU(cudaEventRecord(w->ev0, w->stream));
+    int rc = frame(w, dt, substeps);
+    if (rc != SFP_OK) return rc;
+    CU(cudaEventRecord(w->ev1, w->stream));
+    w->timed = true;
+    w->stats.frames += 1;
+    w->stats.body_substeps += (uint64_t)w->n * substeps;
+    w->stepped = true;
+    return SFP_OK;
+}
+
+int32_t sfp_sync(SfpWorld* w) {
+    if (!w) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    Counters k;
+    TRY(read_counters(w, &k));
+    return check_overflow(w, k);
+}
+
+int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
+    if (!w || (n && !out) || n > w->n) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    if (n) {
+        CU(cudaMemcpyAsync(w->pin_pose, w->ctx.pose, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost,
+                           w->stream));
+        CU(cudaMemcpyAsync(w->pin_vel, w->ctx.vel, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost,
+                           w->stream));
+    }
+    Counters k;
+    TRY(read_counters(w, &k));
+    for (uint32_t i = 0; i < n; ++i) out[i] = sfp::state_from_records(w->pin_pose[i], w->pin_vel[i]);
+    return check_overflow(w, k);
+}
+
+int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, uint32_t n, float dt,
+                      uint32_t substeps) {
+    if (!w || !in || !out || n != w->n || n == 0) return SFP_E_INVALID;
+    if (!(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    CU(cudaStreamSynchronize(w->stream));  // the staging buffers are reused
+    for (uint32_t i = 0; i < n; ++i)
+        sfp::records_from_state(in[i], w->h_minv[i], &w->pin_pose[i], &w->pin_vel[i]);
+    CU(cudaMemcpyAsync(w->ctx.pose, w->pin_pose, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice,
+                       w->stream));
+    CU(cudaMemcpyAsync(w->ctx.vel, w->pin_vel, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice,
+                       w->stream));
+    TRY(sfp_step(w, dt, substeps));
+    return sfp_download_bodies(w, out, n);
+}
+
+namespace {
+struct HostPairs {
+    std::vector<uint2> pairs;       // colour-sorted device order
+    std::vector<uint32_t> colour;   // per pair
+    std::vector<uint32_t> order;    // permutation that sorts by (a,b)
+    Counters k;
+};
+int fetch_pairs(SfpWorld* w, HostPairs* hp) {
+    TRY(read_counters(w, &hp->k));
+    TRY(check_overflow(w, hp->k));
+    uint32_t P = w->stepped ? hp->k.n_pairs : 0u;
+    hp->pairs.resize(P);
+    if (P) {
+        CU(cudaMemcpyAsync(hp->pairs.data(), w->ctx.pairs, sizeof(uint2) * P, cudaMemcpyDeviceToHost,
+                           w->stream));
+        CU(cudaStreamSynchronize(w->stream));
+    }
+    hp->colour.resize(P);
+    for (uint32_t col = 0; col < SFP_MAX_COLOURS; ++col)
+        for (uint32_t i = hp->k.pair_col_off[col]; i < hp->k.pair_col_off[col + 1] && i < P; ++i)
+            hp->colour[i] = col;
+    hp->order.resize(P);
+    for (uint32_t i = 0; i < P; ++i) hp->order[i] = i;
+    std::sort(hp->order.begin(), hp->order.end(), [&](uint32_t x, uint32_t y) {
+        const uint2 &a = hp->pairs[x], &b = hp->pairs[y];
+        return a.x != b.x ? a.x < b.x : a.y < b.y;
+    });
+    return SFP_OK;
+}
+}  // namespace
+
+int32_t sfp_get_pairs(SfpWorld* w, SfpPair* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    HostPairs hp;
+    TRY(fetch_pairs(w, &hp));
+    *n_out = (uint32_t)hp.pairs.size();
+    for (uint32_t i = 0; i < cap && i < hp.pairs.size(); ++i) {
+        out[i].a = hp.pairs[hp.order[i]].x;
+        out[i].b = hp.pairs[hp.order[i]].y;
+    }
+    return SFP_OK;
+}
+
+int32_t sfp_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap, uint32_t* joint_colours,
+                        uint32_t jcap) {
+    if (!w) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    HostPairs hp;
+    TRY(fetch_pairs(w, &hp));
+    if (pair_colours)
+        for (uint32_t i = 0; i < cap && i < hp.pairs.size(); ++i)
+            pair_colours[i] = hp.colour[hp.order[i]];
+    if (joint_colours && w->nj && w->stepped) {
+        std::vector<uint32_t> jc(w->nj);
+        CU(cudaMemcpy(jc.data(), w->ctx.jcol, sizeof(uint32_t) * w->nj, cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < jcap && i < w->nj; ++i) joint_colours[i] = jc[i];
+    }
+    return SFP_OK;
+}
+
+int32_t sfp_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    HostPairs hp;
+    TRY(fetch_pairs(w, &hp));
+    const uint32_t P = (uint32_t)hp.pairs.size();
+    std::vector<sfp::f4> ca(P), cb(P), cp0(P), cp1(P), cs(P), lam(P), pose(w->n);
+    if (P) {
+        const Ctx& c = w->ctx;
+        const float4* src[6] = {c.ca, c.cb, c.cp0, c.cp1, c.cs, c.lam};
+        sfp::f4* dst[6] = {ca.data(), cb.data(), cp0.data(), cp1.data(), cs.data(), lam.data()};
+        for (int k = 0; k < 6; ++k)
+            CU(cudaMemcpyAsync(dst[k], src[k], sizeof(sfp::f4) * P, cudaMemcpyDeviceToHost,
+                               w->stream));
+        CU(cudaMemcpyAsync(pose.data(), c.pose, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost,
+                           w->stream));
+        CU(cudaStreamSynchronize(w->stream));
+    }
+    uint32_t cnt = 0;
+    for (uint32_t i = 0; i < P; ++i) {
+        uint32_t k = hp.order[i];
+        if (sfp::f2u(cb[k].y) == 0u) continue;
+        if (cnt < cap) {
+            sfp::ContactRec r;
+            r.a = ca[k];
+            r.b = cb[k];
+            r.p0 = cp0[k];
+            r.p1 = cp1[k];
+            r.s = cs[k];
+            uint32_t a = hp.pairs[k].x, b = hp.pairs[k].y;
+            out[cnt] = sfp::contact_from_records(a, b, r, lam[k], pose[a], pose[b]);
+        }
+        ++cnt;
+    }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
+int32_t sfp_get_stats(SfpWorld* w, SfpStats* out) {
+    if (!w || !out) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    CU(cudaSetDevice(w->device));
+    Counters k;
+    TRY(read_counters(w, &k));
+    w->stats.n_entries = k.n_entries;
+    w->stats.n_pairs = w->stepped ? k.n_pairs : 0u;
+    w->stats.n_contacts = k.n_contacts;
+    w->stats.n_manifolds = k.n_manifolds;
+    w->stats.n_colours = k.n_colours;
+    w->stats.colour_rounds = k.colour_rounds;
+    w->stats.overflow |= k.overflow;
+    w->stats.max_penetration = sfp::u2f(k.maxpen_bits);
+    std::vector<sfp::f4> pose(w->n), vel(w->n);
+    if (w->n) {
+        CU(cudaMemcpy(pose.data(), w->ctx.pose, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(vel.data(), w->ctx.vel, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost));
+    }
+    sfp::energies(pose, vel, w->h_minv, w->p.gravity_x, w->p.gravity_y, &w->stats.kinetic_energy,
+                  &w->stats.potential_energy);
+    *out = w->stats;
+    return SFP_OK;
+}
+
+const char* sfp_last_error(SfpWorld* w) { return w ? w->err.c_str() : "null world"; }
+
+int32_t sfp_last_step_ms(SfpWorld* w, float* ms) {
+    if (!w || !ms) return SFP_E_INVALID;
+    *ms = 0.0f;
+    if (!w->timed) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    CU(cudaEventSynchronize(w->ev1));
+    CU(cudaEventElapsedTime(ms, w->ev0, w->ev1));
+    return SFP_OK;
+}
+
+const char* sfp_backend(void) { return "cuda-sm_100a"; }
+
+}  // extern "C"

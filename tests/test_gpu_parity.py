@@ -1,0 +1,157 @@
+"""GPU (libsfp_b200.so, through the C ABI) vs the CPU oracle on identical input state.
+
+Bars (BASELINE.json north_star): sorted candidate-pair set and contact counts BIT-EXACT;
+positions / velocities within a stated tolerance.  The oracle in SFP_ORDER_COLOUR performs the
+same Gauss-Seidel sweep in colour order with the same arithmetic (include/sfp_math.h, FMA
+contraction off on both sides), so the tolerance used here is 0: bit-exact state.  The looser
+1e-4 relative bar that accounts for Gauss-Seidel ORDER (reference order vs colour order) is
+measured oracle-vs-oracle in test_oracle_props.py.
+"""
+import numpy as np
+import pytest
+
+import starframe_b200 as sf
+from starframe_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+FIELDS = ("x", "y", "c", "s", "vx", "vy", "omega")
+
+
+def make_worlds(gpu_api, ref_api, bodies, joints, **params):
+    g = sf.World(gpu_api, **params)
+    r = sf.World(ref_api, **params)
+    for w in (g, r):
+        w.upload_bodies(bodies)
+        w.set_joints(joints)
+    return g, r
+
+
+def assert_same_state(g, r, exact=True, tol=0.0):
+    a, b = g.download_bodies(), r.download_bodies()
+    for f in FIELDS:
+        if exact:
+            bad = np.nonzero(a[f].view(np.uint32) != b[f].view(np.uint32))[0]
+            assert bad.size == 0, (f, bad[:8], a[f][bad[:8]], b[f][bad[:8]])
+        else:
+            err = np.max(np.abs(a[f] - b[f]) / (1.0 + np.abs(b[f])))
+            assert err <= tol, (f, err)
+
+
+def assert_same_discrete(g, r):
+    pg, pr = g.get_pairs(), r.get_pairs()
+    assert pg.shape == pr.shape, (pg.shape, pr.shape)
+    assert np.array_equal(pg, pr)
+    sg, sr = g.stats(), r.stats()
+    for k in ("n_entries", "n_pairs", "n_contacts", "n_manifolds", "n_colours", "colour_rounds"):
+        assert sg[k] == sr[k], (k, sg[k], sr[k])
+    assert np.float32(sg["max_penetration"]) == np.float32(sr["max_penetration"])
+    _, cg_, jg = g.get_colours()
+    _, cr_, jr = r.get_colours()
+    assert np.array_equal(cg_, cr_)
+    assert np.array_equal(jg, jr)
+
+
+def run_and_compare(g, r, frames, dt=1 / 60, substeps=8, every=1):
+    for f in range(frames):
+        g.step(dt, substeps)
+        r.step(dt, substeps)
+        if (f + 1) % every == 0 or f == frames - 1:
+            assert_same_discrete(g, r)
+            assert_same_state(g, r)
+
+
+def test_single_substep_stack(gpu_api, ref_api):
+    b, j = scenes.stack100()
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    g.step(1 / 480, 1)
+    r.step(1 / 480, 1)
+    assert_same_discrete(g, r)
+    assert_same_state(g, r)
+
+
+def test_stack100_rollout(gpu_api, ref_api):
+    b, j = scenes.stack100()
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    run_and_compare(g, r, 120, every=10)
+    cg_, cr_ = g.get_contacts(), r.get_contacts()
+    assert cg_.shape == cr_.shape
+    assert cg_.tobytes() == cr_.tobytes()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_soup(gpu_api, ref_api, seed):
+    b, j = scenes.random_soup(600, seed)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    run_and_compare(g, r, 20, every=5)
+
+
+def test_multi_kernel_mode_matches(gpu_api, ref_api):
+    b, j = scenes.random_soup(400, 11)
+    g, r = make_worlds(gpu_api, ref_api, b, j, flags=sf._ffi.FLAG_MULTI_KERNEL)
+    r2 = sf.World(ref_api)
+    run_and_compare(g, r, 5)
+
+
+def test_circles_container_small(gpu_api, ref_api):
+    b, j = scenes.circles_container(2000)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    run_and_compare(g, r, 60, every=20)
+
+
+def test_mixed_pile_small(gpu_api, ref_api):
+    b, j = scenes.mixed_pile(3000)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    run_and_compare(g, r, 60, every=20)
+
+
+def test_ropes_small(gpu_api, ref_api):
+    b, j = scenes.ropes(n_ropes=40, links=32, n_free=300)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    run_and_compare(g, r, 40, every=10)
+
+
+def test_step_host_roundtrip(gpu_api, ref_api):
+    b, j = scenes.mixed_pile(1500)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    sg, sr = g.download_bodies(), r.download_bodies()
+    for _ in range(5):
+        sg = g.step_host(sg)
+        sr = r.step_host(sr)
+    for f in FIELDS:
+        assert np.array_equal(sg[f].view(np.uint32), sr[f].view(np.uint32)), f
+
+
+def test_empty_and_tiny_worlds(gpu_api, ref_api):
+    for n in (0, 1, 2):
+        b, j = scenes.random_soup(max(n, 1), 5)
+        b = b[:n]
+        g, r = make_worlds(gpu_api, ref_api, b, j)
+        g.step()
+        r.step()
+        g.sync()
+        assert g.stats()["n_pairs"] == r.stats()["n_pairs"]
+        if n:
+            assert_same_state(g, r)
+
+
+def test_capacity_overflow_reported(gpu_api):
+    b, j = scenes.random_soup(500, 9, extent=1.0)
+    g = sf.World(gpu_api, max_pairs=16)
+    g.upload_bodies(b)
+    g.step()
+    with pytest.raises(sf.SfpError) as e:
+        g.sync()
+    assert e.value.code == sf._ffi.SFP_E_CAPACITY
+
+
+def test_determinism(gpu_api):
+    b, j = scenes.mixed_pile(2000)
+    outs = []
+    for _ in range(2):
+        g = sf.World(gpu_api)
+        g.upload_bodies(b)
+        for _ in range(30):
+            g.step()
+        outs.append(g.download_bodies().tobytes())
+    assert outs[0] == outs[1]
