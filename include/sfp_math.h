@@ -440,13 +440,44 @@ SFP_HD Manifold collide_polys(const Poly<NA>& A, const Poly<NB>& B, float margin
     float upper2 = dot(v21 - v11, tangent);
     float lower2 = dot(v22 - v11, tangent);
     float span = upper2 - lower2;
+    if (fmaxf(lower2, upper2) < lower1 || fminf(lower2, upper2) > upper1) {
+        /* the incident edge lies entirely beside the reference face: nothing to clip (clipping
+         * would extrapolate along the incident edge and invent a huge depth).  The contact is
+         * between the closest points of the two edges. */
+        float f1, f2;
+        segment_fractions(v11, v12, v21, v22, &f1, &f2);
+        v2 p1 = v11 + f1 * (v12 - v11);
+        v2 p2 = v21 + f2 * (v22 - v21);
+        v2 d = p2 - p1;
+        float dist = len(d);
+        v2 n = n1;
+        if (dist > SFP_EPS) n = (1.0f / dist) * d;
+        if (dot(n, n1) <= 0.0f) {
+            n = n1;
+            dist = dot(d, n1);
+        }
+        if (dist - rsum >= margin) return m;
+        v2 s1 = p1 + r1 * n, s2 = p2 - r2 * n;
+        m.count = 1;
+        m.sep[0] = dist - rsum;
+        if (flip) {
+            m.n = neg(n);
+            m.pa[0] = s2;
+            m.pb[0] = s1;
+        } else {
+            m.n = n;
+            m.pa[0] = s1;
+            m.pb[0] = s2;
+        }
+        return m;
+    }
     v2 vlo = v22, vup = v21;
     if (lower2 < lower1 && span > SFP_EPS) {
-        float t = (lower1 - lower2) / span;
+        float t = fminf((lower1 - lower2) / span, 1.0f);
         vlo = v22 + t * (v21 - v22);
     }
     if (upper2 > upper1 && span > SFP_EPS) {
-        float t = (upper1 - lower2) / span;
+        float t = fmaxf((upper1 - lower2) / span, 0.0f);
         vup = v22 + t * (v21 - v22);
     }
     float seplo = dot(vlo - v11, n1);
