@@ -1,0 +1,477 @@
+#!/usr/bin/env python
+"""bench.py — body-substeps/s of the physics substep loop on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one 60 Hz frame = 8 substeps over the whole scene.
+  N = 1   workload pile100k  (BASELINE.json configs[2], the config north_star's target is quoted
+          on): 100 000 mixed capsule / rounded-rect / circle bodies with friction + restitution.
+          The pile is first stepped `--settle` frames (default 240, SURVEY.md §8d: timing window
+          is the settled pile, contacts dominant); those frames are not timed.
+  N > 1   workload worlds512 (configs[4]): 1024 independent 512-body worlds PER GPU (8192 at
+          N = 8), world ranges partitioned over ranks, no data-path collective ("weak").
+Prints ONE JSON line on rank 0.  value = units all ranks processed / max-over-ranks device time.
+
+--impl reference: the reference's own CPU step cannot be built or run (tree not mounted, no Rust
+toolchain), so this arm times the CPU oracle (oracle/libsfp_ref.so, sequential
+Gauss-Seidel in reference order, "kind": "port") on the same config, on the box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DT, SUBSTEPS = 1.0 / 60.0, 8
+WORLDS_PER_GPU, BODIES_PER_WORLD = 1024, 512
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks + throttle reasons during the timed region"""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                     "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def b_alg(n, pairs, contacts, joints, substeps=SUBSTEPS, whole_step=True):
+    """algorithmic bytes per body-substep (SURVEY.md §8d / BASELINE.md §3)"""
+    p, c, j = pairs / n, contacts / n, joints / n
+    b = 136.0 + 72.0 * p + 344.0 * c + 116.0 * j
+    if whole_step:
+        b += (84.0 + 24.0 * p) / substeps
+    return b
+
+
+def make_scene(workload: str):
+    from starframe_b200 import scenes
+
+    if workload == "pile100k":
+        return scenes.mixed_pile(100_000)
+    if workload == "circles10k":
+        return scenes.circles_container(10_000)
+    if workload == "ropes2k":
+        return scenes.ropes()
+    if workload == "stack100":
+        return scenes.stack100()
+    if workload.startswith("pile"):
+        return scenes.mixed_pile(int(workload[4:]))
+    raise SystemExit(f"unknown workload {workload}")
+
+
+# ------------------------------------------------------------------------------------------
+# single scene on one GPU
+# ------------------------------------------------------------------------------------------
+def run_single(args, rank, world_size):
+    import torch
+
+    import starframe_b200 as sf
+
+    bodies, joints = make_scene(args.workload)
+    n = len(bodies)
+    api = sf.product_api()
+    w = sf.World(api, device=torch.cuda.current_device())
+    w.upload_bodies(bodies)
+    w.set_joints(joints)
+    for _ in range(args.settle):
+        w.step(DT, SUBSTEPS)
+    w.sync()
+    settled = w.download_bodies()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def one_frame():
+        flush.fill_(1)  # L2 flush between frames (outside the timed window)
+        torch.cuda.synchronize()
+        w.step(DT, SUBSTEPS)
+        w.sync()
+        return w.last_step_breakdown_ms()
+
+    for _ in range(args.warmup):
+        one_frame()
+    barrier(world_size)
+    torch.cuda.synchronize()
+    t_dev = t_sub = t_bp = t_col = 0.0
+    with ClockSampler(torch.cuda.current_device()) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            br = one_frame()
+            t_dev += br["step"]
+            t_sub += br["substeps"]
+            t_bp += br["broadphase"]
+            t_col += br["colour"]
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+    barrier(world_size)
+    st = w.stats()
+
+    # end to end through the public call with host buffers (H2D + step + D2H inside the window)
+    state = w.download_bodies()
+    e2e_steps = max(3, min(args.steps, 30))
+    state = w.step_host(state, DT, SUBSTEPS)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        state = w.step_host(state, DT, SUBSTEPS)
+    e2e_s = time.perf_counter() - t0
+
+    t_dev_max = allreduce_max(t_dev, world_size)
+    units = float(n) * SUBSTEPS * args.steps * world_size
+    value = units / (t_dev_max * 1e-3)
+    peak, peak_src = peaks()
+    bytes_sub = b_alg(n, st["n_pairs"], st["n_contacts"], st["n_joints"], whole_step=False) * n * SUBSTEPS
+    ach = bytes_sub / (t_sub / args.steps * 1e-3) / 1e9
+    bytes_step = b_alg(n, st["n_pairs"], st["n_contacts"], st["n_joints"]) * n * SUBSTEPS
+    out = {
+        "metric": "body-substeps/sec", "value": value, "unit": "body-substeps/s",
+        "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t_dev_max / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {
+            "workload": args.workload if world_size == 1 else f"{world_size} replicas of {args.workload}",
+            "bodies": n, "dt": "1/60", "substeps": SUBSTEPS, "settle_frames": args.settle,
+            "pairs_per_body": st["n_pairs"] / n, "contacts_per_body": st["n_contacts"] / n,
+            "joints_per_body": st["n_joints"] / n, "colours": st["n_colours"],
+            "colour_rounds": st["colour_rounds"],
+            "l2": "256 MiB device fill between frames, outside the per-frame CUDA-event window; "
+                  "the 100k-body working set (~30 MB) is L2-resident within a frame by design",
+            "timing": "sum of per-frame CUDA-event times on the library's stream, max over ranks",
+        },
+        "wall_ms_per_step_incl_flush": wall / args.steps * 1e3,
+        "breakdown_ms": {"broadphase": t_bp / args.steps, "colouring": t_col / args.steps,
+                         "substep_kernel": t_sub / args.steps},
+        "roofline": {
+            "bound": "hbm", "kernel": "k_substeps_coop (all 8 substeps of a frame, one launch)",
+            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "peak_source": peak_src, "traffic": None,
+            "algorithmic_bytes_per_launch": bytes_sub,
+            "note": "algorithmic bytes = (136 + 72 p + 344 c + 116 j) * N * S, SURVEY.md §8d; "
+                    "the kernel is grid-sync latency bound, not bandwidth bound (DESIGN.md)",
+        },
+        "roofline_whole_step": {"achieved": bytes_step / (t_dev / args.steps * 1e-3) / 1e9,
+                                "peak": peak, "unit": "GB/s",
+                                "frac": bytes_step / (t_dev / args.steps * 1e-3) / 1e9 / peak},
+        "e2e": {"value": float(n) * SUBSTEPS * e2e_steps / e2e_s, "unit": "body-substeps/s",
+                "h2d_bytes_per_step": 32 * n, "d2h_bytes_per_step": 32 * n,
+                "call": "sfp_step_host (host SfpBodyState in/out, pinned staging inside)",
+                "steps": e2e_steps},
+        "gpu_launches": int(st["launches"]) * args.steps,
+        "launches_per_step": int(st["launches"]),
+        "clocks": clk.summary(),
+        "stats": {k: st[k] for k in ("n_pairs", "n_contacts", "n_manifolds", "max_penetration",
+                                     "kinetic_energy")},
+    }
+    if rank == 0 and not args.no_cpu_baseline and world_size == 1:
+        out["cpu_baseline"] = cpu_baseline_single(bodies, joints, settled, args.cpu_frames)
+    return out
+
+
+def cpu_baseline_single(bodies, joints, settled_state, frames):
+    """the oracle in reference order (sequential Gauss-Seidel, 1 core) on the same settled state"""
+    import starframe_b200 as sf
+    from oracle import loader
+    from starframe_b200 import _ffi
+
+    ref = sf.World(loader.api(), solver_order=_ffi.ORDER_REFERENCE)
+    ref.upload_bodies(bodies)
+    ref.set_joints(joints)
+    state = settled_state
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(frames):
+        state = ref.step_host(state, DT, SUBSTEPS)
+        done += 1
+        if time.perf_counter() - t0 > 30.0:
+            break
+    s = time.perf_counter() - t0
+    return {"value": len(bodies) * SUBSTEPS * done / s, "unit": "body-substeps/s", "cores": 1,
+            "kind": "port",
+            "sample": f"{done} frames x {SUBSTEPS} substeps of the same scene from the same settled "
+                      f"state ({s:.1f} s), sequential Gauss-Seidel in reference order; host has "
+                      f"{os.cpu_count()} logical cores"}
+
+
+# ------------------------------------------------------------------------------------------
+# batched independent worlds, world range partitioned over ranks
+# ------------------------------------------------------------------------------------------
+def run_worlds(args, rank, world_size):
+    import torch
+
+    import starframe_b200 as sf
+    from starframe_b200 import scenes
+
+    nw = args.worlds_per_gpu
+    bodies = scenes.worlds(nw, BODIES_PER_WORLD, first_world=rank * nw)
+    api = sf.product_api()
+    b = sf.Batch(api, nw, BODIES_PER_WORLD, device=torch.cuda.current_device())
+    b.upload(bodies)
+    for _ in range(args.settle):
+        b.step(DT, SUBSTEPS)
+    b.sync()
+    for _ in range(args.warmup):
+        b.step(DT, SUBSTEPS)
+        b.sync()
+    barrier(world_size)
+    torch.cuda.synchronize()
+    t_dev = 0.0
+    with ClockSampler(torch.cuda.current_device()) as clk:
+        for _ in range(args.steps):
+            b.step(DT, SUBSTEPS)
+            b.sync()
+            t_dev += b.last_step_ms()
+        torch.cuda.synchronize()
+    barrier(world_size)
+    st = b.stats()
+    n = nw * BODIES_PER_WORLD
+    pairs, contacts = float(st["n_pairs"].sum()), float(st["n_contacts"].sum())
+    # statistics gathered over ranks (the only collective in the path)
+    tot = allreduce_sum([pairs, contacts, float(n)], world_size)
+    t_dev_max = allreduce_max(t_dev, world_size)
+    units = tot[2] * SUBSTEPS * args.steps
+    value = units / (t_dev_max * 1e-3)
+    peak, peak_src = peaks()
+    bytes_step = b_alg(tot[2], tot[0], tot[1], 0.0) * tot[2] * SUBSTEPS / world_size
+    ach = bytes_step / (t_dev_max / args.steps * 1e-3) / 1e9
+    # e2e: host descs are not re-uploaded per frame in this mode; states are read back per frame
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(e2e_steps):
+        b.step(DT, SUBSTEPS)
+        states = b.download()
+    e2e_s = time.perf_counter() - t0
+    e2e_val = allreduce_sum([n * SUBSTEPS * e2e_steps / e2e_s], world_size)[0]
+    return {
+        "metric": "body-substeps/sec", "value": value, "unit": "body-substeps/s",
+        "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t_dev_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"worlds512: {nw} independent {BODIES_PER_WORLD}-body worlds per GPU "
+                               f"({nw * world_size} total), partitioned by world index",
+                   "bodies": int(tot[2]), "dt": "1/60", "substeps": SUBSTEPS,
+                   "settle_frames": args.settle, "pairs_per_body": tot[0] / tot[2],
+                   "contacts_per_body": tot[1] / tot[2],
+                   "l2": f"per-GPU state {n * 88 / 1e6:.0f} MB + contacts exceeds L2; no flush",
+                   "collective": "statistics only (all_reduce of 3 floats after the timed region)"},
+        "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one CTA per world, whole frame)",
+                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                     "peak_source": peak_src, "traffic": None},
+        "e2e": {"value": e2e_val, "unit": "body-substeps/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 32 * n, "call": "sfp_batch_step + sfp_batch_download"},
+        "gpu_launches": args.steps, "clocks": clk.summary(),
+    }
+
+
+# ------------------------------------------------------------------------------------------
+# reference arm: CPU oracle on the host cores
+# ------------------------------------------------------------------------------------------
+def run_reference(args, rank, world_size):
+    if rank != 0:
+        return None
+    import starframe_b200 as sf
+    from oracle import loader
+    from starframe_b200 import _ffi, scenes
+
+    api = loader.api()
+    t_budget = 45.0
+    if world_size == 1:
+        bodies, joints = make_scene(args.workload)
+        n = len(bodies)
+        ref = sf.World(api, solver_order=_ffi.ORDER_REFERENCE)
+        ref.upload_bodies(bodies)
+        ref.set_joints(joints)
+        # bounded sample: the settle phase is skipped on the CPU (240 frames of 100k bodies would
+        # take minutes); the pile is timed while it forms, frames [0, warmup+steps)
+        t0 = time.perf_counter()
+        for _ in range(args.warmup):
+            ref.step(DT, SUBSTEPS)
+        t1 = time.perf_counter()
+        done = 0
+        for _ in range(args.steps):
+            ref.step(DT, SUBSTEPS)
+            done += 1
+            if time.perf_counter() - t1 > t_budget:
+                break
+        s = time.perf_counter() - t1
+        st = ref.stats()
+        value = n * SUBSTEPS * done / s
+        cores, sample = 1, (f"{done} frames of {args.workload} from spawn (after {args.warmup} "
+                            f"warm-up frames), 1 thread: a single scene's Gauss-Seidel sweep is serial")
+        workload = args.workload
+        steps = done
+    else:
+        import concurrent.futures as cf
+
+        cores = os.cpu_count() or 1
+        nw = min(args.worlds_per_gpu * world_size, 4 * cores)
+        worlds = scenes.worlds(nw, BODIES_PER_WORLD)
+        ws = []
+        for k in range(nw):
+            r = sf.World(api, solver_order=_ffi.ORDER_REFERENCE)
+            r.upload_bodies(worlds[k])
+            ws.append(r)
+
+        def run(r, frames):
+            for _ in range(frames):
+                r.step(DT, SUBSTEPS)
+
+        with cf.ThreadPoolExecutor(cores) as ex:
+            list(ex.map(lambda r: run(r, args.warmup), ws))
+            t1 = time.perf_counter()
+            frames = max(1, min(args.steps, 20))
+            list(ex.map(lambda r: run(r, frames), ws))
+            s = time.perf_counter() - t1
+        n = nw * BODIES_PER_WORLD
+        value = n * SUBSTEPS * frames / s
+        sample = (f"{nw} of the {args.worlds_per_gpu * world_size} worlds x {frames} frames, one world "
+                  f"per task on {cores} threads")
+        workload = "worlds512"
+        steps = frames
+    return {
+        "impl": "reference", "metric": "body-substeps/sec", "value": value,
+        "unit": "body-substeps/s", "n_gpus": world_size, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": s / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload, "dt": "1/60", "substeps": SUBSTEPS},
+        "cpu_baseline": {"value": value, "unit": "body-substeps/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "body-substeps/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "note": "reference CPU step unavailable (tree not mounted, BASELINE.md §0): this is the "
+                "CPU oracle port, sequential Gauss-Seidel in reference order",
+    }
+
+
+# ------------------------------------------------------------------------------------------
+def barrier(world_size):
+    if world_size > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+
+
+def allreduce_max(x, world_size):
+    if world_size == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def allreduce_sum(xs, world_size):
+    if world_size == 1:
+        return list(xs)
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor(list(xs), dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return [float(v) for v in t.tolist()]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=60)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None)
+    ap.add_argument("--settle", type=int, default=240)
+    ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
+    ap.add_argument("--cpu-frames", type=int, default=12)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    if world_size != args.gpus and world_size > 1:
+        args.gpus = world_size
+    if args.workload is None:
+        args.workload = "pile100k" if world_size == 1 else "worlds512"
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        out = run_reference(args, rank, world_size)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return
+
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if args.workload == "worlds512":
+        out = run_worlds(args, rank, world_size)
+    else:
+        out = run_single(args, rank, world_size)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world_size > 1:
+        import torch.distributed as dist
+
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -155,7 +155,8 @@ typedef struct SfpStats {
     float max_penetration;  /* last substep, over contact points, at narrowphase time */
     float kinetic_energy;   /* after last substep */
     float potential_energy; /* -m g.x, after last substep */
-    uint32_t reserved[3];
+    uint32_t launches;      /* kernels launched by the last sfp_step (0 from the oracle) */
+    uint32_t reserved[2];
 } SfpStats; /* 80 bytes */
 
 typedef struct SfpWorld SfpWorld;
@@ -227,6 +228,11 @@ SFP_API const char* sfp_batch_last_error(SfpBatch* b);
  * events on the world's own stream (0 from the oracle) */
 SFP_API int32_t sfp_last_step_ms(SfpWorld* w, float* ms);
 SFP_API int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms);
+
+/* device-time breakdown of the last sfp_step, CUDA events on the world's stream:
+ * out[0] = whole step, out[1] = broadphase (AABBs, cell sort, pair emission),
+ * out[2] = colouring + bucketing by colour, out[3] = the persistent substep kernel. */
+SFP_API int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]);
 
 /* library identification: "cuda-sm_100a" or "cpu-oracle" */
 SFP_API const char* sfp_backend(void);

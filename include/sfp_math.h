@@ -140,6 +140,26 @@ SFP_HD int cell_coord(float x, float inv_cell) {
     return (int)f;
 }
 
+/* cell range of an AABB.  Returns false — and an EMPTY range — when the box is not finite or
+ * covers more than SFP_MAX_CELLS_PER_BODY cells (a runaway body; the caller raises the
+ * overflow flag): such a body takes no part in the broadphase. */
+#define SFP_MAX_CELLS_PER_BODY 16384
+SFP_HD bool cell_range(f4 bb, float inv_cell, int* x0, int* y0, int* x1, int* y1) {
+    bool finite = (bb.x - bb.x == 0.0f) && (bb.y - bb.y == 0.0f) && (bb.z - bb.z == 0.0f) &&
+                  (bb.w - bb.w == 0.0f);
+    *x0 = cell_coord(bb.x, inv_cell);
+    *y0 = cell_coord(bb.y, inv_cell);
+    *x1 = cell_coord(bb.z, inv_cell);
+    *y1 = cell_coord(bb.w, inv_cell);
+    long long cells = (long long)(*x1 - *x0 + 1) * (long long)(*y1 - *y0 + 1);
+    if (!finite || cells > SFP_MAX_CELLS_PER_BODY || cells <= 0) {
+        *x1 = *x0 - 1;
+        *y1 = *y0 - 1;
+        return false;
+    }
+    return true;
+}
+
 /* 32-bit cell key: row-major over the clamped 65536 x 65536 cell lattice */
 SFP_HD uint32_t cell_key(int cx, int cy) {
     return ((uint32_t)(cy - SFP_CELL_MIN) << 16) | (uint32_t)(cx - SFP_CELL_MIN);

@@ -78,15 +78,21 @@ int broadphase(SfpWorld& w, float dt) {
     float inv = 1.0f / w.p.cell_size;
     std::vector<Entry> entries;
     std::vector<int> cx0(w.n), cy0(w.n);
+    bool runaway = false;
     for (uint32_t i = 0; i < w.n; ++i) {
-        int x0 = cell_coord(aabb[i].x, inv), y0 = cell_coord(aabb[i].y, inv);
-        int x1 = cell_coord(aabb[i].z, inv), y1 = cell_coord(aabb[i].w, inv);
+        int x0, y0, x1, y1;
+        if (!cell_range(aabb[i], inv, &x0, &y0, &x1, &y1)) runaway = true;
         cx0[i] = x0;
         cy0[i] = y0;
         for (int cy = y0; cy <= y1; ++cy)
             for (int cx = x0; cx <= x1; ++cx) entries.push_back({cell_key(cx, cy), i});
     }
     w.n_entries = (uint32_t)entries.size();
+    if (runaway) {
+        w.stats.overflow |= 16u;
+        w.err = "a body is not finite or spans more than 16384 cells";
+        return SFP_E_CAPACITY;
+    }
     if (w.p.max_entries && entries.size() > w.p.max_entries) {
         w.stats.overflow |= 1u;
         w.err = "broadphase entry capacity exceeded";

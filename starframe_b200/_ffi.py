@@ -77,7 +77,7 @@ STATS_DTYPE = np.dtype(
         ("n_entries", "<u4"), ("n_pairs", "<u4"), ("n_contacts", "<u4"),
         ("n_manifolds", "<u4"), ("n_colours", "<u4"), ("colour_rounds", "<u4"),
         ("overflow", "<u4"), ("max_penetration", "<f4"), ("kinetic_energy", "<f4"),
-        ("potential_energy", "<f4"), ("reserved", "<u4", (3,)),
+        ("potential_energy", "<f4"), ("launches", "<u4"), ("reserved", "<u4", (2,)),
     ]
 )
 assert PARAMS_DTYPE.itemsize == 64
@@ -94,7 +94,7 @@ PRODUCT_SYMBOLS = [
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
     "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
-    "backend",
+    "last_step_breakdown_ms", "backend",
 ]
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
@@ -156,6 +156,7 @@ class Api:
             "get_stats": [vp, vp],
             "step_host": [vp, vp, vp, u32, f32, u32],
             "last_step_ms": [vp, C.POINTER(f32)],
+            "last_step_breakdown_ms": [vp, vp],
             "brute_pairs": [vp, f32, vp, u32, C.POINTER(u32)],
             "batch_create": [vp, u32, u32, C.POINTER(vp)],
             "batch_destroy": [vp],
@@ -298,6 +299,12 @@ class World:
         ms = C.c_float(0)
         self._check(self.api.fn("last_step_ms")(self.h, C.byref(ms)), "last_step_ms")
         return float(ms.value)
+
+    def last_step_breakdown_ms(self) -> dict:
+        out = np.zeros(4, dtype=np.float32)
+        self._check(self.api.fn("last_step_breakdown_ms")(self.h, _ptr(out)), "breakdown")
+        return {"step": float(out[0]), "broadphase": float(out[1]), "colour": float(out[2]),
+                "substeps": float(out[3])}
 
     def brute_pairs(self, dt: float) -> np.ndarray:
         n = C.c_uint32(0)

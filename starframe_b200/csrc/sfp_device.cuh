@@ -98,8 +98,8 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
         f4 pose = ld4(c.pose, i), vel = ld4(c.vel, i), shape = ld4(c.shape, i);
         f2 mi = ld2(c.minv, i);
         f4 bb = sfp::body_aabb(pose, vel, shape, c.aabb_margin, c.vel_expand, dt);
-        int x0 = sfp::cell_coord(bb.x, c.inv_cell), y0 = sfp::cell_coord(bb.y, c.inv_cell);
-        int x1 = sfp::cell_coord(bb.z, c.inv_cell), y1 = sfp::cell_coord(bb.w, c.inv_cell);
+        int x0, y0, x1, y1;
+        if (!sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1)) atomicOr(&c.cnt->overflow, 16u);
         st4(c.aabb, i, bb);
         int dyn = (mi.x > 0.0f || mi.y > 0.0f) ? 1 : 0;
         c.meta[i] = make_int4(x0, y0, (int)sfp::f2u(c.mat[i].w), dyn);
@@ -116,7 +116,8 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
     for (uint32_t i = tid; i < c.n; i += nth) {
         f4 bb = ld4(c.aabb, i);
         int4 m = c.meta[i];
-        int x1 = sfp::cell_coord(bb.z, c.inv_cell), y1 = sfp::cell_coord(bb.w, c.inv_cell);
+        int x0, y0, x1, y1;
+        sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1);
         uint32_t o = c.cell_off[i];
         for (int cy = m.y; cy <= y1; ++cy)
             for (int cx = m.x; cx <= x1; ++cx) {

@@ -129,8 +129,9 @@ struct SfpWorld {
     SfpParams p;
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_bp = nullptr, ev_col = nullptr;
     bool timed = false;
+    uint32_t launches = 0;
     uint32_t n = 0, nj = 0;
     uint32_t cap_bodies = 0, cap_joints = 0, cap_entries = 0, cap_pairs = 0;
     Ctx ctx;
@@ -290,6 +291,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     cudaStream_t st = w->stream;
     const bool multi = (w->p.flags & SFP_FLAG_MULTI_KERNEL) != 0u;
     const uint32_t gb = blocks_for(w, w->n);
+    const bool mark = !(w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP);
     k_aabb_count<<<gb, TPB, 0, st>>>(c, dt);
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
                       &w->d_cnt->n_entries, st));
@@ -301,18 +303,22 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       &w->d_cnt->n_pairs, st));
     k_pair_write<<<ge, TPB, 0, st>>>(c);
     CU(cudaGetLastError());
+    w->launches += 4 + 3 + 3 + 12;
+    if (mark) CU(cudaEventRecord(w->ev_bp, st));
 
     if (!multi) {
         uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_colour,
                                              blocks_for(w, 4ull * w->n + w->nj));
         void* args[] = {&c};
         TRY(launch_coop(w, (const void*)k_colour_coop, blocks, args));
+        w->launches += 1;
     } else {
         const uint32_t gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
         k_colour_init<<<gp, TPB, 0, st>>>(c);
         for (uint32_t round = 0; round < (uint32_t)MAX_ROUNDS; ++round) {
             k_colour_bid<<<gp, TPB, 0, st>>>(c, round);
             k_colour_take<<<gp, TPB, 0, st>>>(c, round);
+            w->launches += 2;
             uint32_t flag = 0;
             CU(cudaMemcpyAsync(&flag, &w->d_cnt->round_flags[round], sizeof(flag),
                                cudaMemcpyDeviceToHost, st));
@@ -327,6 +333,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       0, w->d_hist, st));
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
+    w->launches += 4 + (w->nj ? 3 : 0);
+    if (mark) CU(cudaEventRecord(w->ev_col, st));
     return SFP_OK;
 }
 
@@ -340,6 +348,7 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
         uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_substep,
                                              blocks_for(w, 4ull * w->n + w->nj));
         void* args[] = {&c, &h, &substeps, &rest_threshold};
+        w->launches += 1;
         return launch_coop(w, (const void*)k_substeps_coop, blocks, args);
     }
     uint32_t ncol = 0;
@@ -354,6 +363,7 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
         k_derive<<<gb, TPB, 0, st>>>(c, inv_h);
         for (uint32_t col = 0; col < ncol; ++col)
             k_solve_vel<<<gp, TPB, 0, st>>>(c, col, h, rest_threshold);
+        w->launches += 3 + 2 * ncol;
     }
     CU(cudaGetLastError());
     return SFP_OK;
@@ -385,7 +395,7 @@ int check_overflow(SfpWorld* w, const Counters& k) {
         char buf[160];
         snprintf(buf, sizeof(buf),
                  "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=colours>64, "
-                 "8=colour rounds)",
+                 "8=colour rounds, 16=runaway or non-finite body)",
                  k.overflow, w->cap_entries, w->cap_pairs);
         w->err = buf;
         return SFP_E_CAPACITY;
@@ -439,6 +449,8 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
         return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&w->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&w->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&w->ev_bp)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&w->ev_col)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaMalloc(&w->d_cnt, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMemset(w->d_cnt, 0, sizeof(Counters))) != cudaSuccess) return fail("cudaMemset", e);
     w->ctx.cnt = w->d_cnt;
@@ -474,6 +486,8 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->pin_vel) cudaFreeHost(w->pin_vel);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
+    if (w->ev_bp) cudaEventDestroy(w->ev_bp);
+    if (w->ev_col) cudaEventDestroy(w->ev_col);
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
     return SFP_OK;
@@ -575,6 +589,7 @@ int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps) {
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
     CU(cudaEventRecord(w->ev0, w->stream));
+    w->launches = 0;
     int rc = frame(w, dt, substeps);
     if (rc != SFP_OK) return rc;
     CU(cudaEventRecord(w->ev1, w->stream));
@@ -743,6 +758,7 @@ int32_t sfp_get_stats(SfpWorld* w, SfpStats* out) {
     w->stats.colour_rounds = k.colour_rounds;
     w->stats.overflow |= k.overflow;
     w->stats.max_penetration = sfp::u2f(k.maxpen_bits);
+    w->stats.launches = w->launches;
     std::vector<sfp::f4> pose(w->n), vel(w->n);
     if (w->n) {
         CU(cudaMemcpy(pose.data(), w->ctx.pose, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost));
@@ -763,6 +779,21 @@ int32_t sfp_last_step_ms(SfpWorld* w, float* ms) {
     CU(cudaSetDevice(w->device));
     CU(cudaEventSynchronize(w->ev1));
     CU(cudaEventElapsedTime(ms, w->ev0, w->ev1));
+    return SFP_OK;
+}
+
+int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]) {
+    if (!w || !out) return SFP_E_INVALID;
+    out[0] = out[1] = out[2] = out[3] = 0.0f;
+    if (!w->timed || w->n == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    CU(cudaEventSynchronize(w->ev1));
+    CU(cudaEventElapsedTime(&out[0], w->ev0, w->ev1));
+    if (!(w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP)) {
+        CU(cudaEventElapsedTime(&out[1], w->ev0, w->ev_bp));
+        CU(cudaEventElapsedTime(&out[2], w->ev_bp, w->ev_col));
+        CU(cudaEventElapsedTime(&out[3], w->ev_col, w->ev1));
+    }
     return SFP_OK;
 }
 

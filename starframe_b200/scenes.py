@@ -113,11 +113,16 @@ def circles_container(n: int = 10_000, seed: int = BASE_SEED + 2, width: float =
 
 
 def mixed_pile(n: int = 100_000, seed: int = BASE_SEED + 3, width: float | None = None,
-               cols: int | None = None):
-    """Config 3: n bodies, type ~ uniform{circle, capsule, rounded rect}, random materials."""
+               cols: int | None = None, rows_hint: int = 100):
+    """Config 3: n bodies, type ~ uniform{circle, capsule, rounded rect}, random materials,
+    spawned on a jittered grid (pitch 0.65 m > the largest bounding diameter, so nothing
+    overlaps at spawn) about `rows_hint` rows high above a static floor with two walls.
+    (SURVEY.md §8d suggested 400 x 250 rows; 250 rows make the top bodies fall 160 m and hit
+    the pile at 55 m/s, which is a ballistics test, not a pile — 100 rows are used instead.)"""
     if cols is None:
-        cols = max(1, int(round(np.sqrt(n * 1.6))))
-    pitch = 0.6
+        cols = max(1, int(np.ceil(n / rows_hint))) if n > rows_hint * rows_hint else max(
+            1, int(round(np.sqrt(n * 1.6))))
+    pitch = 0.65
     if width is None:
         width = cols * pitch + 0.6
     t = (uniform(seed, 1, n) * 3.0).astype(np.int32).clip(0, 2)
@@ -198,10 +203,10 @@ def ropes(n_ropes: int = 2000, links: int = 64, n_free: int = 20_000, seed: int 
 
 
 def small_world(world: int, n_bodies: int = 512, seed: int = BASE_SEED + 5,
-                width: float = 9.0):
+                width: float = 16.0):
     """Config 5, one world: config-3 distribution scaled down; 3 static + (n-3) dynamic."""
     nd = n_bodies - 3
-    cols = max(1, int((width - 0.6) / 0.6))
+    cols = max(1, int((width - 0.6) / 0.65))
     b, _ = mixed_pile(nd, seed=(seed * 1_000_003 + world) & 0x7FFFFFFFFFFF, width=width, cols=cols)
     return b, no_joints()
 
