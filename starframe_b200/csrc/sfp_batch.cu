@@ -1,13 +1,485 @@
-// placeholder — replaced below
+// sfp_batch.cu — batched independent worlds (BASELINE.json config 5): ONE thread block per world
+// runs that world's WHOLE frame — broadphase, colouring, all substeps — in a single launch.
+//
+// Why a different shape from sfp_world.cu: a 512-body world is far too small to fill a B200, and
+// its ~350 dependent phases per frame would each cost a grid-wide barrier.  Inside one CTA the
+// same phases are separated by __syncthreads() (tens of ns) and the world's state (45 KB of
+// bodies, a few hundred KB of contacts) stays in that SM's L1 / the L2.  The grid is the world
+// list: 148 SMs x BATCH_CTAS_PER_SM worlds in flight, the rest queue behind them.
+//
+// The stages are the SAME __device__ functions as the single-world path (sfp_device.cuh), called
+// with (tid, nth) = (threadIdx.x, blockDim.x) on a per-world view of the buffers, so a world
+// stepped in a batch is bit-identical to the same world stepped alone, and to the oracle.  Only
+// the broadphase differs in structure: with 512 bodies an all-pairs AABB sweep (131k tests) is
+// cheaper than hashing and yields exactly the same pair SET, which is all that matters
+// downstream (the colouring depends on the set, not on the order).
+//
+// Reference: none for batching — north_star: "batched independent worlds are partitioned across
+// the 8 GPUs of one box, with NCCL used only to gather statistics".
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
 #include "sfp.h"
-extern "C" {
-int32_t sfp_batch_create(const SfpParams*, uint32_t, uint32_t, SfpBatch** out) { if (out) *out = nullptr; return SFP_E_INVALID; }
-int32_t sfp_batch_destroy(SfpBatch*) { return SFP_OK; }
-int32_t sfp_batch_upload(SfpBatch*, const SfpBodyDesc*) { return SFP_E_INVALID; }
-int32_t sfp_batch_step(SfpBatch*, float, uint32_t) { return SFP_E_INVALID; }
-int32_t sfp_batch_sync(SfpBatch*) { return SFP_E_INVALID; }
-int32_t sfp_batch_download(SfpBatch*, SfpBodyState*) { return SFP_E_INVALID; }
-int32_t sfp_batch_stats(SfpBatch*, SfpStats*) { return SFP_E_INVALID; }
-const char* sfp_batch_last_error(SfpBatch*) { return "batch not built yet"; }
-int32_t sfp_batch_last_step_ms(SfpBatch*, float*) { return SFP_E_INVALID; }
+#include "sfp_device.cuh"
+#include "sfp_host.h"
+#include "sfp_sort.cuh"
+
+using namespace sfpk;
+
+namespace {
+
+constexpr int BTPB = 256;  // threads per world
+
+struct BatchCtx {
+    Ctx base;              // pointers to world 0's slabs; parameters
+    uint32_t bpw;          // bodies per world
+    uint32_t pair_cap;     // pairs per world
+    uint32_t n_worlds;
+    Counters* counters;    // [n_worlds]
+    uint32_t* scratch;     // [n_worlds][bpw] per-body pair counts / offsets
+};
+
+__device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
+    Ctx c = b.base;
+    const size_t bo = (size_t)w * b.bpw, po = (size_t)w * b.pair_cap;
+    c.pose += bo;
+    c.prev += bo;
+    c.vel += bo;
+    c.shape += bo;
+    c.mat += bo;
+    c.minv += bo;
+    c.aabb += bo;
+    c.meta += bo;
+    c.mask += bo;
+    c.claim0 += bo;
+    c.claim1 += bo;
+    c.pairs_raw += po;
+    c.pairs += po;
+    c.pcol += po;
+    c.ca += po;
+    c.cb += po;
+    c.cp0 += po;
+    c.cp1 += po;
+    c.cs += po;
+    c.lam += po;
+    c.cnt = b.counters + w;
+    c.n = b.bpw;
+    c.nj = 0;
+    c.cap_pairs = b.pair_cap;
+    return c;
 }
+
+// all-pairs broadphase of one world: body a scans b > a.  count -> block scan -> write.
+__device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint32_t* smem9) {
+    const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
+    for (uint32_t i = tid; i < n; i += nth) {
+        f4 bb = sfp::body_aabb(ld4(c.pose, i), ld4(c.vel, i), ld4(c.shape, i), c.aabb_margin,
+                               c.vel_expand, dt);
+        int x0, y0, x1, y1;
+        if (!sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1)) atomicOr(&c.cnt->overflow, 16u);
+        st4(c.aabb, i, bb);
+        f2 mi = ld2(c.minv, i);
+        c.meta[i] = make_int4(x0, y0, (int)sfp::f2u(c.mat[i].w), (mi.x > 0.0f || mi.y > 0.0f) ? 1 : 0);
+    }
+    if (tid == 0) {
+        c.cnt->n_colours = 0;
+        c.cnt->colour_rounds = 0;
+        c.cnt->n_entries = 0;
+    }
+    __syncthreads();
+    auto test = [&](uint32_t a, f4 bba, int4 ma, uint32_t b) {
+        int4 mb = c.meta[b];
+        if ((ma.w | mb.w) == 0) return false;
+        if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
+        return sfp::aabb_overlap(bba, ld4(c.aabb, b));
+    };
+    // pass 1: counts per body (strided assignment balances the triangular loop)
+    for (uint32_t a = tid; a < n; a += nth) {
+        f4 bba = ld4(c.aabb, a);
+        int4 ma = c.meta[a];
+        uint32_t k = 0;
+        for (uint32_t b = a + 1; b < n; ++b) k += test(a, bba, ma, b) ? 1u : 0u;
+        cnt_off[a] = k;
+    }
+    __syncthreads();
+    // exclusive scan over n counts by the block (n <= a few thousand): chunked
+    __shared__ uint32_t carry;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += nth) {
+        uint32_t i = base + tid;
+        uint32_t v = (i < n) ? cnt_off[i] : 0u;
+        uint32_t total;
+        uint32_t ex = block_excl_scan(v, &total, smem9);
+        uint32_t cbase = carry;
+        if (i < n) cnt_off[i] = cbase + ex;
+        __syncthreads();
+        if (tid == 0) carry = cbase + total;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        uint32_t P = carry;
+        if (P > c.cap_pairs) {
+            atomicOr(&c.cnt->overflow, 2u);
+            P = c.cap_pairs;
+        }
+        c.cnt->n_pairs = P;
+    }
+    // pass 2: write
+    for (uint32_t a = tid; a < n; a += nth) {
+        f4 bba = ld4(c.aabb, a);
+        int4 ma = c.meta[a];
+        uint32_t o = cnt_off[a];
+        for (uint32_t b = a + 1; b < n; ++b)
+            if (test(a, bba, ma, b)) {
+                if (o < c.cap_pairs) c.pairs_raw[o] = make_uint2(a, b);
+                ++o;
+            }
+    }
+    __syncthreads();
+}
+
+// bucket pairs by colour (stable): for each colour one block-wide scan of the membership flags
+__device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
+    const uint32_t tid = threadIdx.x, nth = blockDim.x;
+    const uint32_t P = c.cnt->n_pairs, ncol = c.cnt->n_colours;
+    __shared__ uint32_t run;
+    if (tid == 0) run = 0;
+    __syncthreads();
+    for (uint32_t col = 0; col <= SFP_MAX_COLOURS; ++col) {
+        if (tid == 0) c.cnt->pair_col_off[col] = run;
+        if (col >= ncol) {
+            __syncthreads();
+            continue;
+        }
+        for (uint32_t base = 0; base < P; base += nth) {
+            uint32_t k = base + tid;
+            bool in = k < P && c.pcol[k] == col;
+            uint32_t total;
+            uint32_t ex = block_excl_scan(in ? 1u : 0u, &total, smem9);
+            uint32_t r = run;
+            if (in) c.pairs[r + ex] = c.pairs_raw[k];
+            __syncthreads();
+            if (tid == 0) run = r + total;
+            __syncthreads();
+        }
+    }
+    if (tid == 0)
+        for (uint32_t col = 0; col <= SFP_MAX_COLOURS; ++col) c.cnt->joint_col_off[col] = 0;
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(BTPB) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
+                                                      float rest_threshold) {
+    __shared__ uint32_t smem9[9];
+    const uint32_t w = blockIdx.x;
+    if (w >= b.n_worlds) return;
+    const Ctx c = world_view(b, w);
+    const uint32_t tid = threadIdx.x, nth = blockDim.x;
+    uint32_t* cnt_off = b.scratch + (size_t)w * b.bpw;
+
+    batch_broadphase(c, cnt_off, dt, smem9);
+
+    // colouring: same rounds as stage_colour_* in the single-world path
+    stage_colour_init(c, tid, nth);
+    __syncthreads();
+    uint32_t round = 0;
+    for (; round < (uint32_t)MAX_ROUNDS; ++round) {
+        stage_colour_bid(c, round, tid, nth);
+        __syncthreads();
+        stage_colour_take(c, round, tid, nth);
+        __syncthreads();
+        if (c.cnt->round_flags[round] == 0u) break;
+    }
+    if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+    __syncthreads();
+    batch_bucket(c, smem9);
+
+    const uint32_t ncol = c.cnt->n_colours;
+    const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    for (uint32_t s = 0; s < substeps; ++s) {
+        stage_integrate(c, h, tid, nth);
+        __syncthreads();
+        stage_narrowphase(c, tid, nth);
+        __syncthreads();
+        for (uint32_t col = 0; col < ncol; ++col) {
+            stage_solve_pos(c, col, inv_h2, tid, nth);
+            __syncthreads();
+        }
+        stage_derive(c, inv_h, tid, nth);
+        __syncthreads();
+        for (uint32_t col = 0; col < ncol; ++col) {
+            stage_solve_vel(c, col, h, rest_threshold, tid, nth);
+            __syncthreads();
+        }
+    }
+}
+
+}  // namespace
+
+#define BCU(call)                                                        \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) {                                         \
+            b->err = std::string(#call) + ": " + cudaGetErrorString(e_); \
+            b->sticky = SFP_E_CUDA;                                      \
+            return SFP_E_CUDA;                                           \
+        }                                                                \
+    } while (0)
+
+struct SfpBatch {
+    SfpParams p;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false, uploaded = false, stepped = false;
+    uint32_t n_worlds = 0, bpw = 0, pair_cap = 0;
+    BatchCtx ctx;
+    std::vector<void*> allocs;
+    std::vector<sfp::f2> h_minv;
+    uint64_t frames = 0, body_substeps = 0;
+    uint32_t n_dynamic_total = 0;
+    std::vector<uint32_t> n_dynamic;
+    std::string err;
+    int32_t sticky = SFP_OK;
+};
+
+namespace {
+template <typename T>
+int balloc(SfpBatch* b, T** out, size_t count) {
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    BCU(cudaMalloc(&p, bytes));
+    BCU(cudaMemset(p, 0, bytes));
+    b->allocs.push_back(p);
+    *out = reinterpret_cast<T*>(p);
+    return SFP_OK;
+}
+#define BTRY(x)                        \
+    do {                               \
+        int rc_ = (x);                 \
+        if (rc_ != SFP_OK) return rc_; \
+    } while (0)
+}  // namespace
+
+extern "C" {
+
+int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bodies_per_world,
+                         SfpBatch** out) {
+    if (!out) return SFP_E_INVALID;
+    *out = nullptr;
+    SfpParams p;
+    if (params) p = *params;
+    else sfp::default_params(&p);
+    if (!sfp::params_valid(p) || p.solver_order != SFP_ORDER_COLOUR) return SFP_E_INVALID;
+    if (n_worlds == 0 || bodies_per_world == 0 || bodies_per_world > 4096) return SFP_E_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        fprintf(stderr, "libsfp_b200: no CUDA device — this library has no CPU fallback\n");
+        return SFP_E_CUDA;
+    }
+    if (p.device < 0 || p.device >= ndev) return SFP_E_INVALID;
+    SfpBatch* b = new (std::nothrow) SfpBatch();
+    if (!b) return SFP_E_NOMEM;
+    b->p = p;
+    b->device = p.device;
+    b->n_worlds = n_worlds;
+    b->bpw = bodies_per_world;
+    b->pair_cap = p.max_pairs ? p.max_pairs : 12u * bodies_per_world + 256u;
+    std::memset(&b->ctx, 0, sizeof(b->ctx));
+    auto die = [&](int rc) {
+        sfp_batch_destroy(b);
+        return (int32_t)rc;
+    };
+    if (cudaSetDevice(b->device) != cudaSuccess) return die(SFP_E_CUDA);
+    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess)
+        return die(SFP_E_CUDA);
+    if (cudaEventCreate(&b->ev0) != cudaSuccess || cudaEventCreate(&b->ev1) != cudaSuccess)
+        return die(SFP_E_CUDA);
+    const size_t nb = (size_t)n_worlds * bodies_per_world, np = (size_t)n_worlds * b->pair_cap;
+    Ctx& c = b->ctx.base;
+    int rc = SFP_OK;
+#define A(ptr, count) \
+    if (rc == SFP_OK) rc = balloc(b, &(ptr), (count))
+    A(c.pose, nb);
+    A(c.prev, nb);
+    A(c.vel, nb);
+    float4 *shape = nullptr, *mat = nullptr;
+    float2* minv = nullptr;
+    A(shape, nb);
+    A(mat, nb);
+    A(minv, nb);
+    c.shape = shape;
+    c.mat = mat;
+    c.minv = minv;
+    A(c.aabb, nb);
+    A(c.meta, nb);
+    A(c.mask, nb);
+    A(c.claim0, nb);
+    A(c.claim1, nb);
+    A(c.pairs_raw, np);
+    A(c.pairs, np);
+    A(c.pcol, np);
+    A(c.ca, np);
+    A(c.cb, np);
+    A(c.cp0, np);
+    A(c.cp1, np);
+    A(c.cs, np);
+    A(c.lam, np);
+    A(b->ctx.counters, n_worlds);
+    A(b->ctx.scratch, nb);
+#undef A
+    if (rc != SFP_OK) return die(rc);
+    // joints are not part of the batched path: give the unused pointers a valid target
+    c.jbod_in = reinterpret_cast<const uint2*>(c.pairs_raw);
+    c.jcol = c.pcol;
+    c.gx = p.gravity_x;
+    c.gy = p.gravity_y;
+    c.inv_cell = 1.0f / p.cell_size;
+    c.aabb_margin = p.aabb_margin;
+    c.vel_expand = p.vel_expand;
+    c.contact_margin = p.contact_margin;
+    b->ctx.bpw = bodies_per_world;
+    b->ctx.pair_cap = b->pair_cap;
+    b->ctx.n_worlds = n_worlds;
+    *out = b;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_destroy(SfpBatch* b) {
+    if (!b) return SFP_OK;
+    cudaSetDevice(b->device);
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    for (void* p : b->allocs) cudaFree(p);
+    if (b->ev0) cudaEventDestroy(b->ev0);
+    if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->stream) cudaStreamDestroy(b->stream);
+    delete b;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
+    if (!b || !bodies) return SFP_E_INVALID;
+    const size_t nb = (size_t)b->n_worlds * b->bpw;
+    for (size_t i = 0; i < nb; ++i)
+        if (!sfp::desc_valid(bodies[i])) {
+            b->err = "invalid body desc at index " + std::to_string(i);
+            return SFP_E_INVALID;
+        }
+    BCU(cudaSetDevice(b->device));
+    std::vector<sfp::f4> pose(nb), vel(nb), shape(nb), mat(nb);
+    b->h_minv.resize(nb);
+    b->n_dynamic.assign(b->n_worlds, 0);
+    for (size_t i = 0; i < nb; ++i) {
+        sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &b->h_minv[i], &shape[i], &mat[i]);
+        if (b->h_minv[i].x > 0.0f || b->h_minv[i].y > 0.0f) b->n_dynamic[i / b->bpw] += 1;
+    }
+    Ctx& c = b->ctx.base;
+    BCU(cudaStreamSynchronize(b->stream));
+    BCU(cudaMemcpy(c.pose, pose.data(), sizeof(sfp::f4) * nb, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(c.prev, pose.data(), sizeof(sfp::f4) * nb, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(c.vel, vel.data(), sizeof(sfp::f4) * nb, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(const_cast<float4*>(c.shape), shape.data(), sizeof(sfp::f4) * nb,
+                   cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(const_cast<float4*>(c.mat), mat.data(), sizeof(sfp::f4) * nb,
+                   cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(const_cast<float2*>(c.minv), b->h_minv.data(), sizeof(sfp::f2) * nb,
+                   cudaMemcpyHostToDevice));
+    BCU(cudaMemset(b->ctx.counters, 0, sizeof(Counters) * b->n_worlds));
+    b->uploaded = true;
+    b->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
+    if (!b || !(dt > 0.0f) || substeps == 0 || substeps > 1024 || !b->uploaded)
+        return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    BCU(cudaSetDevice(b->device));
+    const float h = dt / (float)substeps;
+    const float g = sqrtf(b->p.gravity_x * b->p.gravity_x + b->p.gravity_y * b->p.gravity_y);
+    BCU(cudaEventRecord(b->ev0, b->stream));
+    k_batch_frame<<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, 2.0f * g * h);
+    BCU(cudaGetLastError());
+    BCU(cudaEventRecord(b->ev1, b->stream));
+    b->timed = true;
+    b->stepped = true;
+    b->frames += 1;
+    b->body_substeps += (uint64_t)b->n_worlds * b->bpw * substeps;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_sync(SfpBatch* b) {
+    if (!b) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    BCU(cudaSetDevice(b->device));
+    BCU(cudaStreamSynchronize(b->stream));
+    return SFP_OK;
+}
+
+int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out) {
+    if (!b || !out) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    BCU(cudaSetDevice(b->device));
+    const size_t nb = (size_t)b->n_worlds * b->bpw;
+    std::vector<sfp::f4> pose(nb), vel(nb);
+    BCU(cudaStreamSynchronize(b->stream));
+    BCU(cudaMemcpy(pose.data(), b->ctx.base.pose, sizeof(sfp::f4) * nb, cudaMemcpyDeviceToHost));
+    BCU(cudaMemcpy(vel.data(), b->ctx.base.vel, sizeof(sfp::f4) * nb, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < nb; ++i) out[i] = sfp::state_from_records(pose[i], vel[i]);
+    return SFP_OK;
+}
+
+int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out) {
+    if (!b || !out) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    BCU(cudaSetDevice(b->device));
+    std::vector<Counters> k(b->n_worlds);
+    BCU(cudaStreamSynchronize(b->stream));
+    BCU(cudaMemcpy(k.data(), b->ctx.counters, sizeof(Counters) * b->n_worlds,
+                   cudaMemcpyDeviceToHost));
+    int32_t rc = SFP_OK;
+    for (uint32_t w = 0; w < b->n_worlds; ++w) {
+        SfpStats s;
+        std::memset(&s, 0, sizeof(s));
+        s.frames = b->frames;
+        s.body_substeps = b->body_substeps / b->n_worlds;
+        s.n_bodies = b->bpw;
+        s.n_dynamic = b->n_dynamic.empty() ? 0u : b->n_dynamic[w];
+        s.n_pairs = b->stepped ? k[w].n_pairs : 0u;
+        s.n_contacts = k[w].n_contacts;
+        s.n_manifolds = k[w].n_manifolds;
+        s.n_colours = k[w].n_colours;
+        s.colour_rounds = k[w].colour_rounds;
+        s.overflow = k[w].overflow;
+        s.max_penetration = sfp::u2f(k[w].maxpen_bits);
+        s.launches = 1;
+        out[w] = s;
+        if (k[w].overflow) {
+            b->err = "world " + std::to_string(w) + ": capacity exceeded (bits " +
+                     std::to_string(k[w].overflow) + ")";
+            rc = SFP_E_CAPACITY;
+        }
+    }
+    return rc;
+}
+
+const char* sfp_batch_last_error(SfpBatch* b) { return b ? b->err.c_str() : "null batch"; }
+
+int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms) {
+    if (!b || !ms) return SFP_E_INVALID;
+    *ms = 0.0f;
+    if (!b->timed) return SFP_OK;
+    BCU(cudaSetDevice(b->device));
+    BCU(cudaEventSynchronize(b->ev1));
+    BCU(cudaEventElapsedTime(ms, b->ev0, b->ev1));
+    return SFP_OK;
+}
+
+}  // extern "C"

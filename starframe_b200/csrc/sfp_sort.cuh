@@ -54,7 +54,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total,
 }
 
 // ---- scan, phase 1: per-tile sums ---------------------------------------------------------
-__global__ void __launch_bounds__(SCAN_THREADS)
+static __global__ void __launch_bounds__(SCAN_THREADS)
 k_scan_tile_sums(const uint32_t* __restrict__ in, const uint32_t* __restrict__ n_ptr,
                  uint32_t* __restrict__ tile_sums) {
     __shared__ uint32_t sm[9];
@@ -74,7 +74,7 @@ k_scan_tile_sums(const uint32_t* __restrict__ in, const uint32_t* __restrict__ n
 }
 
 // ---- scan, phase 2: one block scans the tile sums in place --------------------------------
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 k_scan_sums(uint32_t* __restrict__ tile_sums, uint32_t n_tiles, uint32_t* __restrict__ total_out) {
     __shared__ uint32_t sm[33];
     __shared__ uint32_t carry_s;
@@ -105,7 +105,7 @@ k_scan_sums(uint32_t* __restrict__ tile_sums, uint32_t n_tiles, uint32_t* __rest
 }
 
 // ---- scan, phase 3: rescan each tile with its offset; out[n] = total ----------------------
-__global__ void __launch_bounds__(SCAN_THREADS)
+static __global__ void __launch_bounds__(SCAN_THREADS)
 k_scan_apply(const uint32_t* __restrict__ in, const uint32_t* __restrict__ n_ptr,
              const uint32_t* __restrict__ tile_sums, uint32_t* __restrict__ out) {
     __shared__ uint32_t sm[9];
@@ -146,7 +146,7 @@ inline cudaError_t scan_exclusive(const uint32_t* in, uint32_t* out, const uint3
 
 // ---- radix sort pass ----------------------------------------------------------------------
 // hist layout: hist[digit * n_blocks + block]  (digit-major so one scan yields global bases)
-__global__ void __launch_bounds__(RADIX_THREADS)
+static __global__ void __launch_bounds__(RADIX_THREADS)
 k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_ptr, int shift,
              uint32_t* __restrict__ hist) {
     __shared__ uint32_t h[RADIX_BINS];
@@ -166,7 +166,7 @@ k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_p
 }
 
 // one block: exclusive scan over the whole digit-major histogram (RADIX_BINS * n_blocks)
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 k_radix_scan(uint32_t* __restrict__ hist, uint32_t count) {
     __shared__ uint32_t sm[33];
     __shared__ uint32_t carry_s;
@@ -207,7 +207,7 @@ k_radix_scan(uint32_t* __restrict__ hist, uint32_t count) {
 }
 
 // stable scatter.  vals_in == nullptr means "value = source index" (used to build permutations)
-__global__ void __launch_bounds__(RADIX_THREADS)
+static __global__ void __launch_bounds__(RADIX_THREADS)
 k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                 uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                 const uint32_t* __restrict__ n_ptr, int shift,
