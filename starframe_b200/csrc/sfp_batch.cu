@@ -145,46 +145,98 @@ __device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint
     __syncthreads();
 }
 
-// bucket pairs by colour (stable): for each colour one block-wide scan of the membership flags
+// bucket pairs by (colour, shape-type pair): counting sort on the 10-bit key written by
+// stage_colour_take.  Ranks inside a bin come from a shared-memory cursor (integer atomics): the
+// order INSIDE a (colour, type) bin is therefore arbitrary, which changes no result — constraints
+// of one colour touch disjoint bodies — only which contact slot a pair happens to use.
+constexpr int BUCKET_BINS = SFP_MAX_COLOURS * 16;
 __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
+    __shared__ uint32_t bins[BUCKET_BINS];
     const uint32_t tid = threadIdx.x, nth = blockDim.x;
-    const uint32_t P = c.cnt->n_pairs, ncol = c.cnt->n_colours;
-    __shared__ uint32_t run;
-    if (tid == 0) run = 0;
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = tid; k < BUCKET_BINS; k += nth) bins[k] = 0;
     __syncthreads();
-    for (uint32_t col = 0; col <= SFP_MAX_COLOURS; ++col) {
-        if (tid == 0) c.cnt->pair_col_off[col] = run;
-        if (col >= ncol) {
-            __syncthreads();
-            continue;
-        }
-        for (uint32_t base = 0; base < P; base += nth) {
-            uint32_t k = base + tid;
-            bool in = k < P && c.pcol[k] == col;
-            uint32_t total;
-            uint32_t ex = block_excl_scan(in ? 1u : 0u, &total, smem9);
-            uint32_t r = run;
-            if (in) c.pairs[r + ex] = c.pairs_raw[k];
-            __syncthreads();
-            if (tid == 0) run = r + total;
-            __syncthreads();
-        }
+    for (uint32_t k = tid; k < P; k += nth) atomicAdd(&bins[c.pcol[k] & (BUCKET_BINS - 1)], 1u);
+    __syncthreads();
+    // exclusive scan of the bins: BUCKET_BINS / nth consecutive bins per thread
+    constexpr int PER = BUCKET_BINS / BTPB;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        v[j] = bins[tid * PER + j];
+        sum += v[j];
     }
-    if (tid == 0)
-        for (uint32_t col = 0; col <= SFP_MAX_COLOURS; ++col) c.cnt->joint_col_off[col] = 0;
+    uint32_t total;
+    uint32_t ex = block_excl_scan(sum, &total, smem9);
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        bins[tid * PER + j] = ex;
+        ex += v[j];
+    }
+    __syncthreads();
+    for (uint32_t col = tid; col <= SFP_MAX_COLOURS; col += nth) {
+        c.cnt->pair_col_off[col] = (col < SFP_MAX_COLOURS) ? bins[col * 16] : P;
+        c.cnt->joint_col_off[col] = 0;
+    }
+    __syncthreads();
+    for (uint32_t k = tid; k < P; k += nth) {
+        uint32_t pos = atomicAdd(&bins[c.pcol[k] & (BUCKET_BINS - 1)], 1u);
+        c.pairs[pos] = c.pairs_raw[k];
+    }
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(BTPB) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
-                                                      float rest_threshold) {
+// Shared-memory layout of one world (bytes per body): pose 16 | vel 16 | X 16 | meta 16 |
+// minv 8 | mask 8 = 80.  X is time-shared: the AABBs during the broadphase, the two claim
+// arrays during colouring, the substep record `prev` during the substeps.  Everything the
+// solver gathers by body index therefore lives in this SM's shared memory; only the per-pair
+// contact records (read and written by the pair's own thread, coalesced) stay in global memory.
+template <bool SMEM>
+__global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
+                                                         float rest_threshold) {
+    extern __shared__ float4 dyn[];
     __shared__ uint32_t smem9[9];
     const uint32_t w = blockIdx.x;
     if (w >= b.n_worlds) return;
-    const Ctx c = world_view(b, w);
-    const uint32_t tid = threadIdx.x, nth = blockDim.x;
+    Ctx c = world_view(b, w);
+    const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
     uint32_t* cnt_off = b.scratch + (size_t)w * b.bpw;
+    float4 *g_pose = c.pose, *g_vel = c.vel;
+    long long t_prev = clock64();
+    unsigned long long cyc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#define LAP(slot)                          \
+    do {                                   \
+        long long t_now = clock64();       \
+        cyc[slot] += (unsigned long long)(t_now - t_prev); \
+        t_prev = t_now;                    \
+    } while (0)
+    if (SMEM) {
+        float4* s_pose = dyn;
+        float4* s_vel = dyn + n;
+        float4* s_x = dyn + 2 * (size_t)n;
+        int4* s_meta = reinterpret_cast<int4*>(dyn + 3 * (size_t)n);
+        float2* s_minv = reinterpret_cast<float2*>(dyn + 4 * (size_t)n);
+        unsigned long long* s_mask = reinterpret_cast<unsigned long long*>(s_minv + n);
+        for (uint32_t i = tid; i < n; i += nth) {
+            s_pose[i] = g_pose[i];
+            s_vel[i] = g_vel[i];
+            s_minv[i] = c.minv[i];
+        }
+        c.pose = s_pose;
+        c.vel = s_vel;
+        c.minv = s_minv;
+        c.aabb = s_x;
+        c.claim0 = reinterpret_cast<unsigned long long*>(s_x);
+        c.claim1 = reinterpret_cast<unsigned long long*>(s_x) + n;
+        c.prev = s_x;
+        c.meta = s_meta;
+        c.mask = s_mask;
+        __syncthreads();
+    }
+    LAP(0);
 
     batch_broadphase(c, cnt_off, dt, smem9);
+    LAP(1);
 
     // colouring: same rounds as stage_colour_* in the single-world path
     stage_colour_init(c, tid, nth);
@@ -199,26 +251,43 @@ __global__ void __launch_bounds__(BTPB) k_batch_frame(BatchCtx b, float dt, uint
     }
     if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
     __syncthreads();
+    LAP(2);
     batch_bucket(c, smem9);
+    LAP(3);
 
     const uint32_t ncol = c.cnt->n_colours;
     const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
         __syncthreads();
+        LAP(4);
         stage_narrowphase(c, tid, nth);
         __syncthreads();
+        LAP(5);
         for (uint32_t col = 0; col < ncol; ++col) {
             stage_solve_pos(c, col, inv_h2, tid, nth);
             __syncthreads();
         }
+        LAP(6);
         stage_derive(c, inv_h, tid, nth);
         __syncthreads();
+        LAP(7);
         for (uint32_t col = 0; col < ncol; ++col) {
             stage_solve_vel(c, col, h, rest_threshold, tid, nth);
             __syncthreads();
         }
+        LAP(8);
     }
+    if (SMEM) {
+        for (uint32_t i = tid; i < n; i += nth) {
+            g_pose[i] = c.pose[i];
+            g_vel[i] = c.vel[i];
+        }
+    }
+    LAP(0);
+    if (tid == 0)
+        for (int k = 0; k < 10; ++k) c.cnt->stage_cycles[k] = cyc[k];
+#undef LAP
 }
 
 }  // namespace
@@ -240,6 +309,7 @@ struct SfpBatch {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false, uploaded = false, stepped = false;
     uint32_t n_worlds = 0, bpw = 0, pair_cap = 0;
+    size_t smem_bytes = 0;  // 0: the world's bodies stay in global memory (too big for one SM)
     BatchCtx ctx;
     std::vector<void*> allocs;
     std::vector<sfp::f2> h_minv;
@@ -348,6 +418,15 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     b->ctx.bpw = bodies_per_world;
     b->ctx.pair_cap = b->pair_cap;
     b->ctx.n_worlds = n_worlds;
+    {
+        size_t need = (size_t)bodies_per_world * 80u;
+        if (need <= 200u * 1024u) {
+            if (cudaFuncSetAttribute(k_batch_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)need) != cudaSuccess)
+                return die(SFP_E_CUDA);
+            b->smem_bytes = need;
+        }
+    }
     *out = b;
     return SFP_OK;
 }
@@ -405,7 +484,12 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     const float h = dt / (float)substeps;
     const float g = sqrtf(b->p.gravity_x * b->p.gravity_x + b->p.gravity_y * b->p.gravity_y);
     BCU(cudaEventRecord(b->ev0, b->stream));
-    k_batch_frame<<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, 2.0f * g * h);
+    if (b->smem_bytes)
+        k_batch_frame<true><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps,
+                                                                           2.0f * g * h);
+    else
+        k_batch_frame<false><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps,
+                                                                 2.0f * g * h);
     BCU(cudaGetLastError());
     BCU(cudaEventRecord(b->ev1, b->stream));
     b->timed = true;
@@ -468,6 +552,18 @@ int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out) {
         }
     }
     return rc;
+}
+
+/* development aid (not part of include/sfp.h): SM-clock cycles per stage of world `w` */
+__attribute__((visibility("default"))) int32_t sfp_batch_debug_stage_cycles(SfpBatch* b, uint32_t w,
+                                                                          unsigned long long out[10]) {
+    if (!b || !out || w >= b->n_worlds) return SFP_E_INVALID;
+    BCU(cudaSetDevice(b->device));
+    BCU(cudaStreamSynchronize(b->stream));
+    Counters k;
+    BCU(cudaMemcpy(&k, b->ctx.counters + w, sizeof(k), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 10; ++i) out[i] = k.stage_cycles[i];
+    return SFP_OK;
 }
 
 const char* sfp_batch_last_error(SfpBatch* b) { return b ? b->err.c_str() : "null batch"; }

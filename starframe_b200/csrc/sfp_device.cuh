@@ -37,6 +37,10 @@ struct Counters {
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
     uint32_t round_flags[MAX_ROUNDS];
+    // SM-clock cycles spent per stage in the last frame, written by thread 0 (batched path:
+    // of each world's CTA): 0 load/store, 1 broadphase, 2 colouring, 3 bucketing, 4 integrate,
+    // 5 narrowphase, 6 position solve, 7 derive, 8 velocity solve
+    unsigned long long stage_cycles[10];
 };
 
 struct Ctx {
@@ -55,6 +59,7 @@ struct Ctx {
     unsigned long long *mask, *claim0, *claim1;
     uint32_t *pcol, *jcol;
     uint32_t *pcol_sorted, *pperm, *jcol_sorted, *jperm;
+    uint32_t *pkey_tmp, *pval_tmp;  // ping-pong buffers of the two-pass (type, colour) sort
     uint2* pairs;  // colour-sorted
     // joints: upload order (…_in) and colour-sorted
     const uint2* jbod_in;
@@ -250,8 +255,13 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
     for (uint32_t k = tid; k < P; k += nth)
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
-            c.pcol[k] = colour_take_one(c, claim, next_claim, p.x, p.y,
-                                        sfp::pair_priority(p.x, p.y), round);
+            uint32_t col = colour_take_one(c, claim, next_claim, p.x, p.y,
+                                           sfp::pair_priority(p.x, p.y), round);
+            // sort key: colour in the high bits, shape-type pair in the low 4 (narrowphase
+            // coherence inside a colour bucket)
+            if (col != UNCOLOURED)
+                col = (col << 4) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+            c.pcol[k] = col;
         }
     for (uint32_t k = tid; k < c.nj; k += nth)
         if (c.jcol[k] == UNCOLOURED) {
@@ -263,10 +273,11 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
 }
 
 // after the stable sort by colour: gather constraints into colour order, find colour bounds
+// (`shift` strips the sub-key below the colour)
 __device__ __forceinline__ void colour_bounds(const uint32_t* sorted_col, uint32_t n, uint32_t i,
-                                              uint32_t* off) {
-    uint32_t col = sorted_col[i];
-    int prev = (i == 0) ? -1 : (int)sorted_col[i - 1];
+                                              uint32_t* off, int shift) {
+    uint32_t col = sorted_col[i] >> shift;
+    int prev = (i == 0) ? -1 : (int)(sorted_col[i - 1] >> shift);
     for (int cc = prev + 1; cc <= (int)col; ++cc) off[cc] = i;
     if (i == n - 1)
         for (int cc = (int)col + 1; cc <= SFP_MAX_COLOURS; ++cc) off[cc] = n;
@@ -276,7 +287,7 @@ __device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_
     const uint32_t P = c.cnt->n_pairs;
     for (uint32_t i = tid; i < P; i += nth) {
         c.pairs[i] = c.pairs_raw[c.pperm[i]];
-        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off);
+        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off, 4);
     }
     if (P == 0 && tid == 0)
         for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->pair_col_off[cc] = 0;
@@ -285,7 +296,7 @@ __device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_
         c.jbod[i] = c.jbod_in[s];
         c.janc[i] = c.janc_in[s];
         c.jpar[i] = c.jpar_in[s];
-        colour_bounds(c.jcol_sorted, c.nj, i, c.cnt->joint_col_off);
+        colour_bounds(c.jcol_sorted, c.nj, i, c.cnt->joint_col_off, 0);
     }
     if (c.nj == 0 && tid == 0)
         for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->joint_col_off[cc] = 0;
@@ -323,12 +334,14 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
         sfp::ContactRec r = sfp::narrowphase(ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x),
                                              ld4(c.mat, p.x), ld4(c.pose, p.y), ld4(c.vel, p.y),
                                              ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin);
-        st4(c.ca, k, r.a);
-        st4(c.cb, k, r.b);
-        st4(c.cp0, k, r.p0);
-        st4(c.cp1, k, r.p1);
-        st4(c.cs, k, r.s);
         uint32_t cnt = sfp::f2u(r.b.y);
+        st4(c.cb, k, r.b);
+        if (cnt) {  // an empty manifold is fully described by count == 0
+            st4(c.ca, k, r.a);
+            st4(c.cp0, k, r.p0);
+            st4(c.cp1, k, r.p1);
+            st4(c.cs, k, r.s);
+        }
         npts += cnt;
         nman += cnt ? 1u : 0u;
         if (cnt > 0) maxpen = fmaxf(maxpen, -r.s.x);

@@ -211,6 +211,8 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.pcol, cp, bag));
     TRY(alloc_dev(w, &c.pcol_sorted, cp, bag));
     TRY(alloc_dev(w, &c.pperm, cp, bag));
+    TRY(alloc_dev(w, &c.pkey_tmp, cp, bag));
+    TRY(alloc_dev(w, &c.pval_tmp, cp, bag));
     TRY(alloc_dev(w, &c.ca, cp, bag));
     TRY(alloc_dev(w, &c.cb, cp, bag));
     TRY(alloc_dev(w, &c.cp0, cp, bag));
@@ -326,14 +328,17 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
             if (!flag) break;
         }
     }
-    CU(radix_pass(c.pcol, nullptr, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs, 0,
+    // stable LSD sort of the pairs by (colour, shape-type pair): key = colour << 4 | type, 10 bits
+    CU(radix_pass(c.pcol, nullptr, c.pkey_tmp, c.pval_tmp, &w->d_cnt->n_pairs, w->cap_pairs, 0,
                   w->d_hist, st));
+    CU(radix_pass(c.pkey_tmp, c.pval_tmp, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs,
+                  8, w->d_hist, st));
     if (w->nj)
         CU(radix_pass(c.jcol, nullptr, c.jcol_sorted, c.jperm, &w->d_cnt->n_joints, w->cap_joints,
                       0, w->d_hist, st));
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 4 + (w->nj ? 3 : 0);
+    w->launches += 7 + (w->nj ? 3 : 0);
     if (mark) CU(cudaEventRecord(w->ev_col, st));
     return SFP_OK;
 }
