@@ -117,21 +117,49 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
     }
 }
 
+// (cell, body) entries.  A body covering few cells writes them itself; a body covering many
+// (the floor of a pile covers thousands) is handed to its whole warp, 32 cells per step.
 __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, uint32_t nth) {
-    for (uint32_t i = tid; i < c.n; i += nth) {
-        f4 bb = ld4(c.aabb, i);
-        int4 m = c.meta[i];
-        int x0, y0, x1, y1;
-        sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1);
-        uint32_t o = c.cell_off[i];
-        for (int cy = m.y; cy <= y1; ++cy)
-            for (int cx = m.x; cx <= x1; ++cx) {
-                if (o < c.cap_entries) {
-                    c.ekey0[o] = sfp::cell_key(cx, cy);
-                    c.eval0[o] = i;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t base = tid - lane; base < c.n; base += nth) {
+        const uint32_t i = base + lane;
+        int x0 = 0, y0 = 0, x1 = -1, y1 = -1;
+        uint32_t o = 0, cnt = 0;
+        if (i < c.n) {
+            f4 bb = ld4(c.aabb, i);
+            sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1);
+            o = c.cell_off[i];
+            cnt = (uint32_t)(x1 - x0 + 1) * (uint32_t)(y1 - y0 + 1);
+        }
+        const bool big = cnt > 32u;
+        if (!big) {
+            for (int cy = y0; cy <= y1; ++cy)
+                for (int cx = x0; cx <= x1; ++cx) {
+                    if (o < c.cap_entries) {
+                        c.ekey0[o] = sfp::cell_key(cx, cy);
+                        c.eval0[o] = i;
+                    }
+                    ++o;
                 }
-                ++o;
+        }
+        uint32_t todo = __ballot_sync(0xffffffffu, big);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1u;
+            const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
+            const int bx1 = __shfl_sync(0xffffffffu, x1, src);
+            const uint32_t bo = __shfl_sync(0xffffffffu, o, src);
+            const uint32_t bcnt = __shfl_sync(0xffffffffu, cnt, src);
+            const uint32_t bi = base + (uint32_t)src;
+            const uint32_t w = (uint32_t)(bx1 - bx0 + 1);
+            for (uint32_t k = lane; k < bcnt; k += 32u) {
+                uint32_t pos = bo + k;
+                if (pos < c.cap_entries) {
+                    c.ekey0[pos] = sfp::cell_key(bx0 + (int)(k % w), by0 + (int)(k / w));
+                    c.eval0[pos] = bi;
+                }
             }
+        }
     }
     if (tid == 0 && c.cnt->n_entries > c.cap_entries) {
         c.cnt->n_entries = c.cap_entries;
@@ -383,38 +411,65 @@ __device__ __forceinline__ void store_pos(const Ctx& c, uint32_t i, const sfp::B
     }
 }
 
+// what the solver reads of one candidate pair
+struct PairRec {
+    uint2 p;
+    f4 ca, cb, q0, q1;
+};
+__device__ __forceinline__ PairRec load_pair_rec(const Ctx& c, uint32_t k) {
+    PairRec r;
+    r.p = c.pairs[k];
+    r.cb = ld4(c.cb, k);
+    r.ca = ld4(c.ca, k);
+    r.q0 = ld4(c.cp0, k);
+    r.q1 = ld4(c.cp1, k);
+    return r;
+}
+
+__device__ __forceinline__ void solve_pos_pair(const Ctx& c, uint32_t k, const PairRec& r) {
+    uint32_t cnt = sfp::f2u(r.cb.y);
+    f4 lam;
+    lam.x = lam.y = lam.z = lam.w = 0.0f;
+    if (cnt > 0) {
+        sfp::BodyPos A = load_pos(c, r.p.x), B = load_pos(c, r.p.y);
+        lam = sfp::solve_contact_manifold(&A, &B, sfp::mk(r.ca.x, r.ca.y), cnt,
+                                          sfp::mk(r.q0.x, r.q0.y), sfp::mk(r.q0.z, r.q0.w),
+                                          sfp::mk(r.q1.x, r.q1.y), sfp::mk(r.q1.z, r.q1.w), r.ca.z);
+        store_pos(c, r.p.x, A);
+        store_pos(c, r.p.y, B);
+    }
+    st4(c.lam, k, lam);
+}
+
+__device__ __forceinline__ void solve_pos_joint(const Ctx& c, uint32_t k, float inv_h2) {
+    uint2 jb = c.jbod[k];
+    float4 an = c.janc[k], pr = c.jpar[k];
+    sfp::BodyPos A = load_pos(c, jb.x), B = load_pos(c, jb.y);
+    sfp::solve_joint(&A, &B, sfp::mk(an.x, an.y), sfp::mk(an.z, an.w), pr.x, pr.y, sfp::f2u(pr.z),
+                     inv_h2);
+    store_pos(c, jb.x, A);
+    store_pos(c, jb.y, B);
+}
+
+// items of one colour: its joints first, then its pairs.  `skip_first`: the caller has
+// already handled item `tid` (from a prefetched record).
 __device__ __forceinline__ void stage_solve_pos(const Ctx& c, uint32_t colour, float inv_h2,
-                                                uint32_t tid, uint32_t nth) {
+                                                uint32_t tid, uint32_t nth, bool skip_first = false) {
     const uint32_t j0 = c.cnt->joint_col_off[colour], j1 = c.cnt->joint_col_off[colour + 1];
     const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
     const uint32_t nj = j1 - j0, total = nj + (p1 - p0);
-    for (uint32_t t = tid; t < total; t += nth) {
+    for (uint32_t t = skip_first ? tid + nth : tid; t < total; t += nth) {
         if (t < nj) {
-            uint32_t k = j0 + t;
-            uint2 jb = c.jbod[k];
-            float4 an = c.janc[k], pr = c.jpar[k];
-            sfp::BodyPos A = load_pos(c, jb.x), B = load_pos(c, jb.y);
-            sfp::solve_joint(&A, &B, sfp::mk(an.x, an.y), sfp::mk(an.z, an.w), pr.x, pr.y,
-                             sfp::f2u(pr.z), inv_h2);
-            store_pos(c, jb.x, A);
-            store_pos(c, jb.y, B);
+            solve_pos_joint(c, j0 + t, inv_h2);
         } else {
             uint32_t k = p0 + (t - nj);
+            // an empty manifold needs only its count
             f4 cb = ld4(c.cb, k);
-            uint32_t cnt = sfp::f2u(cb.y);
-            f4 lam;
-            lam.x = lam.y = lam.z = lam.w = 0.0f;
-            if (cnt > 0) {
-                uint2 p = c.pairs[k];
-                f4 ca = ld4(c.ca, k), q0 = ld4(c.cp0, k), q1 = ld4(c.cp1, k);
-                sfp::BodyPos A = load_pos(c, p.x), B = load_pos(c, p.y);
-                lam = sfp::solve_contact_manifold(&A, &B, sfp::mk(ca.x, ca.y), cnt,
-                                                  sfp::mk(q0.x, q0.y), sfp::mk(q0.z, q0.w),
-                                                  sfp::mk(q1.x, q1.y), sfp::mk(q1.z, q1.w), ca.z);
-                store_pos(c, p.x, A);
-                store_pos(c, p.y, B);
+            if (sfp::f2u(cb.y) == 0u) {
+                c.lam[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                continue;
             }
-            st4(c.lam, k, lam);
+            solve_pos_pair(c, k, load_pair_rec(c, k));
         }
     }
 }
@@ -430,34 +485,39 @@ __device__ __forceinline__ void stage_derive(const Ctx& c, float inv_h, uint32_t
     }
 }
 
+__device__ __forceinline__ void solve_vel_pair(const Ctx& c, uint32_t k, const PairRec& r, f4 lam,
+                                               float h, float rest_threshold) {
+    if (!(lam.x > 0.0f || lam.z > 0.0f)) return;
+    uint32_t cnt = sfp::f2u(r.cb.y);
+    f4 va = ld4(c.vel, r.p.x), vb = ld4(c.vel, r.p.y);
+    f4 pa = ld4(c.pose, r.p.x), pb = ld4(c.pose, r.p.y);
+    f2 ma = ld2(c.minv, r.p.x), mb = ld2(c.minv, r.p.y);
+    sfp::BodyVel A, B;
+    A.v = sfp::mk(va.x, va.y);
+    A.w = va.z;
+    A.im = ma.x;
+    A.ii = ma.y;
+    B.v = sfp::mk(vb.x, vb.y);
+    B.w = vb.z;
+    B.im = mb.x;
+    B.ii = mb.y;
+    sfp::solve_manifold_velocity(&A, &B, sfp::mk(pa.z, pa.w), sfp::mk(pb.z, pb.w),
+                                 sfp::mk(r.ca.x, r.ca.y), cnt, sfp::mk(r.q0.x, r.q0.y),
+                                 sfp::mk(r.q0.z, r.q0.w), sfp::mk(r.q1.x, r.q1.y),
+                                 sfp::mk(r.q1.z, r.q1.w), lam, r.cb.z, r.cb.w, r.ca.z, r.ca.w, r.cb.x,
+                                 h, rest_threshold);
+    if (ma.x > 0.0f || ma.y > 0.0f) c.vel[r.p.x] = make_float4(A.v.x, A.v.y, A.w, 0.0f);
+    if (mb.x > 0.0f || mb.y > 0.0f) c.vel[r.p.y] = make_float4(B.v.x, B.v.y, B.w, 0.0f);
+}
+
 __device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, float h,
-                                                float rest_threshold, uint32_t tid, uint32_t nth) {
+                                                float rest_threshold, uint32_t tid, uint32_t nth,
+                                                bool skip_first = false) {
     const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
-    for (uint32_t k = p0 + tid; k < p1; k += nth) {
+    for (uint32_t k = p0 + (skip_first ? tid + nth : tid); k < p1; k += nth) {
         f4 lam = ld4(c.lam, k);
         if (!(lam.x > 0.0f || lam.z > 0.0f)) continue;
-        f4 cb = ld4(c.cb, k), ca = ld4(c.ca, k);
-        uint32_t cnt = sfp::f2u(cb.y);
-        uint2 p = c.pairs[k];
-        f4 va = ld4(c.vel, p.x), vb = ld4(c.vel, p.y);
-        f4 pa = ld4(c.pose, p.x), pb = ld4(c.pose, p.y);
-        f2 ma = ld2(c.minv, p.x), mb = ld2(c.minv, p.y);
-        sfp::BodyVel A, B;
-        A.v = sfp::mk(va.x, va.y);
-        A.w = va.z;
-        A.im = ma.x;
-        A.ii = ma.y;
-        B.v = sfp::mk(vb.x, vb.y);
-        B.w = vb.z;
-        B.im = mb.x;
-        B.ii = mb.y;
-        v2 qa = sfp::mk(pa.z, pa.w), qb = sfp::mk(pb.z, pb.w), n = sfp::mk(ca.x, ca.y);
-        f4 q0 = ld4(c.cp0, k), q1 = ld4(c.cp1, k);
-        sfp::solve_manifold_velocity(&A, &B, qa, qb, n, cnt, sfp::mk(q0.x, q0.y),
-                                     sfp::mk(q0.z, q0.w), sfp::mk(q1.x, q1.y), sfp::mk(q1.z, q1.w),
-                                     lam, cb.z, cb.w, ca.z, ca.w, cb.x, h, rest_threshold);
-        if (ma.x > 0.0f || ma.y > 0.0f) c.vel[p.x] = make_float4(A.v.x, A.v.y, A.w, 0.0f);
-        if (mb.x > 0.0f || mb.y > 0.0f) c.vel[p.y] = make_float4(B.v.x, B.v.y, B.w, 0.0f);
+        solve_vel_pair(c, k, load_pair_rec(c, k), lam, h, rest_threshold);
     }
 }
 

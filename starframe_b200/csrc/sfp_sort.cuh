@@ -165,44 +165,51 @@ k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_p
     hist[threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
 }
 
-// one block: exclusive scan over the whole digit-major histogram (RADIX_BINS * n_blocks)
+// one block: exclusive scan over the digit-major histogram, restricted to the blocks that hold
+// live keys (the grid is sized for the buffer capacity, the live count is usually far smaller).
+// Warp w owns digits w, w+32, ...: it sums each of its rows, the 256 row sums are scanned by
+// warp 0, then every warp rewrites its rows as running offsets.
 static __global__ void __launch_bounds__(1024)
-k_radix_scan(uint32_t* __restrict__ hist, uint32_t count) {
-    __shared__ uint32_t sm[33];
-    __shared__ uint32_t carry_s;
+k_radix_scan(uint32_t* __restrict__ hist, uint32_t n_blocks, const uint32_t* __restrict__ n_ptr) {
+    __shared__ uint32_t row_base[RADIX_BINS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    for (uint32_t base = 0; base < count; base += 1024 * 4) {
-        // 4 consecutive elements per thread
-        uint32_t i0 = base + threadIdx.x * 4;
-        uint32_t v[4];
+    const uint32_t n = *n_ptr;
+    const uint32_t live = min(n_blocks, (n + RADIX_TILE - 1) / RADIX_TILE);
+    for (int d = warp; d < RADIX_BINS; d += 32) {
+        const uint32_t* row = hist + (size_t)d * n_blocks;
         uint32_t s = 0;
+        for (uint32_t b = lane; b < live; b += 32) s += row[b];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            v[k] = (i0 + k < count) ? hist[i0 + k] : 0u;
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) row_base[d] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        // exclusive scan of 256 row sums: 8 consecutive per lane
+        uint32_t v[8], s = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            v[k] = row_base[lane * 8 + k];
             s += v[k];
         }
-        uint32_t inc = warp_incl_scan(s, lane);
-        if (lane == 31) sm[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t w = sm[lane];
-            uint32_t winc = warp_incl_scan(w, lane);
-            sm[lane] = winc - w;
-            if (lane == 31) sm[32] = winc;
-        }
-        __syncthreads();
-        uint32_t ex = carry_s + sm[warp] + inc - s;
+        uint32_t ex = warp_incl_scan(s, lane) - s;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            if (i0 + k < count) hist[i0 + k] = ex;
+        for (int k = 0; k < 8; ++k) {
+            row_base[lane * 8 + k] = ex;
             ex += v[k];
         }
-        uint32_t chunk_total = sm[32];
-        __syncthreads();
-        if (threadIdx.x == 0) carry_s += chunk_total;
-        __syncthreads();
+    }
+    __syncthreads();
+    for (int d = warp; d < RADIX_BINS; d += 32) {
+        uint32_t* row = hist + (size_t)d * n_blocks;
+        uint32_t run = row_base[d];
+        for (uint32_t b0 = 0; b0 < live; b0 += 32) {
+            uint32_t b = b0 + lane;
+            uint32_t v = (b < live) ? row[b] : 0u;
+            uint32_t inc = warp_incl_scan(v, lane);
+            if (b < live) row[b] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
     }
 }
 
@@ -276,7 +283,7 @@ inline cudaError_t radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, 
                               uint32_t* hist, cudaStream_t st) {
     uint32_t nb = radix_blocks(cap);
     k_radix_hist<<<nb, RADIX_THREADS, 0, st>>>(keys_in, n_ptr, shift, hist);
-    k_radix_scan<<<1, 1024, 0, st>>>(hist, RADIX_BINS * nb);
+    k_radix_scan<<<1, 1024, 0, st>>>(hist, nb, n_ptr);
     k_radix_scatter<<<nb, RADIX_THREADS, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n_ptr,
                                                   shift, hist);
     return cudaGetLastError();

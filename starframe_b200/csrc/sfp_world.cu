@@ -86,27 +86,118 @@ __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
     if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
 }
 
+// Colours are split into a HEAD (big colours: one grid-wide phase each) and a TAIL (every colour
+// from `tail` on has at most TAIL_ITEMS constraints).  A tail colour is a handful of
+// constraints around the few high-degree bodies of the scene; a grid-wide phase for it costs
+// the same ~3-5 us as a phase with 50 000 constraints.  So the whole tail is run by block 0
+// alone, colours separated by __syncthreads(), inside ONE grid-wide phase.  The order of
+// constraints is unchanged (colour order), so results are too.
+constexpr uint32_t TAIL_ITEMS = 2 * TPB;
+
+__device__ __forceinline__ uint32_t colour_items(const Ctx& c, uint32_t col) {
+    return (c.cnt->pair_col_off[col + 1] - c.cnt->pair_col_off[col]) +
+           (c.cnt->joint_col_off[col + 1] - c.cnt->joint_col_off[col]);
+}
+
 __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t substeps,
                                                        float rest_threshold) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
     const uint32_t ncol = vload(&c.cnt->n_colours);
+    uint32_t tail = ncol;
+    while (tail > 0 && colour_items(c, tail - 1) <= TAIL_ITEMS) --tail;
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+
+    // Prefetch: the contact record of this thread's first item of the NEXT colour does not
+    // depend on anything the current phase writes, so it is loaded before the barrier and only
+    // the body gather remains on the critical path after it.
+    PairRec rec;
+    uint32_t rec_k = 0;
+    bool have = false;
+    auto prefetch_pos = [&](uint32_t col) {
+        have = false;
+        if (col >= tail) return;
+        if (c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return;
+        uint32_t k = c.cnt->pair_col_off[col] + tid;
+        if (k < c.cnt->pair_col_off[col + 1]) {
+            rec = load_pair_rec(c, k);
+            rec_k = k;
+            have = true;
+        }
+    };
+    f4 rec_lam;
+    auto prefetch_vel = [&](uint32_t col) {
+        have = false;
+        if (col >= tail) return;
+        uint32_t k = c.cnt->pair_col_off[col] + tid;
+        if (k < c.cnt->pair_col_off[col + 1]) {
+            rec_lam = ld4(c.lam, k);
+            rec = load_pair_rec(c, k);
+            rec_k = k;
+            have = true;
+        }
+    };
+
+    // per-stage wall time (ns, %globaltimer) seen by thread 0 — the phases are grid-wide, so
+    // one observer is representative
+    unsigned long long t_prev = 0, acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    auto lap = [&](int slot) {
+        if (tid == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (slot >= 0) acc[slot] += t - t_prev;
+            t_prev = t;
+        }
+    };
+    lap(-1);
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
         grid.sync();
+        lap(4);
         stage_narrowphase(c, tid, nth);
         grid.sync();
-        for (uint32_t col = 0; col < ncol; ++col) {
-            stage_solve_pos(c, col, inv_h2, tid, nth);
+        lap(5);
+        have = false;
+        for (uint32_t col = 0; col < tail; ++col) {
+            if (have) solve_pos_pair(c, rec_k, rec);
+            stage_solve_pos(c, col, inv_h2, tid, nth, have);
+            prefetch_pos(col + 1);
             grid.sync();
         }
+        lap(6);
+        if (tail < ncol) {
+            if (blockIdx.x == 0)
+                for (uint32_t col = tail; col < ncol; ++col) {
+                    stage_solve_pos(c, col, inv_h2, threadIdx.x, blockDim.x);
+                    __syncthreads();
+                }
+            grid.sync();
+        }
+        lap(9);
         stage_derive(c, inv_h, tid, nth);
         grid.sync();
-        for (uint32_t col = 0; col < ncol; ++col) {
-            stage_solve_vel(c, col, h, rest_threshold, tid, nth);
+        lap(7);
+        have = false;
+        for (uint32_t col = 0; col < tail; ++col) {
+            if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
+            stage_solve_vel(c, col, h, rest_threshold, tid, nth, have);
+            prefetch_vel(col + 1);
             grid.sync();
         }
+        lap(8);
+        if (tail < ncol) {
+            if (blockIdx.x == 0)
+                for (uint32_t col = tail; col < ncol; ++col) {
+                    stage_solve_vel(c, col, h, rest_threshold, threadIdx.x, blockDim.x);
+                    __syncthreads();
+                }
+            grid.sync();
+        }
+        lap(9);
+    }
+    if (tid == 0) {
+        for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
+        c.cnt->stage_cycles[0] = tail;
     }
 }
 
@@ -799,6 +890,17 @@ int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]) {
         CU(cudaEventElapsedTime(&out[2], w->ev_bp, w->ev_col));
         CU(cudaEventElapsedTime(&out[3], w->ev_col, w->ev1));
     }
+    return SFP_OK;
+}
+
+/* development aid (not part of include/sfp.h): ns per stage of the last substep kernel, as seen
+ * by thread 0: [4] integrate [5] narrowphase [6] head position colours [7] derive
+ * [8] head velocity colours [9] tail colours (both passes); [0] = index of the first tail colour */
+__attribute__((visibility("default"))) int32_t sfp_debug_stage_ns(SfpWorld* w, unsigned long long out[10]) {
+    if (!w || !out) return SFP_E_INVALID;
+    Counters k;
+    TRY(read_counters(w, &k));
+    for (int i = 0; i < 10; ++i) out[i] = k.stage_cycles[i];
     return SFP_OK;
 }
 
