@@ -947,6 +947,18 @@ SFP_HD void solve_manifold_velocity(BodyVel* A, BodyVel* B, v2 qa, v2 qb, v2 n, 
 #define SFP_MAX_COLOURS 64
 #define SFP_MAX_BODIES (1u << 22) /* body ids are packed into 22 bits of the priority key */
 #define SFP_NO_CLAIM 0xffffffffffffffffull
+/* Solve order inside a substep: the colours with more than SFP_TAIL_ITEMS constraints in
+ * ascending colour index, then the remaining (small) colours in ascending index.  (The CUDA
+ * path runs every small colour inside one grid-wide phase; fixing the order here keeps the
+ * oracle and the device on the same Gauss-Seidel sequence.) */
+#define SFP_TAIL_ITEMS 512u
+/* Colours are carried over from the previous frame for the pairs that persist; every
+ * SFP_RECOLOUR_PERIOD-th colouring starts from scratch so that stale high colours cannot pile
+ * up.  The count restarts at every body / joint upload. */
+#define SFP_RECOLOUR_PERIOD 32u
+/* previous-frame colour table: open-addressing hash of (a, b) -> colour, one u64 per slot:
+ * (colour + 1) << 44 | a << 22 | b;  0 = empty */
+#define SFP_CTAB_KEYMASK ((1ull << 44) - 1ull)
 
 SFP_HD uint32_t hash32(uint32_t x) {
     x ^= x >> 16;
@@ -967,6 +979,12 @@ SFP_HD uint64_t joint_priority(uint32_t j) {
     uint32_t h = hash32(j ^ 0x5bd1e995u);
     return ((uint64_t)(h >> 13) << 45) | (1ull << 44) | (uint64_t)j;
 }
+
+SFP_HD uint64_t ctab_key(uint32_t a, uint32_t b) { return ((uint64_t)a << 22) | (uint64_t)b; }
+SFP_HD uint64_t ctab_pack(uint32_t a, uint32_t b, uint32_t colour) {
+    return ((uint64_t)(colour + 1u) << 44) | ctab_key(a, b);
+}
+SFP_HD uint32_t ctab_hash(uint32_t a, uint32_t b) { return hash32(a * 0x9e3779b9u ^ hash32(b + 0x7f4a7c15u)); }
 
 /* index of the lowest zero bit of a 64-bit mask (64 if none) */
 SFP_HD int lowest_free(uint64_t mask) {

@@ -23,6 +23,7 @@
 #include <cstdint>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "sfp.h"
@@ -44,6 +45,10 @@ struct SfpWorld {
     std::vector<ContactRec> contacts;    /* aligned with pairs */
     std::vector<f4> lambdas;             /* aligned with pairs: ln0, lt0, ln1, lt1 */
     uint32_t n_colours = 0, colour_rounds = 0, n_entries = 0;
+    /* colours of the previous frame, for the warm start */
+    std::unordered_map<uint64_t, uint32_t> prev_pair_colour;
+    std::vector<uint32_t> prev_joint_colour;
+    uint32_t colour_age = 0; /* colourings since the last upload */
     SfpStats stats;
     std::string err;
     float last_ms = 0.0f;
@@ -149,7 +154,33 @@ int colour_constraints(SfpWorld& w) {
             --remaining;
             ncol = std::max(ncol, 1u);
         }
-    while (remaining > 0) {
+    /* warm start: a constraint that existed in the previous frame keeps its colour (those
+     * colours were proper among themselves and still are) */
+    const bool warm = (w.colour_age % SFP_RECOLOUR_PERIOD) != 0u;
+    w.colour_age += 1;
+    if (warm) {
+        auto keep = [&](uint32_t a, uint32_t b, uint32_t c, uint32_t* colour) {
+            if (is_dynamic(w, a)) mask[a] |= 1ull << c;
+            if (is_dynamic(w, b)) mask[b] |= 1ull << c;
+            *colour = c;
+            ncol = std::max(ncol, c + 1u);
+            --remaining;
+        };
+        for (uint32_t k = 0; k < P; ++k) {
+            auto it = w.prev_pair_colour.find(ctab_key(w.pairs[k].a, w.pairs[k].b));
+            if (it != w.prev_pair_colour.end())
+                keep(w.pairs[k].a, w.pairs[k].b, it->second, &w.pair_colour[k]);
+        }
+        if (w.prev_joint_colour.size() == J)
+            for (uint32_t k = 0; k < J; ++k)
+                if (w.joint_colour[k] == UNC && w.prev_joint_colour[k] != UNC)
+                    keep(w.joints[k].body_a, w.joints[k].body_b, w.prev_joint_colour[k],
+                         &w.joint_colour[k]);
+    }
+    /* at least one (possibly empty) round, like the device loop */
+    bool first = w.n > 0;
+    while (remaining > 0 || first) {
+        first = false;
         ++rounds;
         std::fill(claim.begin(), claim.end(), SFP_NO_CLAIM);
         auto bid = [&](uint32_t body, uint64_t key) {
@@ -190,6 +221,11 @@ int colour_constraints(SfpWorld& w) {
     }
     w.n_colours = ncol;
     w.colour_rounds = rounds;
+    w.prev_pair_colour.clear();
+    w.prev_pair_colour.reserve(P * 2);
+    for (uint32_t k = 0; k < P; ++k)
+        w.prev_pair_colour[ctab_key(w.pairs[k].a, w.pairs[k].b)] = w.pair_colour[k];
+    w.prev_joint_colour = w.joint_colour;
     if (overflow) {
         w.stats.overflow |= 4u;
         w.err = "more than 64 constraint colours needed";
@@ -301,12 +337,23 @@ void substep(SfpWorld& w, float h) {
     w.stats.n_contacts = npts;
     w.stats.n_manifolds = nman;
     w.stats.max_penetration = maxpen;
+    /* colour order: big colours first, then the small ones (see SFP_TAIL_ITEMS) */
+    std::vector<uint32_t> order;
+    if (w.p.solver_order != SFP_ORDER_REFERENCE) {
+        std::vector<uint32_t> items(w.n_colours, 0);
+        for (uint32_t k = 0; k < P; ++k) items[w.pair_colour[k]] += 1;
+        for (uint32_t k = 0; k < J; ++k) items[w.joint_colour[k]] += 1;
+        for (uint32_t c = 0; c < w.n_colours; ++c)
+            if (items[c] > SFP_TAIL_ITEMS) order.push_back(c);
+        for (uint32_t c = 0; c < w.n_colours; ++c)
+            if (items[c] <= SFP_TAIL_ITEMS) order.push_back(c);
+    }
     /* A5 + A6 */
     if (w.p.solver_order == SFP_ORDER_REFERENCE) {
         for (uint32_t k = 0; k < J; ++k) solve_joint_position(w, k, inv_h2);
         for (uint32_t k = 0; k < P; ++k) solve_pair_position(w, k);
     } else {
-        for (uint32_t c = 0; c < w.n_colours; ++c) {
+        for (uint32_t c : order) {
             for (uint32_t k = 0; k < J; ++k)
                 if (w.joint_colour[k] == c) solve_joint_position(w, k, inv_h2);
             for (uint32_t k = 0; k < P; ++k)
@@ -320,7 +367,7 @@ void substep(SfpWorld& w, float h) {
     if (w.p.solver_order == SFP_ORDER_REFERENCE) {
         for (uint32_t k = 0; k < P; ++k) solve_pair_velocity(w, k, h, rest_threshold);
     } else {
-        for (uint32_t c = 0; c < w.n_colours; ++c)
+        for (uint32_t c : order)
             for (uint32_t k = 0; k < P; ++k)
                 if (w.pair_colour[k] == c) solve_pair_velocity(w, k, h, rest_threshold);
     }
@@ -412,6 +459,9 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
     w->contacts.clear();
     w->lambdas.clear();
     w->pair_colour.clear();
+    w->prev_pair_colour.clear();
+    w->prev_joint_colour.clear();
+    w->colour_age = 0;
     w->stepped = false;
     return SFP_OK;
 }
@@ -426,6 +476,9 @@ int32_t sfp_ref_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n) 
         }
     w->joints.assign(joints, joints + n);
     w->joint_colour.clear();
+    w->prev_pair_colour.clear();
+    w->prev_joint_colour.clear();
+    w->colour_age = 0;
     w->stats.n_joints = n;
     return SFP_OK;
 }

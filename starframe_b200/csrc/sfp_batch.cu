@@ -43,6 +43,7 @@ struct BatchCtx {
     uint32_t n_worlds;
     Counters* counters;    // [n_worlds]
     uint32_t* scratch;     // [n_worlds][bpw] per-body pair counts / offsets
+    uint32_t tab_slots;    // colour-table slots per world (power of two)
 };
 
 __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
@@ -68,6 +69,8 @@ __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
     c.cp1 += po;
     c.cs += po;
     c.lam += po;
+    c.tab_old += (size_t)w * b.tab_slots;
+    c.tab_new += (size_t)w * b.tab_slots;
     c.cnt = b.counters + w;
     c.n = b.bpw;
     c.nj = 0;
@@ -240,7 +243,12 @@ __global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, u
 
     // colouring: same rounds as stage_colour_* in the single-world path
     stage_colour_init(c, tid, nth);
+    for (uint32_t k = tid; k <= c.tab_mask; k += nth) c.tab_new[k] = 0ull;
     __syncthreads();
+    if (c.warm) {
+        stage_colour_warm(c, tid, nth);
+        __syncthreads();
+    }
     uint32_t round = 0;
     for (; round < (uint32_t)MAX_ROUNDS; ++round) {
         stage_colour_bid(c, round, tid, nth);
@@ -250,12 +258,20 @@ __global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, u
         if (c.cnt->round_flags[round] == 0u) break;
     }
     if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+    stage_colour_record(c, tid, nth);
     __syncthreads();
     LAP(2);
     batch_bucket(c, smem9);
     LAP(3);
 
     const uint32_t ncol = c.cnt->n_colours;
+    // solve order: big colours ascending, then small colours ascending (SFP_TAIL_ITEMS)
+    const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
+    const unsigned long long big = big_colour_mask(c, ncol), small = all & ~big;
+    auto next_bit = [](unsigned long long m, int after) {
+        unsigned long long r = (after >= 63) ? 0ull : (m & (~0ull << (after + 1)));
+        return r ? (__ffsll((long long)r) - 1) : 64;
+    };
     const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
@@ -264,17 +280,23 @@ __global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, u
         stage_narrowphase(c, tid, nth);
         __syncthreads();
         LAP(5);
-        for (uint32_t col = 0; col < ncol; ++col) {
-            stage_solve_pos(c, col, inv_h2, tid, nth);
-            __syncthreads();
+        for (int pass = 0; pass < 2; ++pass) {
+            const unsigned long long m = pass ? small : big;
+            for (int col = next_bit(m, -1); col < 64; col = next_bit(m, col)) {
+                stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth);
+                __syncthreads();
+            }
         }
         LAP(6);
         stage_derive(c, inv_h, tid, nth);
         __syncthreads();
         LAP(7);
-        for (uint32_t col = 0; col < ncol; ++col) {
-            stage_solve_vel(c, col, h, rest_threshold, tid, nth);
-            __syncthreads();
+        for (int pass = 0; pass < 2; ++pass) {
+            const unsigned long long m = pass ? small : big;
+            for (int col = next_bit(m, -1); col < 64; col = next_bit(m, col)) {
+                stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth);
+                __syncthreads();
+            }
         }
         LAP(8);
     }
@@ -314,6 +336,8 @@ struct SfpBatch {
     std::vector<void*> allocs;
     std::vector<sfp::f2> h_minv;
     uint64_t frames = 0, body_substeps = 0;
+    unsigned long long* d_tab[2] = {nullptr, nullptr};
+    uint32_t colour_age = 0;
     uint32_t n_dynamic_total = 0;
     std::vector<uint32_t> n_dynamic;
     std::string err;
@@ -404,6 +428,12 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     A(c.lam, np);
     A(b->ctx.counters, n_worlds);
     A(b->ctx.scratch, nb);
+    uint32_t slots = 256;
+    while (slots < 2u * b->pair_cap) slots <<= 1;
+    A(b->d_tab[0], (size_t)n_worlds * slots);
+    A(b->d_tab[1], (size_t)n_worlds * slots);
+    b->ctx.tab_slots = slots;
+    c.tab_mask = slots - 1u;
 #undef A
     if (rc != SFP_OK) return die(rc);
     // joints are not part of the batched path: give the unused pointers a valid target
@@ -471,6 +501,7 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
     BCU(cudaMemcpy(const_cast<float2*>(c.minv), b->h_minv.data(), sizeof(sfp::f2) * nb,
                    cudaMemcpyHostToDevice));
     BCU(cudaMemset(b->ctx.counters, 0, sizeof(Counters) * b->n_worlds));
+    b->colour_age = 0;
     b->uploaded = true;
     b->stepped = false;
     return SFP_OK;
@@ -483,6 +514,10 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     BCU(cudaSetDevice(b->device));
     const float h = dt / (float)substeps;
     const float g = sqrtf(b->p.gravity_x * b->p.gravity_x + b->p.gravity_y * b->p.gravity_y);
+    b->ctx.base.warm = (b->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+    b->ctx.base.tab_old = b->d_tab[(b->colour_age + 1u) & 1u];
+    b->ctx.base.tab_new = b->d_tab[b->colour_age & 1u];
+    b->colour_age += 1;
     BCU(cudaEventRecord(b->ev0, b->stream));
     if (b->smem_bytes)
         k_batch_frame<true><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps,

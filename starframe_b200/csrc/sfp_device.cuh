@@ -60,6 +60,10 @@ struct Ctx {
     uint32_t *pcol, *jcol;
     uint32_t *pcol_sorted, *pperm, *jcol_sorted, *jperm;
     uint32_t *pkey_tmp, *pval_tmp;  // ping-pong buffers of the two-pass (type, colour) sort
+    // colour tables (sfp_math.h, SFP_CTAB_*): last frame's (read) and this frame's (built)
+    unsigned long long *tab_old, *tab_new;
+    uint32_t tab_mask;  // slots - 1 (power of two)
+    uint32_t warm;      // 1: carry colours over from tab_old / the previous jcol
     uint2* pairs;  // colour-sorted
     // joints: upload order (…_in) and colour-sorted
     const uint2* jbod_in;
@@ -222,10 +226,72 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
     for (uint32_t k = tid; k < c.nj; k += nth) {
         uint2 jb = c.jbod_in[k];
         bool dyn = (c.meta[jb.x].w | c.meta[jb.y].w) != 0;
-        c.jcol[k] = dyn ? UNCOLOURED : 0u;
-        if (!dyn) atomicMax(&c.cnt->n_colours, 1u);
+        if (!dyn) {
+            c.jcol[k] = 0u;
+            atomicMax(&c.cnt->n_colours, 1u);
+        } else if (!c.warm) {
+            c.jcol[k] = UNCOLOURED;
+        }
     }
     for (uint32_t k = tid; k < MAX_ROUNDS; k += nth) c.cnt->round_flags[k] = 0u;
+}
+
+// warm start: a constraint that existed in the previous frame keeps its colour.  Runs after
+// stage_colour_init (masks are zero), before the first round.
+__device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b, uint32_t col) {
+    if (c.meta[a].w) atomicOr(&c.mask[a], 1ull << col);
+    if (c.meta[b].w) atomicOr(&c.mask[b], 1ull << col);
+    atomicMax(&c.cnt->n_colours, col + 1u);
+}
+__device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, uint32_t nth) {
+    if (!c.warm) return;
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = tid; k < P; k += nth) {
+        uint2 p = c.pairs_raw[k];
+        const unsigned long long key = sfp::ctab_key(p.x, p.y);
+        uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
+        for (;;) {
+            unsigned long long slot = c.tab_old[h];
+            if (slot == 0ull) break;
+            if ((slot & SFP_CTAB_KEYMASK) == key) {
+                uint32_t col = (uint32_t)(slot >> 44) - 1u;
+                colour_keep(c, p.x, p.y, col);
+                c.pcol[k] = (col << 4) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+                break;
+            }
+            h = (h + 1u) & c.tab_mask;
+        }
+    }
+    for (uint32_t k = tid; k < c.nj; k += nth) {
+        uint32_t col = c.jcol[k];
+        uint2 jb = c.jbod_in[k];
+        if (col != UNCOLOURED && (c.meta[jb.x].w | c.meta[jb.y].w) != 0) colour_keep(c, jb.x, jb.y, col);
+    }
+}
+
+// record this frame's colours for the next one (tab_new was zeroed by the host / the caller)
+__device__ __forceinline__ void stage_colour_record(const Ctx& c, uint32_t tid, uint32_t nth) {
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = tid; k < P; k += nth) {
+        uint32_t key16 = c.pcol[k];
+        if (key16 == UNCOLOURED) continue;
+        uint2 p = c.pairs_raw[k];
+        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, key16 >> 4);
+        uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
+        while (atomicCAS(&c.tab_new[h], 0ull, packed) != 0ull) h = (h + 1u) & c.tab_mask;
+    }
+}
+
+// colours with more than SFP_TAIL_ITEMS constraints, as a bit mask (the solve order is: those
+// in ascending index, then the others in ascending index)
+__device__ __forceinline__ unsigned long long big_colour_mask(const Ctx& c, uint32_t ncol) {
+    unsigned long long m = 0ull;
+    for (uint32_t col = 0; col < ncol; ++col) {
+        uint32_t items = (c.cnt->pair_col_off[col + 1] - c.cnt->pair_col_off[col]) +
+                         (c.cnt->joint_col_off[col + 1] - c.cnt->joint_col_off[col]);
+        if (items > SFP_TAIL_ITEMS) m |= 1ull << col;
+    }
+    return m;
 }
 
 __device__ __forceinline__ void colour_bid_one(const Ctx& c, unsigned long long* claim, uint32_t a,

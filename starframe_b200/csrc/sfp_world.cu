@@ -48,6 +48,10 @@ __global__ void __launch_bounds__(TPB) k_pair_write(Ctx c) {
     stage_pairs<true>(c, c.ekey0, c.eval0, gtid(), gnth());
 }
 __global__ void __launch_bounds__(TPB) k_colour_init(Ctx c) { stage_colour_init(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_colour_warm(Ctx c) { stage_colour_warm(c, gtid(), gnth()); }
+__global__ void __launch_bounds__(TPB) k_colour_record(Ctx c) {
+    stage_colour_record(c, gtid(), gnth());
+}
 __global__ void __launch_bounds__(TPB) k_colour_bid(Ctx c, uint32_t round) {
     stage_colour_bid(c, round, gtid(), gnth());
 }
@@ -75,6 +79,10 @@ __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
     const uint32_t tid = gtid(), nth = gnth();
     stage_colour_init(c, tid, nth);
     grid.sync();
+    if (c.warm) {
+        stage_colour_warm(c, tid, nth);
+        grid.sync();
+    }
     uint32_t round = 0;
     for (; round < (uint32_t)MAX_ROUNDS; ++round) {
         stage_colour_bid(c, round, tid, nth);
@@ -84,19 +92,19 @@ __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
         if (vload(&c.cnt->round_flags[round]) == 0u) break;
     }
     if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+    stage_colour_record(c, tid, nth);
 }
 
-// Colours are split into a HEAD (big colours: one grid-wide phase each) and a TAIL (every colour
-// from `tail` on has at most TAIL_ITEMS constraints).  A tail colour is a handful of
-// constraints around the few high-degree bodies of the scene; a grid-wide phase for it costs
-// the same ~3-5 us as a phase with 50 000 constraints.  So the whole tail is run by block 0
-// alone, colours separated by __syncthreads(), inside ONE grid-wide phase.  The order of
-// constraints is unchanged (colour order), so results are too.
-constexpr uint32_t TAIL_ITEMS = 2 * TPB;
-
-__device__ __forceinline__ uint32_t colour_items(const Ctx& c, uint32_t col) {
-    return (c.cnt->pair_col_off[col + 1] - c.cnt->pair_col_off[col]) +
-           (c.cnt->joint_col_off[col + 1] - c.cnt->joint_col_off[col]);
+// Colours are split into BIG ones (more than SFP_TAIL_ITEMS constraints: one grid-wide phase
+// each) and SMALL ones.  A small colour is a handful of constraints around the few high-degree
+// bodies of the scene; a grid-wide phase for it costs the same ~3-4 us as a phase with 50 000
+// constraints.  So all small colours are run by block 0 alone, separated by __syncthreads(),
+// inside ONE grid-wide phase.  The solve order (big colours ascending, then small colours
+// ascending) is part of the algorithm's definition (sfp_math.h) and the oracle follows it.
+__device__ __forceinline__ int next_bit(unsigned long long m, int after) {
+    // lowest set bit of m with index > after (after = -1 for the first); 64 if none
+    unsigned long long r = (after >= 63) ? 0ull : (m & (~0ull << (after + 1)));
+    return r ? (__ffsll((long long)r) - 1) : 64;
 }
 
 __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t substeps,
@@ -104,19 +112,19 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
     const uint32_t ncol = vload(&c.cnt->n_colours);
-    uint32_t tail = ncol;
-    while (tail > 0 && colour_items(c, tail - 1) <= TAIL_ITEMS) --tail;
+    const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
+    const unsigned long long big = big_colour_mask(c, ncol), small = all & ~big;
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
 
-    // Prefetch: the contact record of this thread's first item of the NEXT colour does not
+    // Prefetch: the contact record of this thread's first item of the NEXT big colour does not
     // depend on anything the current phase writes, so it is loaded before the barrier and only
     // the body gather remains on the critical path after it.
     PairRec rec;
     uint32_t rec_k = 0;
     bool have = false;
-    auto prefetch_pos = [&](uint32_t col) {
+    auto prefetch_pos = [&](int col) {
         have = false;
-        if (col >= tail) return;
+        if (col >= 64) return;
         if (c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return;
         uint32_t k = c.cnt->pair_col_off[col] + tid;
         if (k < c.cnt->pair_col_off[col + 1]) {
@@ -126,9 +134,9 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
         }
     };
     f4 rec_lam;
-    auto prefetch_vel = [&](uint32_t col) {
+    auto prefetch_vel = [&](int col) {
         have = false;
-        if (col >= tail) return;
+        if (col >= 64) return;
         uint32_t k = c.cnt->pair_col_off[col] + tid;
         if (k < c.cnt->pair_col_off[col + 1]) {
             rec_lam = ld4(c.lam, k);
@@ -158,17 +166,17 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
         grid.sync();
         lap(5);
         have = false;
-        for (uint32_t col = 0; col < tail; ++col) {
+        for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_pos_pair(c, rec_k, rec);
-            stage_solve_pos(c, col, inv_h2, tid, nth, have);
-            prefetch_pos(col + 1);
+            stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth, have);
+            prefetch_pos(next_bit(big, col));
             grid.sync();
         }
         lap(6);
-        if (tail < ncol) {
+        if (small) {
             if (blockIdx.x == 0)
-                for (uint32_t col = tail; col < ncol; ++col) {
-                    stage_solve_pos(c, col, inv_h2, threadIdx.x, blockDim.x);
+                for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
+                    stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x);
                     __syncthreads();
                 }
             grid.sync();
@@ -178,17 +186,17 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
         grid.sync();
         lap(7);
         have = false;
-        for (uint32_t col = 0; col < tail; ++col) {
+        for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
-            stage_solve_vel(c, col, h, rest_threshold, tid, nth, have);
-            prefetch_vel(col + 1);
+            stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth, have);
+            prefetch_vel(next_bit(big, col));
             grid.sync();
         }
         lap(8);
-        if (tail < ncol) {
+        if (small) {
             if (blockIdx.x == 0)
-                for (uint32_t col = tail; col < ncol; ++col) {
-                    stage_solve_vel(c, col, h, rest_threshold, threadIdx.x, blockDim.x);
+                for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
+                    stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x);
                     __syncthreads();
                 }
             grid.sync();
@@ -197,7 +205,7 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
     }
     if (tid == 0) {
         for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
-        c.cnt->stage_cycles[0] = tail;
+        c.cnt->stage_cycles[0] = (unsigned long long)__popcll(big);
     }
 }
 
@@ -229,6 +237,9 @@ struct SfpWorld {
     std::vector<void*> body_allocs, joint_allocs;
     uint32_t *d_scan_tiles = nullptr, *d_hist = nullptr;
     uint32_t hist_blocks = 0;
+    unsigned long long* d_tab[2] = {nullptr, nullptr};
+    uint32_t tab_slots = 0;
+    uint32_t colour_age = 0;  // colourings since the last upload (warm start, sfp_math.h)
     Counters* d_cnt = nullptr;
     // host mirrors
     std::vector<sfp::f2> h_minv;
@@ -310,6 +321,12 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.cp1, cp, bag));
     TRY(alloc_dev(w, &c.cs, cp, bag));
     TRY(alloc_dev(w, &c.lam, cp, bag));
+    uint32_t slots = 1024;
+    while (slots < 2u * cp) slots <<= 1;
+    TRY(alloc_dev(w, &w->d_tab[0], slots, bag));
+    TRY(alloc_dev(w, &w->d_tab[1], slots, bag));
+    w->tab_slots = slots;
+    c.tab_mask = slots - 1u;
     w->cap_bodies = cb;
     w->cap_entries = ce;
     w->cap_pairs = cp;
@@ -399,6 +416,12 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     w->launches += 4 + 3 + 3 + 12;
     if (mark) CU(cudaEventRecord(w->ev_bp, st));
 
+    // warm start: read last frame's table, build this frame's in the other one
+    c.warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+    c.tab_old = w->d_tab[(w->colour_age + 1u) & 1u];
+    c.tab_new = w->d_tab[w->colour_age & 1u];
+    w->colour_age += 1;
+    CU(cudaMemsetAsync(c.tab_new, 0, sizeof(unsigned long long) * w->tab_slots, st));
     if (!multi) {
         uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_colour,
                                              blocks_for(w, 4ull * w->n + w->nj));
@@ -408,6 +431,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     } else {
         const uint32_t gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
         k_colour_init<<<gp, TPB, 0, st>>>(c);
+        if (c.warm) k_colour_warm<<<gp, TPB, 0, st>>>(c);
+        w->launches += 1 + c.warm;
         for (uint32_t round = 0; round < (uint32_t)MAX_ROUNDS; ++round) {
             k_colour_bid<<<gp, TPB, 0, st>>>(c, round);
             k_colour_take<<<gp, TPB, 0, st>>>(c, round);
@@ -418,6 +443,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
             CU(cudaStreamSynchronize(st));
             if (!flag) break;
         }
+        k_colour_record<<<gp, TPB, 0, st>>>(c);
+        w->launches += 1;
     }
     // stable LSD sort of the pairs by (colour, shape-type pair): key = colour << 4 | type, 10 bits
     CU(radix_pass(c.pcol, nullptr, c.pkey_tmp, c.pval_tmp, &w->d_cnt->n_pairs, w->cap_pairs, 0,
@@ -434,6 +461,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     return SFP_OK;
 }
 
+int read_counters(SfpWorld* w, Counters* out);
+
 int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
     Ctx& c = w->ctx;
     cudaStream_t st = w->stream;
@@ -447,18 +476,24 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
         w->launches += 1;
         return launch_coop(w, (const void*)k_substeps_coop, blocks, args);
     }
-    uint32_t ncol = 0;
-    CU(cudaMemcpyAsync(&ncol, &w->d_cnt->n_colours, sizeof(ncol), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    Counters k;
+    TRY(read_counters(w, &k));
+    const uint32_t ncol = k.n_colours;
+    std::vector<uint32_t> order;  // big colours, then small ones (SFP_TAIL_ITEMS)
+    for (int pass = 0; pass < 2; ++pass)
+        for (uint32_t col = 0; col < ncol; ++col) {
+            uint32_t items = (k.pair_col_off[col + 1] - k.pair_col_off[col]) +
+                             (k.joint_col_off[col + 1] - k.joint_col_off[col]);
+            if ((items > SFP_TAIL_ITEMS) == (pass == 0)) order.push_back(col);
+        }
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
     const uint32_t gb = blocks_for(w, w->n), gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
     for (uint32_t s = 0; s < substeps; ++s) {
         k_integrate<<<gb, TPB, 0, st>>>(c, h);
         k_narrowphase<<<gp, TPB, 0, st>>>(c);
-        for (uint32_t col = 0; col < ncol; ++col) k_solve_pos<<<gp, TPB, 0, st>>>(c, col, inv_h2);
+        for (uint32_t col : order) k_solve_pos<<<gp, TPB, 0, st>>>(c, col, inv_h2);
         k_derive<<<gb, TPB, 0, st>>>(c, inv_h);
-        for (uint32_t col = 0; col < ncol; ++col)
-            k_solve_vel<<<gp, TPB, 0, st>>>(c, col, h, rest_threshold);
+        for (uint32_t col : order) k_solve_vel<<<gp, TPB, 0, st>>>(c, col, h, rest_threshold);
         w->launches += 3 + 2 * ncol;
     }
     CU(cudaGetLastError());
@@ -640,6 +675,7 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     CU(cudaStreamSynchronize(st));  // the host vectors above die at return
     w->stats.n_bodies = n;
     w->stats.n_dynamic = ndyn;
+    w->colour_age = 0;
     w->stepped = false;
     return SFP_OK;
 }
@@ -677,6 +713,7 @@ int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
     CU(cudaMemcpyAsync(&w->d_cnt->n_joints, &nj, sizeof(nj), cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));
     w->stats.n_joints = nj;
+    w->colour_age = 0;
     return SFP_OK;
 }
 
