@@ -314,6 +314,19 @@ __global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, u
 
 }  // namespace
 
+// The dynamic shared-memory limit of k_batch_frame is a per-device property of the FUNCTION,
+// shared by every batch in the process: only ever raise it (a later, smaller batch must not
+// pull it below what an earlier, larger one launches with).
+static cudaError_t raise_batch_smem_limit(int device, size_t bytes) {
+    static size_t current[64] = {0};
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    if (bytes <= current[device]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(k_batch_frame<true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) current[device] = bytes;
+    return e;
+}
+
 #define BCU(call)                                                        \
     do {                                                                 \
         cudaError_t e_ = (call);                                         \
@@ -451,9 +464,7 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     {
         size_t need = (size_t)bodies_per_world * 80u;
         if (need <= 200u * 1024u) {
-            if (cudaFuncSetAttribute(k_batch_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)need) != cudaSuccess)
-                return die(SFP_E_CUDA);
+            if (raise_batch_smem_limit(b->device, need) != cudaSuccess) return die(SFP_E_CUDA);
             b->smem_bytes = need;
         }
     }

@@ -79,6 +79,20 @@ def test_batch_partition_is_world_index_independent(gpu_api):
         same(a[4 + k], b[k])
 
 
+def test_small_batch_created_after_a_large_one_does_not_break_it(gpu_api):
+    """the kernel's shared-memory limit is per function, not per batch: creating a batch of
+    small worlds must not lower it under a live batch of larger worlds"""
+    big = sf.Batch(gpu_api, 2, 512)
+    big.upload(scenes.worlds(2, 512))
+    big.step()
+    small = sf.Batch(gpu_api, 2, 32)
+    small.upload(scenes.worlds(2, 32))
+    small.step()
+    big.step()
+    big.sync()
+    small.sync()
+
+
 def test_batch_rejects_bad_arguments(gpu_api):
     with pytest.raises(sf.SfpError):
         sf.Batch(gpu_api, 0, 64)
