@@ -1,0 +1,138 @@
+// sfp.hpp — header-only C++ mirror of the reference's Physics / Body / Collider surface over the
+// C ABI of sfp.h.  The reference is compiled (Rust) code; its exact signatures are unavailable
+// (tree not mounted), so names and argument meaning follow BASELINE.json's
+// north_star vocabulary.  The Rust-side equivalent is sketched in INTEGRATION.md.
+//
+// Link against libsfp_b200.so (product) — or, in tests only, compile with -DSFP_USE_ORACLE and
+// link libsfp_ref.so to drive the CPU oracle through the same classes.
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "sfp.h"
+
+namespace starframe {
+
+#ifdef SFP_USE_ORACLE
+#define SFP_FN(name) sfp_ref_##name
+#else
+#define SFP_FN(name) sfp_##name
+#endif
+
+struct Material {
+    float static_friction = 0.5f, dynamic_friction = 0.3f, restitution = 0.0f;
+};
+
+struct Collider {
+    uint32_t shape = SFP_SHAPE_CIRCLE;
+    float hx = 0.0f, hy = 0.0f, radius = 0.5f;
+    Material material;
+    uint16_t layer = 1, mask = 0xffff;
+    static Collider new_circle(float r) { return {SFP_SHAPE_CIRCLE, 0.0f, 0.0f, r}; }
+    static Collider new_capsule(float length, float r) {
+        return {SFP_SHAPE_CAPSULE, 0.5f * length, 0.0f, r};
+    }
+    static Collider new_rect(float w, float h) { return {SFP_SHAPE_RECT, 0.5f * w, 0.5f * h, 0.0f}; }
+    static Collider new_rounded_rect(float w, float h, float r) {
+        return {SFP_SHAPE_RECT, 0.5f * w - r, 0.5f * h - r, r};
+    }
+    Collider with_material(Material m) const {
+        Collider c = *this;
+        c.material = m;
+        return c;
+    }
+};
+
+struct Body {
+    float x = 0.0f, y = 0.0f, angle = 0.0f, vx = 0.0f, vy = 0.0f, omega = 0.0f, density = 1.0f;
+    bool is_static = false;
+    static Body new_static(float x, float y, float angle = 0.0f) {
+        Body b;
+        b.x = x, b.y = y, b.angle = angle, b.is_static = true;
+        return b;
+    }
+    static Body new_dynamic(float x, float y, float angle = 0.0f, float density = 1.0f) {
+        Body b;
+        b.x = x, b.y = y, b.angle = angle, b.density = density;
+        return b;
+    }
+};
+
+class Physics {
+   public:
+    explicit Physics(float gx = 0.0f, float gy = -9.81f, uint32_t substeps = 8)
+        : substeps_(substeps) {
+        SfpParams p;
+        SFP_FN(default_params)(&p);
+        p.gravity_x = gx;
+        p.gravity_y = gy;
+        check(SFP_FN(create)(&p, &w_), "create");
+    }
+    ~Physics() { SFP_FN(destroy)(w_); }
+    Physics(const Physics&) = delete;
+    Physics& operator=(const Physics&) = delete;
+
+    uint32_t add_body(const Body& b, const Collider& c) {
+        SfpBodyDesc d{};
+        d.x = b.x, d.y = b.y, d.angle = b.angle, d.vx = b.vx, d.vy = b.vy, d.omega = b.omega;
+        d.hx = c.hx, d.hy = c.hy, d.radius = c.radius, d.shape = c.shape, d.density = b.density;
+        d.mu_s = c.material.static_friction, d.mu_d = c.material.dynamic_friction;
+        d.restitution = c.material.restitution;
+        d.category = c.layer, d.mask = c.mask, d.flags = b.is_static ? SFP_BODY_STATIC : 0u;
+        bodies_.push_back(d);
+        dirty_ = true;
+        return (uint32_t)bodies_.size() - 1u;
+    }
+    uint32_t add_distance_constraint(uint32_t a, uint32_t b, float rest, float compliance = 0.0f) {
+        return add_joint(a, b, rest, compliance, SFP_JOINT_DISTANCE);
+    }
+    uint32_t add_rope_constraint(uint32_t a, uint32_t b, float max_len, float compliance = 0.0f) {
+        return add_joint(a, b, max_len, compliance, SFP_JOINT_ROPE);
+    }
+    // the reference's per-frame step: frame dt, substep count
+    void tick(float dt = 1.0f / 60.0f) {
+        flush();
+        check(SFP_FN(step)(w_, dt, substeps_), "step");
+    }
+    std::vector<SfpBodyState> body_states() {
+        flush();
+        std::vector<SfpBodyState> out(bodies_.size());
+        check(SFP_FN(download_bodies)(w_, out.data(), (uint32_t)out.size()), "download_bodies");
+        return out;
+    }
+    SfpStats stats() {
+        SfpStats s;
+        check(SFP_FN(get_stats)(w_, &s), "get_stats");
+        return s;
+    }
+
+   private:
+    uint32_t add_joint(uint32_t a, uint32_t b, float rest, float compliance, uint32_t kind) {
+        SfpJointDesc j{};
+        j.body_a = a, j.body_b = b, j.rest = rest, j.compliance = compliance, j.kind = kind;
+        joints_.push_back(j);
+        dirty_ = true;
+        return (uint32_t)joints_.size() - 1u;
+    }
+    void flush() {
+        if (!dirty_) return;
+        check(SFP_FN(set_joints)(w_, nullptr, 0), "set_joints");
+        check(SFP_FN(upload_bodies)(w_, bodies_.data(), (uint32_t)bodies_.size()), "upload_bodies");
+        check(SFP_FN(set_joints)(w_, joints_.data(), (uint32_t)joints_.size()), "set_joints");
+        dirty_ = false;
+    }
+    void check(int32_t rc, const char* what) {
+        if (rc != SFP_OK)
+            throw std::runtime_error(std::string(what) + " failed (" + std::to_string(rc) +
+                                     "): " + (w_ ? SFP_FN(last_error)(w_) : ""));
+    }
+    SfpWorld* w_ = nullptr;
+    uint32_t substeps_;
+    std::vector<SfpBodyDesc> bodies_;
+    std::vector<SfpJointDesc> joints_;
+    bool dirty_ = true;
+};
+
+}  // namespace starframe
