@@ -224,6 +224,25 @@ SFP_API int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out);
 SFP_API int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out);
 SFP_API const char* sfp_batch_last_error(SfpBatch* b);
 
+/* ---- one small world without any allocation ------------------------------------------ */
+/* No counterpart in the reference (its step is CPU code and owns no device memory); added for
+ * hosts that must not allocate while they run — see the comment on the definition in
+ * starframe_b200/csrc/sfp_batch.cu for who they are and the rules that follow.
+ *
+ * Steps ONE world of n <= SFP_NOALLOC_MAX_BODIES bodies for `frames` frames of `substeps`
+ * substeps and writes the resulting states to out[0..n).  Calls no cudaMalloc / cudaFree /
+ * allocating routine, on the device or on the heap: every intermediate lives in a fixed
+ * SFP_NOALLOC_SCRATCH_BYTES device array that each GPU loading the library holds until exit.
+ * Result: bit-identical to sfp_batch_* on one world.  Worlds beyond the limits are refused with
+ * SFP_E_CAPACITY.  The first call on a device does a one-off set-up (make it before any stream
+ * capture); calls sharing a GPU must not overlap in time (they share the array); the call is
+ * synchronous.  err (optional, err_cap bytes) receives a message on failure. */
+#define SFP_NOALLOC_MAX_BODIES 1024u
+#define SFP_NOALLOC_SCRATCH_BYTES (2304u * 1024u)
+SFP_API int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodies,
+                                       uint32_t n, float dt, uint32_t substeps, uint32_t frames,
+                                       SfpBodyState* out, char* err, uint32_t err_cap);
+
 /* device-time of the last sfp_step / sfp_batch_step in milliseconds, measured with CUDA
  * events on the world's own stream (0 from the oracle) */
 SFP_API int32_t sfp_last_step_ms(SfpWorld* w, float* ms);

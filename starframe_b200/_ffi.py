@@ -94,7 +94,7 @@ PRODUCT_SYMBOLS = [
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
     "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
-    "last_step_breakdown_ms", "backend",
+    "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
@@ -166,6 +166,7 @@ class Api:
             "batch_download": [vp, vp],
             "batch_stats": [vp, vp],
             "batch_last_step_ms": [vp, C.POINTER(f32)],
+            "step_small_noalloc": [vp, vp, u32, f32, u32, u32, vp, C.c_char_p, u32],
         }
         for name, args in sig.items():
             if not self.has(name):
@@ -191,6 +192,21 @@ class Api:
         if rc != SFP_OK:
             raise SfpError(rc, "default_params")
         return p
+
+
+def step_small_noalloc(api: "Api", bodies: np.ndarray, frames: int = 1, dt: float = 1.0 / 60.0,
+                       substeps: int = 8, params: np.ndarray | None = None) -> np.ndarray:
+    """sfp_step_small_noalloc: one small world stepped inside the library's fixed scratch
+    array — for hosts that may not allocate device memory while running (include/sfp.h)."""
+    b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE)
+    out = np.zeros(b.shape[0], dtype=BODY_STATE_DTYPE)
+    err = C.create_string_buffer(512)
+    p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1)
+    rc = api.fn("step_small_noalloc")(_ptr(p), _ptr(b), b.shape[0], dt, substeps, frames,
+                                      _ptr(out), err, 512)
+    if rc != SFP_OK:
+        raise SfpError(rc, "step_small_noalloc", err.value.decode())
+    return out
 
 
 class World:

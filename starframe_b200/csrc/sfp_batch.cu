@@ -624,4 +624,229 @@ int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms) {
     return SFP_OK;
 }
 
+
+/* ------------------------------------------------------------------------------------------
+ * sfp_step_small_noalloc — one small world, stepped with NO allocation of any kind.
+ *
+ * Who needs this: host code that is not allowed to grow the device heap while it runs.  An
+ * engine that steps physics from its render / audio-paced frame thread cannot afford
+ * cudaMalloc or cudaFree there — both take the driver's allocator lock and wait for the whole
+ * device to go idle, so every other stream of the process (rendering interop copies, other
+ * worlds) stalls behind them — and an engine that carves up the GPU's memory once at start-up
+ * has no budget left for a library to allocate from later.  sfp_create / sfp_batch_create
+ * size their buffers with cudaMalloc; this entry point instead runs the same one-CTA-per-world
+ * frame kernel (k_batch_frame) with every intermediate buffer — AABBs, candidate pairs,
+ * colours, colour tables, contact records, counters — carved out of one fixed array that is
+ * part of the library image.
+ *
+ * The array: g_small_scratch below, SFP_NOALLOC_SCRATCH_BYTES (about 2.2 MiB) of device memory
+ * on every GPU that loads the library, held until the process exits.  It bounds the world size:
+ * n <= SFP_NOALLOC_MAX_BODIES (1024) and at most 12 n + 256 candidate pairs; larger requests are
+ * refused with SFP_E_CAPACITY and a message, nothing is truncated silently.
+ *
+ * In host code the array's name is only a stand-in for the symbol, not a device address, so the
+ * address is looked up with cudaGetSymbolAddress — once per device, with that device current,
+ * on the FIRST call that names the device (that first call also raises the kernel's dynamic
+ * shared-memory limit).  Make that first call before any stream capture begins.
+ *
+ * All calls on one GPU share the array and it keeps whatever the previous call left in it.
+ * What has to start from zero (the counters with their sticky overflow bits; the colour table
+ * is re-zeroed by the kernel itself every frame) is cleared at the start of each call; the
+ * rest is fully rewritten before it is read.  Two calls that overlap in time on the same GPU
+ * — from two threads, or two processes' worth of streams — would trample each other's
+ * intermediates: serialise them.  The call itself is synchronous (it returns after the
+ * result has been copied back) and uses the default stream.
+ *
+ * It performs: host-side conversion of `bodies` into a fixed host staging area, H2D copies into
+ * the array, `frames` launches of the frame kernel (the first one colours from scratch, the
+ * following ones carry colours over exactly like sfp_batch_step), D2H copy, conversion to `out`.
+ * The result is bit-identical to sfp_batch_create(1 world, n bodies) + sfp_batch_upload +
+ * `frames` x sfp_batch_step + sfp_batch_download.
+ * ------------------------------------------------------------------------------------------ */
+}  // extern "C"  (reopened below)
+
+namespace {
+
+constexpr uint32_t NA_MAX_BODIES = 1024;
+constexpr uint32_t NA_PAIR_CAP = 12u * NA_MAX_BODIES + 256u;
+constexpr uint32_t NA_TAB_SLOTS = 32768;  // power of two >= 2 * NA_PAIR_CAP
+static_assert(NA_TAB_SLOTS >= 2u * NA_PAIR_CAP, "colour table too small");
+
+constexpr size_t na_align(size_t x) { return (x + 255u) & ~(size_t)255u; }
+// layout of the scratch array (every region 256-byte aligned)
+constexpr size_t NA_OFF_POSE = 0;
+constexpr size_t NA_OFF_PREV = NA_OFF_POSE + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_VEL = NA_OFF_PREV + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_SHAPE = NA_OFF_VEL + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_MAT = NA_OFF_SHAPE + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_MINV = NA_OFF_MAT + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_AABB = NA_OFF_MINV + na_align(sizeof(float2) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_META = NA_OFF_AABB + na_align(sizeof(float4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_MASK = NA_OFF_META + na_align(sizeof(int4) * NA_MAX_BODIES);
+constexpr size_t NA_OFF_CLAIM0 = NA_OFF_MASK + na_align(8u * NA_MAX_BODIES);
+constexpr size_t NA_OFF_CLAIM1 = NA_OFF_CLAIM0 + na_align(8u * NA_MAX_BODIES);
+constexpr size_t NA_OFF_CNTOFF = NA_OFF_CLAIM1 + na_align(8u * NA_MAX_BODIES);
+constexpr size_t NA_OFF_PRAW = NA_OFF_CNTOFF + na_align(4u * NA_MAX_BODIES);
+constexpr size_t NA_OFF_PAIRS = NA_OFF_PRAW + na_align(sizeof(uint2) * NA_PAIR_CAP);
+constexpr size_t NA_OFF_PCOL = NA_OFF_PAIRS + na_align(sizeof(uint2) * NA_PAIR_CAP);
+constexpr size_t NA_OFF_CREC = NA_OFF_PCOL + na_align(4u * NA_PAIR_CAP);  // 6 float4 arrays
+constexpr size_t NA_CREC_STRIDE = na_align(sizeof(float4) * NA_PAIR_CAP);
+constexpr size_t NA_OFF_TAB0 = NA_OFF_CREC + 6u * NA_CREC_STRIDE;
+constexpr size_t NA_OFF_TAB1 = NA_OFF_TAB0 + na_align(8u * NA_TAB_SLOTS);
+constexpr size_t NA_OFF_CNT = NA_OFF_TAB1 + na_align(8u * NA_TAB_SLOTS);
+constexpr size_t NA_SCRATCH_BYTES = NA_OFF_CNT + na_align(sizeof(Counters));
+static_assert(NA_SCRATCH_BYTES <= (size_t)SFP_NOALLOC_SCRATCH_BYTES, "sfp.h states a smaller maximum");
+
+// the one fixed scratch area (see the comment above)
+static __device__ __align__(256) unsigned char g_small_scratch[SFP_NOALLOC_SCRATCH_BYTES];
+
+// per-device set-up state and the host staging area (fixed size: no heap)
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char* g_small_scratch_addr[NA_MAX_DEVICES];  // device address of g_small_scratch
+bool g_small_ready[NA_MAX_DEVICES];
+sfp::f4 na_h_pose[NA_MAX_BODIES], na_h_vel[NA_MAX_BODIES], na_h_shape[NA_MAX_BODIES],
+    na_h_mat[NA_MAX_BODIES];
+sfp::f2 na_h_minv[NA_MAX_BODIES];
+
+void na_msg(char* err, uint32_t cap, const char* what, const char* detail) {
+    if (err && cap) snprintf(err, cap, "%s%s%s", what, detail ? ": " : "", detail ? detail : "");
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodies, uint32_t n,
+                               float dt, uint32_t substeps, uint32_t frames, SfpBodyState* out,
+                               char* err, uint32_t err_cap) {
+    if (err && err_cap) err[0] = 0;
+    if (!bodies || !out || n == 0 || !(dt > 0.0f) || substeps == 0 || substeps > 1024 || frames == 0) {
+        na_msg(err, err_cap, "sfp_step_small_noalloc: invalid argument", nullptr);
+        return SFP_E_INVALID;
+    }
+    if (n > NA_MAX_BODIES) {
+        if (err && err_cap)
+            snprintf(err, err_cap,
+                     "sfp_step_small_noalloc: %u bodies requested, the fixed scratch area holds at "
+                     "most %u (and %u candidate pairs); use sfp_create / sfp_batch_create for "
+                     "larger worlds",
+                     n, NA_MAX_BODIES, NA_PAIR_CAP);
+        return SFP_E_CAPACITY;
+    }
+    SfpParams p;
+    if (params) p = *params;
+    else sfp::default_params(&p);
+    if (!sfp::params_valid(p) || p.solver_order != SFP_ORDER_COLOUR || p.device < 0 ||
+        p.device >= NA_MAX_DEVICES) {
+        na_msg(err, err_cap, "sfp_step_small_noalloc: invalid parameters", nullptr);
+        return SFP_E_INVALID;
+    }
+    for (uint32_t i = 0; i < n; ++i)
+        if (!sfp::desc_valid(bodies[i])) {
+            if (err && err_cap)
+                snprintf(err, err_cap, "sfp_step_small_noalloc: invalid body desc at index %u", i);
+            return SFP_E_INVALID;
+        }
+#define NCU(call)                                                   \
+    do {                                                            \
+        cudaError_t e_ = (call);                                    \
+        if (e_ != cudaSuccess) {                                    \
+            na_msg(err, err_cap, #call, cudaGetErrorString(e_));    \
+            return SFP_E_CUDA;                                      \
+        }                                                           \
+    } while (0)
+    NCU(cudaSetDevice(p.device));
+    if (!g_small_ready[p.device]) {
+        // once per device, with that device current: the symbol's address ON THIS DEVICE
+        unsigned char* ptr = nullptr;
+        NCU(cudaGetSymbolAddress((void**)&ptr, g_small_scratch));
+        NCU(raise_batch_smem_limit(p.device, (size_t)NA_MAX_BODIES * 80u));
+        g_small_scratch_addr[p.device] = ptr;
+        g_small_ready[p.device] = true;
+    }
+    unsigned char* base = g_small_scratch_addr[p.device];
+
+    BatchCtx ctx;
+    std::memset(&ctx, 0, sizeof(ctx));
+    Ctx& c = ctx.base;
+    c.pose = reinterpret_cast<float4*>(base + NA_OFF_POSE);
+    c.prev = reinterpret_cast<float4*>(base + NA_OFF_PREV);
+    c.vel = reinterpret_cast<float4*>(base + NA_OFF_VEL);
+    c.shape = reinterpret_cast<const float4*>(base + NA_OFF_SHAPE);
+    c.mat = reinterpret_cast<const float4*>(base + NA_OFF_MAT);
+    c.minv = reinterpret_cast<const float2*>(base + NA_OFF_MINV);
+    c.aabb = reinterpret_cast<float4*>(base + NA_OFF_AABB);
+    c.meta = reinterpret_cast<int4*>(base + NA_OFF_META);
+    c.mask = reinterpret_cast<unsigned long long*>(base + NA_OFF_MASK);
+    c.claim0 = reinterpret_cast<unsigned long long*>(base + NA_OFF_CLAIM0);
+    c.claim1 = reinterpret_cast<unsigned long long*>(base + NA_OFF_CLAIM1);
+    c.pairs_raw = reinterpret_cast<uint2*>(base + NA_OFF_PRAW);
+    c.pairs = reinterpret_cast<uint2*>(base + NA_OFF_PAIRS);
+    c.pcol = reinterpret_cast<uint32_t*>(base + NA_OFF_PCOL);
+    float4* crec = reinterpret_cast<float4*>(base + NA_OFF_CREC);
+    const size_t cstride = NA_CREC_STRIDE / sizeof(float4);
+    c.ca = crec;
+    c.cb = crec + cstride;
+    c.cp0 = crec + 2 * cstride;
+    c.cp1 = crec + 3 * cstride;
+    c.cs = crec + 4 * cstride;
+    c.lam = crec + 5 * cstride;
+    c.jbod_in = reinterpret_cast<const uint2*>(c.pairs_raw);
+    c.jcol = c.pcol;
+    c.tab_mask = NA_TAB_SLOTS - 1u;
+    c.gx = p.gravity_x;
+    c.gy = p.gravity_y;
+    c.inv_cell = 1.0f / p.cell_size;
+    c.aabb_margin = p.aabb_margin;
+    c.vel_expand = p.vel_expand;
+    c.contact_margin = p.contact_margin;
+    ctx.bpw = n;
+    ctx.pair_cap = NA_PAIR_CAP;
+    ctx.n_worlds = 1;
+    ctx.counters = reinterpret_cast<Counters*>(base + NA_OFF_CNT);
+    ctx.scratch = reinterpret_cast<uint32_t*>(base + NA_OFF_CNTOFF);
+    ctx.tab_slots = NA_TAB_SLOTS;
+    unsigned long long* tab[2] = {reinterpret_cast<unsigned long long*>(base + NA_OFF_TAB0),
+                                  reinterpret_cast<unsigned long long*>(base + NA_OFF_TAB1)};
+
+    for (uint32_t i = 0; i < n; ++i)
+        sfp::body_from_desc(bodies[i], &na_h_pose[i], &na_h_vel[i], &na_h_minv[i], &na_h_shape[i],
+                            &na_h_mat[i]);
+    NCU(cudaMemcpy(c.pose, na_h_pose, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
+    NCU(cudaMemcpy(c.vel, na_h_vel, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
+    NCU(cudaMemcpy(const_cast<float4*>(c.shape), na_h_shape, sizeof(sfp::f4) * n,
+                   cudaMemcpyHostToDevice));
+    NCU(cudaMemcpy(const_cast<float4*>(c.mat), na_h_mat, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
+    NCU(cudaMemcpy(const_cast<float2*>(c.minv), na_h_minv, sizeof(sfp::f2) * n,
+                   cudaMemcpyHostToDevice));
+    // the previous call's counters (sticky overflow bits, colour counts) must not leak in
+    NCU(cudaMemset(ctx.counters, 0, sizeof(Counters)));
+
+    const float h = dt / (float)substeps;
+    const float g = sqrtf(p.gravity_x * p.gravity_x + p.gravity_y * p.gravity_y);
+    for (uint32_t f = 0; f < frames; ++f) {
+        c.warm = (f % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+        c.tab_old = tab[(f + 1u) & 1u];
+        c.tab_new = tab[f & 1u];
+        k_batch_frame<true><<<1, BTPB, (size_t)n * 80u, 0>>>(ctx, dt, substeps, 2.0f * g * h);
+        NCU(cudaGetLastError());
+    }
+    NCU(cudaMemcpy(na_h_pose, c.pose, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost));
+    NCU(cudaMemcpy(na_h_vel, c.vel, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost));
+    Counters k;
+    NCU(cudaMemcpy(&k, ctx.counters, sizeof(k), cudaMemcpyDeviceToHost));
+#undef NCU
+    for (uint32_t i = 0; i < n; ++i) out[i] = sfp::state_from_records(na_h_pose[i], na_h_vel[i]);
+    if (k.overflow) {
+        if (err && err_cap)
+            snprintf(err, err_cap,
+                     "sfp_step_small_noalloc: capacity exceeded inside the fixed scratch area "
+                     "(bits %u: 2 = more than %u candidate pairs, 4 = more than 64 colours, "
+                     "16 = runaway body)",
+                     k.overflow, NA_PAIR_CAP);
+        return SFP_E_CAPACITY;
+    }
+    return SFP_OK;
+}
+
 }  // extern "C"
