@@ -184,39 +184,46 @@ SFP_HD bool layers_collide(uint32_t la, uint32_t lb) {
 #define SFP_LINEAR_SLOP 0.005f
 #define SFP_EPS 1.0e-9f
 
-template <int N>
+/* Convex core with 2 (capsule) or 4 (rectangle) vertices.  One runtime-sized type and ONE copy
+ * of each routine below serve every shape pair: per-(NA,NB) template instances made the
+ * narrowphase 84 KB of SASS, and the batched kernel (three CTAs per SM in different stages)
+ * spent most of its stall cycles waiting for instruction fetch.  Loops run to 4 with a
+ * `i < count` predicate so the vertex arrays stay in registers. */
 struct Poly {
-    v2 v[N]; /* CCW vertices, relative to the frame origin */
-    v2 n[N]; /* outward normal of edge v[i] -> v[(i+1)%N]  */
+    v2 v[4]; /* CCW vertices, relative to the frame origin */
+    v2 n[4]; /* outward normal of edge v[i] -> v[(i+1)%count]  */
+    int count;
     float r;
 };
 
-/* world-space core polygon of a collider, translated by -origin */
-SFP_HD Poly<2> make_poly2(v2 pos, v2 q, f4 shape, v2 origin) {
-    Poly<2> p;
-    v2 c = pos - origin;
-    v2 d = mk(q.x * shape.x, q.y * shape.x);
-    p.v[0] = c - d;
-    p.v[1] = c + d;
-    p.n[0] = mk(q.y, -q.x);
-    p.n[1] = mk(-q.y, q.x);
-    p.r = shape.z;
-    return p;
-}
-SFP_HD Poly<4> make_poly4(v2 pos, v2 q, f4 shape, v2 origin) {
-    Poly<4> p;
+/* world-space core polygon of a capsule / rectangle collider, translated by -origin */
+SFP_HD Poly make_poly(v2 pos, v2 q, f4 shape, v2 origin) {
+    Poly p;
     v2 c = pos - origin;
     v2 ax = mk(q.x * shape.x, q.y * shape.x);  /* R * (hx, 0) */
-    v2 ay = mk(-q.y * shape.y, q.x * shape.y); /* R * (0, hy) */
-    p.v[0] = (c - ax) - ay;
-    p.v[1] = (c + ax) - ay;
-    p.v[2] = (c + ax) + ay;
-    p.v[3] = (c - ax) + ay;
-    p.n[0] = mk(q.y, -q.x);
-    p.n[1] = mk(q.x, q.y);
-    p.n[2] = mk(-q.y, q.x);
-    p.n[3] = mk(-q.x, -q.y);
     p.r = shape.z;
+    if (shape_type(shape) == SHAPE_CAPSULE) {
+        p.count = 2;
+        p.v[0] = c - ax;
+        p.v[1] = c + ax;
+        p.v[2] = p.v[0];
+        p.v[3] = p.v[1];
+        p.n[0] = mk(q.y, -q.x);
+        p.n[1] = mk(-q.y, q.x);
+        p.n[2] = p.n[0];
+        p.n[3] = p.n[1];
+    } else {
+        v2 ay = mk(-q.y * shape.y, q.x * shape.y); /* R * (0, hy) */
+        p.count = 4;
+        p.v[0] = (c - ax) - ay;
+        p.v[1] = (c + ax) - ay;
+        p.v[2] = (c + ax) + ay;
+        p.v[3] = (c - ax) + ay;
+        p.n[0] = mk(q.y, -q.x);
+        p.n[1] = mk(q.x, q.y);
+        p.n[2] = mk(-q.y, q.x);
+        p.n[3] = mk(-q.x, -q.y);
+    }
     return p;
 }
 
@@ -255,31 +262,41 @@ SFP_HD Manifold collide_points(v2 ca, float ra, v2 cb, float rb, float margin) {
     return m;
 }
 
-/* polygon core P (N >= 2) vs point core c.  Normal returned points from P to the point. */
-template <int N>
-SFP_HD Manifold collide_poly_point(const Poly<N>& P, v2 c, float rc, float margin) {
+/* edge e of P: its two vertices and its normal (register-resident selection) */
+SFP_HD void poly_edge(const Poly& P, int e, v2* a, v2* b, v2* n) {
+    int e2 = (e + 1 == P.count) ? 0 : e + 1;
+    *a = P.v[0];
+    *b = P.v[0];
+    *n = P.n[0];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (i == e) {
+            *a = P.v[i];
+            *n = P.n[i];
+        }
+        if (i == e2) *b = P.v[i];
+    }
+}
+
+/* polygon core P vs point core c.  Normal returned points from P to the point. */
+SFP_HD Manifold collide_poly_point(const Poly& P, v2 c, float rc, float margin) {
     Manifold m = manifold_none();
     float best = -3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-        float s = dot(P.n[i], c - P.v[i]);
-        if (s > best) {
-            best = s;
-            bi = i;
+    for (int i = 0; i < 4; ++i) {
+        if (i < P.count) {
+            float s = dot(P.n[i], c - P.v[i]);
+            if (s > best) {
+                best = s;
+                bi = i;
+            }
         }
     }
     float rsum = P.r + rc;
     if (best - rsum >= margin) return m;
-    v2 v1 = P.v[0], v2_ = P.v[0], nf = P.n[0];
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-        if (i == bi) {
-            v1 = P.v[i];
-            v2_ = P.v[(i + 1) % N];
-            nf = P.n[i];
-        }
-    }
+    v2 v1, v2_, nf;
+    poly_edge(P, bi, &v1, &v2_, &nf);
     float u1 = dot(c - v1, v2_ - v1);
     float u2 = dot(c - v2_, v1 - v2_);
     v2 n = nf;
@@ -309,21 +326,24 @@ SFP_HD Manifold collide_poly_point(const Poly<N>& P, v2 c, float rc, float margi
 }
 
 /* max over edges of P1 of the min over vertices of P2 of the signed distance */
-template <int N1, int N2>
-SFP_HD float max_separation(const Poly<N1>& P1, const Poly<N2>& P2, int* edge) {
+SFP_HD float max_separation(const Poly& P1, const Poly& P2, int* edge) {
     float best = -3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < N1; ++i) {
-        float si = 3.0e38f;
+    for (int i = 0; i < 4; ++i) {
+        if (i < P1.count) {
+            float si = 3.0e38f;
 #pragma unroll
-        for (int j = 0; j < N2; ++j) {
-            float sij = dot(P1.n[i], P2.v[j] - P1.v[i]);
-            si = fminf(si, sij);
-        }
-        if (si > best) {
-            best = si;
-            bi = i;
+            for (int j = 0; j < 4; ++j) {
+                if (j < P2.count) {
+                    float sij = dot(P1.n[i], P2.v[j] - P1.v[i]);
+                    si = fminf(si, sij);
+                }
+            }
+            if (si > best) {
+                best = si;
+                bi = i;
+            }
         }
     }
     *edge = bi;
@@ -355,32 +375,18 @@ SFP_HD void segment_fractions(v2 p1, v2 q1, v2 p2, v2 q2, float* f1, float* f2) 
     *f2 = t;
 }
 
-template <int N>
-SFP_HD void poly_edge(const Poly<N>& P, int e, v2* a, v2* b, v2* n) {
-    *a = P.v[0];
-    *b = P.v[0];
-    *n = P.n[0];
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-        if (i == e) {
-            *a = P.v[i];
-            *b = P.v[(i + 1) % N];
-            *n = P.n[i];
-        }
-    }
-}
-
 /* edge of P whose normal is most anti-parallel to n */
-template <int N>
-SFP_HD int incident_edge(const Poly<N>& P, v2 n) {
+SFP_HD int incident_edge(const Poly& P, v2 n) {
     float best = 3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-        float d = dot(P.n[i], n);
-        if (d < best) {
-            best = d;
-            bi = i;
+    for (int i = 0; i < 4; ++i) {
+        if (i < P.count) {
+            float d = dot(P.n[i], n);
+            if (d < best) {
+                best = d;
+                bi = i;
+            }
         }
     }
     return bi;
@@ -390,12 +396,11 @@ SFP_HD int incident_edge(const Poly<N>& P, v2 n) {
  * the cores are disjoint and the closest features are two vertices the result is one point
  * with a vertex-vertex normal, otherwise the incident edge is clipped against the reference
  * face's side planes (1 or 2 points). */
-template <int NA, int NB>
-SFP_HD Manifold collide_polys(const Poly<NA>& A, const Poly<NB>& B, float margin) {
+SFP_HD Manifold collide_polys(const Poly& A, const Poly& B, float margin) {
     Manifold m = manifold_none();
     int ea = 0, eb = 0;
-    float sa = max_separation<NA, NB>(A, B, &ea);
-    float sb = max_separation<NB, NA>(B, A, &eb);
+    float sa = max_separation(A, B, &ea);
+    float sb = max_separation(B, A, &eb);
     float rsum = A.r + B.r;
     if (sa - rsum >= margin || sb - rsum >= margin) return m;
 
@@ -403,15 +408,15 @@ SFP_HD Manifold collide_polys(const Poly<NA>& A, const Poly<NB>& B, float margin
     v2 v11, v12, n1, v21, v22, n2;
     float r1, r2;
     if (flip) {
-        poly_edge<NB>(B, eb, &v11, &v12, &n1);
-        int ie = incident_edge<NA>(A, n1);
-        poly_edge<NA>(A, ie, &v21, &v22, &n2);
+        poly_edge(B, eb, &v11, &v12, &n1);
+        int ie = incident_edge(A, n1);
+        poly_edge(A, ie, &v21, &v22, &n2);
         r1 = B.r;
         r2 = A.r;
     } else {
-        poly_edge<NA>(A, ea, &v11, &v12, &n1);
-        int ie = incident_edge<NB>(B, n1);
-        poly_edge<NB>(B, ie, &v21, &v22, &n2);
+        poly_edge(A, ea, &v11, &v12, &n1);
+        int ie = incident_edge(B, n1);
+        poly_edge(B, ie, &v21, &v22, &n2);
         r1 = A.r;
         r2 = B.r;
     }
@@ -553,26 +558,17 @@ SFP_HD Manifold collide(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float marg
     uint32_t ta = shape_type(shape_a), tb = shape_type(shape_b);
     v2 cb = xb - xa;
     v2 zero = mk(0.0f, 0.0f);
-    if (ta == SHAPE_CIRCLE) {
-        if (tb == SHAPE_CIRCLE) return collide_points(zero, shape_a.z, cb, shape_b.z, margin);
-        if (tb == SHAPE_CAPSULE)
-            return manifold_flip(collide_poly_point<2>(make_poly2(xb, qb, shape_b, xa), zero,
-                                                       shape_a.z, margin));
-        return manifold_flip(
-            collide_poly_point<4>(make_poly4(xb, qb, shape_b, xa), zero, shape_a.z, margin));
+    if (ta == SHAPE_CIRCLE && tb == SHAPE_CIRCLE)
+        return collide_points(zero, shape_a.z, cb, shape_b.z, margin);
+    if (ta == SHAPE_CIRCLE || tb == SHAPE_CIRCLE) {
+        /* one call site: the polygon is whichever body is not the circle */
+        const bool a_round = ta == SHAPE_CIRCLE;
+        Poly P = make_poly(a_round ? xb : xa, a_round ? qb : qa, a_round ? shape_b : shape_a, xa);
+        Manifold m = collide_poly_point(P, a_round ? zero : cb, a_round ? shape_a.z : shape_b.z,
+                                        margin);
+        return a_round ? manifold_flip(m) : m;
     }
-    if (ta == SHAPE_CAPSULE) {
-        Poly<2> A = make_poly2(xa, qa, shape_a, xa);
-        if (tb == SHAPE_CIRCLE) return collide_poly_point<2>(A, cb, shape_b.z, margin);
-        if (tb == SHAPE_CAPSULE)
-            return collide_polys<2, 2>(A, make_poly2(xb, qb, shape_b, xa), margin);
-        return collide_polys<2, 4>(A, make_poly4(xb, qb, shape_b, xa), margin);
-    }
-    Poly<4> A = make_poly4(xa, qa, shape_a, xa);
-    if (tb == SHAPE_CIRCLE) return collide_poly_point<4>(A, cb, shape_b.z, margin);
-    if (tb == SHAPE_CAPSULE)
-        return collide_polys<4, 2>(A, make_poly2(xb, qb, shape_b, xa), margin);
-    return collide_polys<4, 4>(A, make_poly4(xb, qb, shape_b, xa), margin);
+    return collide_polys(make_poly(xa, qa, shape_a, xa), make_poly(xb, qb, shape_b, xa), margin);
 }
 
 /* ------------------------------------------------------------------------------------- */
