@@ -34,7 +34,10 @@ using namespace sfpk;
 
 namespace {
 
-constexpr int BTPB = 256;  // threads per world
+#ifndef SFP_BTPB
+#define SFP_BTPB 256
+#endif
+constexpr int BTPB = SFP_BTPB;  // threads per world
 
 struct BatchCtx {
     Ctx base;              // pointers to world 0's slabs; parameters
@@ -78,7 +81,7 @@ __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
     return c;
 }
 
-// all-pairs broadphase of one world: body a scans b > a.  count -> block scan -> write.
+// all-pairs broadphase of one world
 __device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint32_t* smem9) {
     const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
     for (uint32_t i = tid; i < n; i += nth) {
@@ -97,55 +100,46 @@ __device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint
     }
     __syncthreads();
     auto test = [&](uint32_t a, f4 bba, int4 ma, uint32_t b) {
+        (void)a;
+        if (!sfp::aabb_overlap(bba, ld4(c.aabb, b))) return false;  // rejects almost everything
         int4 mb = c.meta[b];
         if ((ma.w | mb.w) == 0) return false;
-        if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
-        return sfp::aabb_overlap(bba, ld4(c.aabb, b));
+        return sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z);
     };
-    // pass 1: counts per body (strided assignment balances the triangular loop)
-    for (uint32_t a = tid; a < n; a += nth) {
-        f4 bba = ld4(c.aabb, a);
-        int4 ma = c.meta[a];
-        uint32_t k = 0;
-        for (uint32_t b = a + 1; b < n; ++b) k += test(a, bba, ma, b) ? 1u : 0u;
-        cnt_off[a] = k;
+    // Single pass: body a scans b > a and appends its pairs through a shared-memory cursor
+    // (warp-aggregated integer atomics).  The ORDER of pairs_raw is therefore arbitrary, which
+    // changes no result: colouring depends on the pair set only.  Thread t takes bodies t and
+    // n-1-t, so every thread runs n-1 tests.
+    __shared__ uint32_t cursor;
+    if (tid == 0) cursor = 0;
+    __syncthreads();
+    const uint32_t half = (n + 1u) / 2u;
+    for (uint32_t t = tid; t < half; t += nth) {
+        for (int side = 0; side < 2; ++side) {
+            const uint32_t a = side ? (n - 1u - t) : t;
+            if (side && a == t) break;  // middle body of an odd count
+            f4 bba = ld4(c.aabb, a);
+            int4 ma = c.meta[a];
+            for (uint32_t b = a + 1; b < n; ++b) {
+                if (test(a, bba, ma, b)) {
+                    uint32_t pos = atomicAdd(&cursor, 1u);
+                    if (pos < c.cap_pairs) c.pairs_raw[pos] = make_uint2(a, b);
+                }
+            }
+        }
     }
     __syncthreads();
-    // exclusive scan over n counts by the block (n <= a few thousand): chunked
-    __shared__ uint32_t carry;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (uint32_t base = 0; base < n; base += nth) {
-        uint32_t i = base + tid;
-        uint32_t v = (i < n) ? cnt_off[i] : 0u;
-        uint32_t total;
-        uint32_t ex = block_excl_scan(v, &total, smem9);
-        uint32_t cbase = carry;
-        if (i < n) cnt_off[i] = cbase + ex;
-        __syncthreads();
-        if (tid == 0) carry = cbase + total;
-        __syncthreads();
-    }
     if (tid == 0) {
-        uint32_t P = carry;
+        uint32_t P = cursor;
         if (P > c.cap_pairs) {
             atomicOr(&c.cnt->overflow, 2u);
             P = c.cap_pairs;
         }
         c.cnt->n_pairs = P;
     }
-    // pass 2: write
-    for (uint32_t a = tid; a < n; a += nth) {
-        f4 bba = ld4(c.aabb, a);
-        int4 ma = c.meta[a];
-        uint32_t o = cnt_off[a];
-        for (uint32_t b = a + 1; b < n; ++b)
-            if (test(a, bba, ma, b)) {
-                if (o < c.cap_pairs) c.pairs_raw[o] = make_uint2(a, b);
-                ++o;
-            }
-    }
     __syncthreads();
+    (void)cnt_off;
+    (void)smem9;
 }
 
 // bucket pairs by (colour, shape-type pair): counting sort on the 10-bit key written by
@@ -194,8 +188,11 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
 // arrays during colouring, the substep record `prev` during the substeps.  Everything the
 // solver gathers by body index therefore lives in this SM's shared memory; only the per-pair
 // contact records (read and written by the pair's own thread, coalesced) stay in global memory.
+#ifndef SFP_BCTAS
+#define SFP_BCTAS 3
+#endif
 template <bool SMEM>
-__global__ void __launch_bounds__(BTPB, 3) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
+__global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
                                                          float rest_threshold) {
     extern __shared__ float4 dyn[];
     __shared__ uint32_t smem9[9];

@@ -21,7 +21,9 @@ from . import _ffi
 from ._ffi import (BODY_DESC_DTYPE, BODY_STATIC, JOINT_DESC_DTYPE, JOINT_DISTANCE, JOINT_ROPE,
                    SHAPE_CAPSULE, SHAPE_CIRCLE, SHAPE_RECT, Api, World)
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libsfp_b200.so")
+LIB_PATH = os.environ.get(
+    "SFP_B200_LIB",
+    os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libsfp_b200.so"))
 _api: Api | None = None
 
 
