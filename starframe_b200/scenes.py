@@ -146,18 +146,22 @@ def mixed_pile(n: int = 100_000, seed: int = BASE_SEED + 3, width: float | None 
     return np.concatenate([container(width, height, mu_s=0.6, mu_d=0.42, e=0.1), b]), no_joints()
 
 
-def ropes(n_ropes: int = 2000, links: int = 64, n_free: int = 20_000, seed: int = BASE_SEED + 4):
+def ropes(n_ropes: int = 2000, links: int = 64, n_free: int = 20_000, seed: int = BASE_SEED + 4,
+          rope_rows: int = 4):
     """Config 4: n_ropes chains of `links` particles (circle r=0.03, spacing 0.08) hanging from
-    static anchors on a grid, joined by distance constraints, plus free circles and a floor."""
+    static anchors (rope_rows tiers of anchors), joined by distance constraints, plus free
+    circles spawned in the gaps between the ropes over the whole height, and a floor.
+    (SURVEY.md §8d put the anchors on a 50 x 40 grid, i.e. 40 tiers = 230 m of height: the
+    free circles then arrive at 65 m/s.  4 tiers keep every speed below ~25 m/s.)"""
     spacing = 0.08
-    acols = max(1, int(round(np.sqrt(n_ropes * 1.25))))
-    arows = (n_ropes + acols - 1) // acols
+    arows = max(1, min(rope_rows, n_ropes))
+    acols = (n_ropes + arows - 1) // arows
     ax_pitch = 0.5
     rope_len = links * spacing
     row_pitch = rope_len + 0.6
     width = acols * ax_pitch + 2.0
     top = arows * row_pitch + 1.0
-    parts = [container(width, top + 2.0)]
+    parts = [container(width, top + 4.0)]
     n_static0 = 3
     # anchors: small static circles on a layer that collides with nothing
     anchors = empty_bodies(n_ropes)
@@ -181,14 +185,14 @@ def ropes(n_ropes: int = 2000, links: int = 64, n_free: int = 20_000, seed: int 
     lk["y"] = anchors["y"][rope_of] - (k + 1) * spacing
     lk["mu_s"], lk["mu_d"] = 0.4, 0.3
     parts.append(lk)
-    # free circles raining through the ropes
+    # free circles in the gaps between rope columns, spread over the height
     fr = empty_bodies(n_free)
-    fcols = max(1, int(width / 0.3))
     fi = np.arange(n_free)
+    frows = max(1, (n_free + acols - 1) // acols)
     fr["shape"] = SHAPE_CIRCLE
     fr["radius"] = uniform(seed, 2, n_free, 0.05, 0.10)
-    fr["x"] = (fi % fcols - 0.5 * (fcols - 1)) * 0.3 + uniform(seed, 3, n_free, -0.03, 0.03)
-    fr["y"] = top + 1.0 + (fi // fcols) * 0.3
+    fr["x"] = (fi % acols - 0.5 * (acols - 1)) * ax_pitch + 0.25 + uniform(seed, 3, n_free, -0.05, 0.05)
+    fr["y"] = 0.5 + (fi // acols) * ((top + 2.5) / frows) + uniform(seed, 4, n_free, 0.0, 0.02)
     parts.append(fr)
     bodies = np.concatenate(parts)
     link0 = n_static0 + n_ropes
