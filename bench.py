@@ -253,7 +253,7 @@ def run_worlds(args, rank, world_size):
     from starframe_b200 import scenes
 
     nw = args.worlds_per_gpu
-    bodies = scenes.worlds(nw, BODIES_PER_WORLD, first_world=rank * nw)
+    bodies = scenes.worlds(nw, BODIES_PER_WORLD, first_world=world_range(rank, nw).start)
     api = sf.product_api()
     b = sf.Batch(api, nw, BODIES_PER_WORLD, device=torch.cuda.current_device())
     b.upload(bodies)
@@ -411,13 +411,19 @@ def barrier(world_size):
         dist.barrier()
 
 
+def _reduce_device():
+    import torch.distributed as dist
+
+    return "cuda" if dist.get_backend() == "nccl" else "cpu"
+
+
 def allreduce_max(x, world_size):
     if world_size == 1:
         return x
     import torch
     import torch.distributed as dist
 
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    t = torch.tensor([x], dtype=torch.float64, device=_reduce_device())
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
@@ -428,9 +434,14 @@ def allreduce_sum(xs, world_size):
     import torch
     import torch.distributed as dist
 
-    t = torch.tensor(list(xs), dtype=torch.float64, device="cuda")
+    t = torch.tensor(list(xs), dtype=torch.float64, device=_reduce_device())
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return [float(v) for v in t.tolist()]
+
+
+def world_range(rank, worlds_per_rank):
+    """world indices owned by `rank`: contiguous block partition (no overlap, no gap)"""
+    return range(rank * worlds_per_rank, (rank + 1) * worlds_per_rank)
 
 
 def main():
