@@ -87,6 +87,16 @@ class ClockSampler:
                 "samples": len(self.rows)}
 
 
+def ncu_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel, from the committed ncu capture (or None)"""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(workload, {}).get("bytes_per_launch")
+    except Exception:
+        return None
+
+
 def b_alg(n, pairs, contacts, joints, substeps=SUBSTEPS, whole_step=True):
     """algorithmic bytes per body-substep (SURVEY.md §8d / BASELINE.md §3)"""
     p, c, j = pairs / n, contacts / n, joints / n
@@ -195,7 +205,7 @@ def run_single(args, rank, world_size):
         "roofline": {
             "bound": "hbm", "kernel": "k_substeps_coop (all 8 substeps of a frame, one launch)",
             "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "peak_source": peak_src, "traffic": None,
+            "peak_source": peak_src, "traffic": ncu_traffic(args.workload),
             "algorithmic_bytes_per_launch": bytes_sub,
             "note": "algorithmic bytes = (136 + 72 p + 344 c + 116 j) * N * S, SURVEY.md §8d; "
                     "the kernel is grid-sync latency bound, not bandwidth bound (DESIGN.md)",
@@ -306,7 +316,11 @@ def run_worlds(args, rank, world_size):
                    "collective": "statistics only (all_reduce of 3 floats after the timed region)"},
         "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one CTA per world, whole frame)",
                      "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                     "peak_source": peak_src, "traffic": None},
+                     "peak_source": peak_src, "traffic": ncu_traffic("worlds512"),
+                     "algorithmic_bytes_per_launch": bytes_step,
+                     "note": "traffic < algorithmic bytes: the per-substep re-reads the algorithmic "
+                             "count charges (bodies, pair lists) are served from shared memory / "
+                             "L2; what reaches DRAM is mostly the contact records written each substep"},
         "e2e": {"value": e2e_val, "unit": "body-substeps/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 32 * n, "call": "sfp_batch_step + sfp_batch_download"},
         "gpu_launches": args.steps, "clocks": clk.summary(),

@@ -113,36 +113,30 @@ inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4
     mat->w = u2f((uint32_t)d.category | ((uint32_t)d.mask << 16));
 }
 
+static_assert(sizeof(StateRec) == sizeof(SfpBodyState), "StateRec mirrors SfpBodyState");
+
 inline SfpBodyState state_from_records(f4 pose, f4 vel) {
+    StateRec r = state_pack(pose, vel);
     SfpBodyState s;
-    s.x = pose.x;
-    s.y = pose.y;
-    s.c = pose.z;
-    s.s = pose.w;
-    s.vx = vel.x;
-    s.vy = vel.y;
-    s.omega = vel.z;
-    s.angle = atan2f(pose.w, pose.z);
+    std::memcpy(&s, &r, sizeof(s));
     return s;
 }
 
-inline void records_from_state(const SfpBodyState& s, f2 minv, f4* pose, f4* vel) {
-    pose->x = s.x;
-    pose->y = s.y;
-    float n2 = s.c * s.c + s.s * s.s;
-    if (n2 > 0.0f) {
-        float inv = 1.0f / sqrtf(n2);
-        pose->z = s.c * inv;
-        pose->w = s.s * inv;
-    } else {
-        pose->z = cosf(s.angle);
-        pose->w = sinf(s.angle);
+/* a state whose rotor is (0, 0) carries its rotation in `angle` only: give it a rotor */
+inline SfpBodyState state_with_rotor(const SfpBodyState& in) {
+    SfpBodyState s = in;
+    if (!(s.c * s.c + s.s * s.s > 0.0f)) {
+        s.c = cosf(s.angle);
+        s.s = sinf(s.angle);
     }
-    bool is_static = !(minv.x > 0.0f || minv.y > 0.0f);
-    vel->x = is_static ? 0.0f : s.vx;
-    vel->y = is_static ? 0.0f : s.vy;
-    vel->z = is_static ? 0.0f : s.omega;
-    vel->w = 0.0f;
+    return s;
+}
+
+inline void records_from_state(const SfpBodyState& in, f2 minv, f4* pose, f4* vel) {
+    SfpBodyState s = state_with_rotor(in);
+    StateRec r;
+    std::memcpy(&r, &s, sizeof(r));
+    state_unpack(r, minv, pose, vel);
 }
 
 inline bool joint_valid(const SfpJointDesc& j, uint32_t n_bodies) {

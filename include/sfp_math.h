@@ -67,6 +67,39 @@ SFP_HD float rot_delta_tan(v2 q, v2 qp) {
     return sd / cd;
 }
 
+/* atan / atan2 from + - * / only (Cephes' atanf reduction and polynomial, |error| < 2e-7 rad):
+ * the library's and the device's atan2f differ in the last bits, and the angle reported to the
+ * scene graph must be the same number on both sides. */
+SFP_HD float atan_det(float x) {
+    float sign = 1.0f;
+    if (x < 0.0f) {
+        sign = -1.0f;
+        x = -x;
+    }
+    float y;
+    if (x > 2.414213562373095f) { /* tan(3 pi / 8) */
+        y = 1.5707963267948966f;
+        x = -(1.0f / x);
+    } else if (x > 0.4142135623730950f) { /* tan(pi / 8) */
+        y = 0.7853981633974483f;
+        x = (x - 1.0f) / (x + 1.0f);
+    } else {
+        y = 0.0f;
+    }
+    float z = x * x;
+    float p = (((8.05374449538e-2f * z - 1.38776856032e-1f) * z + 1.99777106478e-1f) * z -
+               3.33329491539e-1f) * z * x + x;
+    return sign * (y + p);
+}
+SFP_HD float atan2_det(float y, float x) {
+    const float pi = 3.14159265358979323846f;
+    if (x > 0.0f) return atan_det(y / x);
+    if (x < 0.0f) return (y >= 0.0f) ? atan_det(y / x) + pi : atan_det(y / x) - pi;
+    if (y > 0.0f) return 0.5f * pi;
+    if (y < 0.0f) return -0.5f * pi;
+    return 0.0f;
+}
+
 /* ------------------------------------------------------------------------------------- */
 /* State records (SoA: one array per record; SURVEY.md §8a A0, 88 B/body)                */
 /* ------------------------------------------------------------------------------------- */
@@ -105,6 +138,36 @@ SFP_HD float u2f(uint32_t u) {
 enum { SHAPE_CIRCLE = 0, SHAPE_CAPSULE = 1, SHAPE_RECT = 2 };
 
 SFP_HD uint32_t shape_type(f4 shape) { return f2u(shape.w) & 3u; }
+
+/* what the scene graph exchanges per body (layout of SfpBodyState in sfp.h) */
+struct StateRec {
+    float x, y, c, s, vx, vy, omega, angle;
+};
+SFP_HD StateRec state_pack(f4 pose, f4 vel) {
+    StateRec r;
+    r.x = pose.x;
+    r.y = pose.y;
+    r.c = pose.z;
+    r.s = pose.w;
+    r.vx = vel.x;
+    r.vy = vel.y;
+    r.omega = vel.z;
+    r.angle = atan2_det(pose.w, pose.z);
+    return r;
+}
+/* requires (c, s) != (0, 0); the host substitutes cos / sin of `angle` for a zero rotor */
+SFP_HD void state_unpack(StateRec r, f2 minv, f4* pose, f4* vel) {
+    pose->x = r.x;
+    pose->y = r.y;
+    float inv = 1.0f / sqrtf(r.c * r.c + r.s * r.s);
+    pose->z = r.c * inv;
+    pose->w = r.s * inv;
+    bool is_static = !(minv.x > 0.0f || minv.y > 0.0f);
+    vel->x = is_static ? 0.0f : r.vx;
+    vel->y = is_static ? 0.0f : r.vy;
+    vel->z = is_static ? 0.0f : r.omega;
+    vel->w = 0.0f;
+}
 
 /* ------------------------------------------------------------------------------------- */
 /* Broadphase arithmetic (A2)                                                            */

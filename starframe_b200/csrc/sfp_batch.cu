@@ -309,6 +309,22 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
 #undef LAP
 }
 
+__global__ void __launch_bounds__(256) k_batch_pack(const float4* __restrict__ pose,
+                                                    const float4* __restrict__ vel,
+                                                    sfp::StateRec* __restrict__ out, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x) {
+        float4 p = pose[i], v = vel[i];
+        f4 fp, fv;
+        fp.x = p.x, fp.y = p.y, fp.z = p.z, fp.w = p.w;
+        fv.x = v.x, fv.y = v.y, fv.z = v.z, fv.w = v.w;
+        sfp::StateRec r = sfp::state_pack(fp, fv);
+        float4* o = reinterpret_cast<float4*>(out + i);
+        o[0] = make_float4(r.x, r.y, r.c, r.s);
+        o[1] = make_float4(r.vx, r.vy, r.omega, r.angle);
+    }
+}
+
 }  // namespace
 
 // The dynamic shared-memory limit of k_batch_frame is a per-device property of the FUNCTION,
@@ -348,6 +364,9 @@ struct SfpBatch {
     uint64_t frames = 0, body_substeps = 0;
     unsigned long long* d_tab[2] = {nullptr, nullptr};
     uint32_t colour_age = 0;
+    sfp::StateRec* d_state = nullptr;   // device AoS staging for downloads
+    SfpBodyState* pin_state = nullptr;  // pinned host staging, pin_states entries
+    size_t pin_states = 0;
     uint32_t n_dynamic_total = 0;
     std::vector<uint32_t> n_dynamic;
     std::string err;
@@ -444,6 +463,10 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     A(b->d_tab[1], (size_t)n_worlds * slots);
     b->ctx.tab_slots = slots;
     c.tab_mask = slots - 1u;
+    A(b->d_state, nb);
+    b->pin_states = std::min<size_t>(nb, (size_t)2 << 20);  // <= 64 MiB pinned
+    if (rc == SFP_OK && cudaMallocHost(&b->pin_state, sizeof(SfpBodyState) * b->pin_states) != cudaSuccess)
+        rc = SFP_E_CUDA;
 #undef A
     if (rc != SFP_OK) return die(rc);
     // joints are not part of the batched path: give the unused pointers a valid target
@@ -474,6 +497,7 @@ int32_t sfp_batch_destroy(SfpBatch* b) {
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
     for (void* p : b->allocs) cudaFree(p);
+    if (b->pin_state) cudaFreeHost(b->pin_state);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
     if (b->stream) cudaStreamDestroy(b->stream);
@@ -555,11 +579,19 @@ int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out) {
     if (b->sticky != SFP_OK) return b->sticky;
     BCU(cudaSetDevice(b->device));
     const size_t nb = (size_t)b->n_worlds * b->bpw;
-    std::vector<sfp::f4> pose(nb), vel(nb);
-    BCU(cudaStreamSynchronize(b->stream));
-    BCU(cudaMemcpy(pose.data(), b->ctx.base.pose, sizeof(sfp::f4) * nb, cudaMemcpyDeviceToHost));
-    BCU(cudaMemcpy(vel.data(), b->ctx.base.vel, sizeof(sfp::f4) * nb, cudaMemcpyDeviceToHost));
-    for (size_t i = 0; i < nb; ++i) out[i] = sfp::state_from_records(pose[i], vel[i]);
+    // packed on the device into AoS states (incl. the angle), then one copy per 64 MiB chunk
+    // through the pinned staging buffer
+    k_batch_pack<<<(unsigned)std::min<size_t>((nb + 255) / 256, 148 * 8), 256, 0, b->stream>>>(
+        b->ctx.base.pose, b->ctx.base.vel, b->d_state, nb);
+    BCU(cudaGetLastError());
+    const size_t chunk = b->pin_states;
+    for (size_t o = 0; o < nb; o += chunk) {
+        size_t m = std::min(chunk, nb - o);
+        BCU(cudaMemcpyAsync(b->pin_state, b->d_state + o, sizeof(SfpBodyState) * m,
+                            cudaMemcpyDeviceToHost, b->stream));
+        BCU(cudaStreamSynchronize(b->stream));
+        std::memcpy(out + o, b->pin_state, sizeof(SfpBodyState) * m);
+    }
     return SFP_OK;
 }
 

@@ -73,6 +73,33 @@ __global__ void __launch_bounds__(TPB) k_solve_vel(Ctx c, uint32_t colour, float
     stage_solve_vel(c, colour, h, rt, gtid(), gnth());
 }
 
+// ---- scene-graph state <-> solver records, on the device (AoS SfpBodyState, 32 B/body) -------
+__global__ void __launch_bounds__(TPB) k_pack_states(const float4* __restrict__ pose,
+                                                     const float4* __restrict__ vel,
+                                                     sfp::StateRec* __restrict__ out, uint32_t n) {
+    for (uint32_t i = gtid(); i < n; i += gnth()) {
+        sfp::StateRec r = sfp::state_pack(ld4(pose, i), ld4(vel, i));
+        float4* o = reinterpret_cast<float4*>(out + i);
+        o[0] = make_float4(r.x, r.y, r.c, r.s);
+        o[1] = make_float4(r.vx, r.vy, r.omega, r.angle);
+    }
+}
+__global__ void __launch_bounds__(TPB) k_unpack_states(const sfp::StateRec* __restrict__ in,
+                                                       const float2* __restrict__ minv,
+                                                       float4* __restrict__ pose,
+                                                       float4* __restrict__ vel, uint32_t n) {
+    for (uint32_t i = gtid(); i < n; i += gnth()) {
+        const float4* q = reinterpret_cast<const float4*>(in + i);
+        float4 a = q[0], b = q[1];
+        sfp::StateRec r;
+        r.x = a.x, r.y = a.y, r.c = a.z, r.s = a.w, r.vx = b.x, r.vy = b.y, r.omega = b.z, r.angle = b.w;
+        f4 p, v;
+        sfp::state_unpack(r, ld2(minv, i), &p, &v);
+        st4(pose, i, p);
+        st4(vel, i, v);
+    }
+}
+
 // ---- persistent cooperative kernels (product path) ----------------------------------------
 __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
     cg::grid_group grid = cg::this_grid();
@@ -244,7 +271,8 @@ struct SfpWorld {
     // host mirrors
     std::vector<sfp::f2> h_minv;
     std::vector<sfp::f4> h_shape, h_mat;
-    sfp::f4 *pin_pose = nullptr, *pin_vel = nullptr;  // pinned staging, cap_bodies each
+    SfpBodyState* pin_state = nullptr;   // pinned host staging, cap_bodies states
+    sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
     uint32_t pin_cap = 0;
     int coop_max_colour = 0, coop_max_substep = 0, n_sm = 0;
     SfpStats stats;
@@ -336,11 +364,10 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     w->hist_blocks = radix_blocks(biggest);
     CU(cudaMalloc(&w->d_scan_tiles, sizeof(uint32_t) * (biggest / SCAN_TILE + 4)));
     CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * (size_t)w->hist_blocks));
-    if (w->pin_pose) cudaFreeHost(w->pin_pose);
-    if (w->pin_vel) cudaFreeHost(w->pin_vel);
-    w->pin_pose = w->pin_vel = nullptr;
-    CU(cudaMallocHost(&w->pin_pose, sizeof(sfp::f4) * cb));
-    CU(cudaMallocHost(&w->pin_vel, sizeof(sfp::f4) * cb));
+    if (w->pin_state) cudaFreeHost(w->pin_state);
+    w->pin_state = nullptr;
+    CU(cudaMallocHost(&w->pin_state, sizeof(SfpBodyState) * cb));
+    TRY(alloc_dev(w, &w->d_state, cb, bag));
     w->pin_cap = cb;
     return SFP_OK;
 }
@@ -613,8 +640,7 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
     if (w->d_hist) cudaFree(w->d_hist);
     if (w->d_cnt) cudaFree(w->d_cnt);
-    if (w->pin_pose) cudaFreeHost(w->pin_pose);
-    if (w->pin_vel) cudaFreeHost(w->pin_vel);
+    if (w->pin_state) cudaFreeHost(w->pin_state);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
     if (w->ev_bp) cudaEventDestroy(w->ev_bp);
@@ -747,14 +773,15 @@ int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
     if (n) {
-        CU(cudaMemcpyAsync(w->pin_pose, w->ctx.pose, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost,
-                           w->stream));
-        CU(cudaMemcpyAsync(w->pin_vel, w->ctx.vel, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost,
-                           w->stream));
+        // states are packed on the device (incl. the angle), one D2H copy, no per-body host work
+        k_pack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->ctx.pose, w->ctx.vel, w->d_state, n);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(w->pin_state, w->d_state, sizeof(SfpBodyState) * n,
+                           cudaMemcpyDeviceToHost, w->stream));
     }
     Counters k;
     TRY(read_counters(w, &k));
-    for (uint32_t i = 0; i < n; ++i) out[i] = sfp::state_from_records(w->pin_pose[i], w->pin_vel[i]);
+    if (n) std::memcpy(out, w->pin_state, sizeof(SfpBodyState) * n);
     return check_overflow(w, k);
 }
 
@@ -764,13 +791,16 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
     if (!(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
-    CU(cudaStreamSynchronize(w->stream));  // the staging buffers are reused
-    for (uint32_t i = 0; i < n; ++i)
-        sfp::records_from_state(in[i], w->h_minv[i], &w->pin_pose[i], &w->pin_vel[i]);
-    CU(cudaMemcpyAsync(w->ctx.pose, w->pin_pose, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice,
+    CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
+    std::memcpy(w->pin_state, in, sizeof(SfpBodyState) * n);
+    for (uint32_t i = 0; i < n; ++i)  // rare: a state that carries its rotation in `angle` only
+        if (!(in[i].c * in[i].c + in[i].s * in[i].s > 0.0f))
+            w->pin_state[i] = sfp::state_with_rotor(in[i]);
+    CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * n, cudaMemcpyHostToDevice,
                        w->stream));
-    CU(cudaMemcpyAsync(w->ctx.vel, w->pin_vel, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice,
-                       w->stream));
+    k_unpack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->d_state, w->ctx.minv, w->ctx.pose,
+                                                            w->ctx.vel, n);
+    CU(cudaGetLastError());
     TRY(sfp_step(w, dt, substeps));
     return sfp_download_bodies(w, out, n);
 }
