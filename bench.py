@@ -117,6 +117,8 @@ def make_scene(workload: str):
         return scenes.ropes()
     if workload == "stack100":
         return scenes.stack100()
+    if workload.startswith("shelves"):
+        return scenes.shelves(int(workload[7:] or 4_000_000))
     if workload.startswith("pile"):
         return scenes.mixed_pile(int(workload[4:]))
     raise SystemExit(f"unknown workload {workload}")

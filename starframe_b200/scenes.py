@@ -146,6 +146,33 @@ def mixed_pile(n: int = 100_000, seed: int = BASE_SEED + 3, width: float | None 
     return np.concatenate([container(width, height, mu_s=0.6, mu_d=0.42, e=0.1), b]), no_joints()
 
 
+def shelves(n: int = 4_000_000, levels: int = 64, rows: int = 32, seed: int = BASE_SEED + 6):
+    """Scale point beyond BASELINE.json's configs: n mixed bodies spread
+    over `levels` static floors stacked 24 m apart, `rows` spawn rows per floor, so the whole
+    scene stays within ~1.5 km of the origin (FP32 positions) while its state (n x 88 B plus
+    pair data) is several times the 126 MB L2 — the size at which HBM bandwidth, not phase
+    latency, bounds the step."""
+    per_level = (n + levels - 1) // levels
+    cols = (per_level + rows - 1) // rows
+    pitch, gap = 0.65, 24.0
+    width = cols * pitch + 0.6
+    parts = []
+    for lv in range(levels):
+        parts.append(static_rect(0.0, lv * gap - 0.25, 0.5 * width + 0.5, 0.25, mu_s=0.6, mu_d=0.42,
+                                 e=0.1))
+    parts.append(static_rect(-0.5 * width - 0.25, 0.5 * levels * gap, 0.25, 0.5 * levels * gap + 1.0))
+    parts.append(static_rect(0.5 * width + 0.25, 0.5 * levels * gap, 0.25, 0.5 * levels * gap + 1.0))
+    b, _ = mixed_pile(n, seed=seed, cols=cols, width=width)
+    b = b[3:]
+    i = np.arange(n)
+    lv = i // per_level
+    k = i % per_level
+    b["x"] = (k % cols - 0.5 * (cols - 1)) * pitch + uniform(seed, 20, n, -0.02, 0.02)
+    b["y"] = lv * gap + 0.35 + (k // cols) * pitch + uniform(seed, 21, n, 0.0, 0.02)
+    parts.append(b)
+    return np.concatenate(parts), no_joints()
+
+
 def ropes(n_ropes: int = 2000, links: int = 64, n_free: int = 20_000, seed: int = BASE_SEED + 4,
           rope_rows: int = 4):
     """Config 4: n_ropes chains of `links` particles (circle r=0.03, spacing 0.08) hanging from
