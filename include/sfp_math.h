@@ -1006,6 +1006,14 @@ SFP_HD void solve_manifold_velocity(BodyVel* A, BodyVel* B, v2 qa, v2 qb, v2 n, 
 #define SFP_MAX_COLOURS 64
 #define SFP_MAX_BODIES (1u << 22) /* body ids are packed into 22 bits of the priority key */
 #define SFP_NO_CLAIM 0xffffffffffffffffull
+/* Colours 0..62 are proper colours (a body's mask bit is set, no two constraints of a colour
+ * share a dynamic body).  A constraint that wins its bodies but finds all 63 taken — a body with
+ * more than 63 partners, e.g. a long dynamic plank carrying a crowd — joins the SERIAL group,
+ * "colour" 63: its members may share bodies, so they are solved one after another, after every
+ * proper colour, joints in upload order and then pairs in (a, b) order.  Slow but correct;
+ * at most SFP_SERIAL_MAX members (beyond that the step reports SFP_E_CAPACITY). */
+#define SFP_SERIAL_COLOUR 63
+#define SFP_SERIAL_MAX 1024u
 /* Solve order inside a substep: the colours with more than SFP_TAIL_ITEMS constraints in
  * ascending colour index, then the remaining (small) colours in ascending index.  (The CUDA
  * path runs every small colour inside one grid-wide phase; fixing the order here keeps the
@@ -1046,6 +1054,13 @@ SFP_HD uint64_t ctab_pack(uint32_t a, uint32_t b, uint32_t colour) {
 SFP_HD uint32_t ctab_hash(uint32_t a, uint32_t b) { return hash32(a * 0x9e3779b9u ^ hash32(b + 0x7f4a7c15u)); }
 
 /* index of the lowest zero bit of a 64-bit mask (64 if none) */
+SFP_HD int lowest_free(uint64_t mask);
+/* colour for a constraint whose dynamic bodies use the colours in `mask` */
+SFP_HD int pick_colour(uint64_t mask) {
+    int c = lowest_free(mask | (1ull << SFP_SERIAL_COLOUR));
+    return c >= SFP_SERIAL_COLOUR ? SFP_SERIAL_COLOUR : c;
+}
+
 SFP_HD int lowest_free(uint64_t mask) {
     uint64_t inv = ~mask;
     if (inv == 0ull) return 64;

@@ -145,7 +145,7 @@ int colour_constraints(SfpWorld& w) {
     std::vector<uint64_t> pkey(P), jkey(J);
     for (uint32_t k = 0; k < P; ++k) pkey[k] = pair_priority(w.pairs[k].a, w.pairs[k].b);
     for (uint32_t k = 0; k < J; ++k) jkey[k] = joint_priority(k);
-    uint32_t remaining = P + J, rounds = 0, ncol = 0;
+    uint32_t remaining = P + J, rounds = 0, ncol = 0, serial = 0;
     bool overflow = false;
     /* constraints without a dynamic end never conflict: colour 0 */
     for (uint32_t k = 0; k < J; ++k)
@@ -160,8 +160,12 @@ int colour_constraints(SfpWorld& w) {
     w.colour_age += 1;
     if (warm) {
         auto keep = [&](uint32_t a, uint32_t b, uint32_t c, uint32_t* colour) {
-            if (is_dynamic(w, a)) mask[a] |= 1ull << c;
-            if (is_dynamic(w, b)) mask[b] |= 1ull << c;
+            if (c != SFP_SERIAL_COLOUR) {
+                if (is_dynamic(w, a)) mask[a] |= 1ull << c;
+                if (is_dynamic(w, b)) mask[b] |= 1ull << c;
+            } else if (++serial > SFP_SERIAL_MAX) {
+                overflow = true;
+            }
             *colour = c;
             ncol = std::max(ncol, c + 1u);
             --remaining;
@@ -201,13 +205,13 @@ int colour_constraints(SfpWorld& w) {
             if (da && claim[a] != key) return;
             if (db && claim[b] != key) return;
             uint64_t m = (da ? mask[a] : 0ull) | (db ? mask[b] : 0ull);
-            int c = lowest_free(m);
-            if (c >= SFP_MAX_COLOURS) {
+            int c = pick_colour(m);
+            if (c != SFP_SERIAL_COLOUR) {
+                if (da) mask[a] |= 1ull << c;
+                if (db) mask[b] |= 1ull << c;
+            } else if (++serial > SFP_SERIAL_MAX) {
                 overflow = true;
-                c = SFP_MAX_COLOURS - 1;
             }
-            if (da) mask[a] |= 1ull << c;
-            if (db) mask[b] |= 1ull << c;
             *colour = (uint32_t)c;
             ncol = std::max(ncol, (uint32_t)c + 1u);
             --remaining;
@@ -228,7 +232,7 @@ int colour_constraints(SfpWorld& w) {
     w.prev_joint_colour = w.joint_colour;
     if (overflow) {
         w.stats.overflow |= 4u;
-        w.err = "more than 64 constraint colours needed";
+        w.err = "more than SFP_SERIAL_MAX constraints left without a colour";
         return SFP_E_CAPACITY;
     }
     return SFP_OK;
@@ -344,9 +348,10 @@ void substep(SfpWorld& w, float h) {
         for (uint32_t k = 0; k < P; ++k) items[w.pair_colour[k]] += 1;
         for (uint32_t k = 0; k < J; ++k) items[w.joint_colour[k]] += 1;
         for (uint32_t c = 0; c < w.n_colours; ++c)
-            if (items[c] > SFP_TAIL_ITEMS) order.push_back(c);
+            if (c != SFP_SERIAL_COLOUR && items[c] > SFP_TAIL_ITEMS) order.push_back(c);
         for (uint32_t c = 0; c < w.n_colours; ++c)
-            if (items[c] <= SFP_TAIL_ITEMS) order.push_back(c);
+            if (c != SFP_SERIAL_COLOUR && items[c] <= SFP_TAIL_ITEMS) order.push_back(c);
+        if (w.n_colours > SFP_SERIAL_COLOUR) order.push_back(SFP_SERIAL_COLOUR); /* serial, last */
     }
     /* A5 + A6 */
     if (w.p.solver_order == SFP_ORDER_REFERENCE) {

@@ -264,7 +264,11 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
     const uint32_t ncol = c.cnt->n_colours;
     // solve order: big colours ascending, then small colours ascending (SFP_TAIL_ITEMS)
     const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
-    const unsigned long long big = big_colour_mask(c, ncol), small = all & ~big;
+    const unsigned long long big = big_colour_mask(c, ncol);
+    const unsigned long long small = all & ~big & ~(1ull << SFP_SERIAL_COLOUR);
+    const bool serial = ncol > SFP_SERIAL_COLOUR;
+    if (serial) serial_sort_pairs(c, ncol);
+    __syncthreads();
     auto next_bit = [](unsigned long long m, int after) {
         unsigned long long r = (after >= 63) ? 0ull : (m & (~0ull << (after + 1)));
         return r ? (__ffsll((long long)r) - 1) : 64;
@@ -284,6 +288,10 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
                 __syncthreads();
             }
         }
+        if (serial) {
+            if (tid == 0) serial_solve_pos(c, ncol, inv_h2);
+            __syncthreads();
+        }
         LAP(6);
         stage_derive(c, inv_h, tid, nth);
         __syncthreads();
@@ -294,6 +302,10 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
                 stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth);
                 __syncthreads();
             }
+        }
+        if (serial) {
+            if (tid == 0) serial_solve_vel(c, ncol, h, rest_threshold);
+            __syncthreads();
         }
         LAP(8);
     }
@@ -870,7 +882,7 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
         if (err && err_cap)
             snprintf(err, err_cap,
                      "sfp_step_small_noalloc: capacity exceeded inside the fixed scratch area "
-                     "(bits %u: 2 = more than %u candidate pairs, 4 = more than 64 colours, "
+                     "(bits %u: 2 = more than %u candidate pairs, 4 = serial group too large, "
                      "16 = runaway body)",
                      k.overflow, NA_PAIR_CAP);
         return SFP_E_CAPACITY;

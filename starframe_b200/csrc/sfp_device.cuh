@@ -239,8 +239,10 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
 // warm start: a constraint that existed in the previous frame keeps its colour.  Runs after
 // stage_colour_init (masks are zero), before the first round.
 __device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b, uint32_t col) {
-    if (c.meta[a].w) atomicOr(&c.mask[a], 1ull << col);
-    if (c.meta[b].w) atomicOr(&c.mask[b], 1ull << col);
+    if (col != SFP_SERIAL_COLOUR) {
+        if (c.meta[a].w) atomicOr(&c.mask[a], 1ull << col);
+        if (c.meta[b].w) atomicOr(&c.mask[b], 1ull << col);
+    }
     atomicMax(&c.cnt->n_colours, col + 1u);
 }
 __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, uint32_t nth) {
@@ -289,9 +291,38 @@ __device__ __forceinline__ unsigned long long big_colour_mask(const Ctx& c, uint
     for (uint32_t col = 0; col < ncol; ++col) {
         uint32_t items = (c.cnt->pair_col_off[col + 1] - c.cnt->pair_col_off[col]) +
                          (c.cnt->joint_col_off[col + 1] - c.cnt->joint_col_off[col]);
-        if (items > SFP_TAIL_ITEMS) m |= 1ull << col;
+        if (items > SFP_TAIL_ITEMS && col != SFP_SERIAL_COLOUR) m |= 1ull << col;
     }
     return m;
+}
+
+// ---- the serial group ("colour" 63, sfp_math.h): members may share bodies ----------------------
+__device__ __forceinline__ uint32_t serial_pairs(const Ctx& c, uint32_t ncol, uint32_t* first) {
+    if (ncol <= SFP_SERIAL_COLOUR) return 0u;
+    *first = c.cnt->pair_col_off[SFP_SERIAL_COLOUR];
+    return c.cnt->pair_col_off[SFP_SERIAL_COLOUR + 1] - *first;
+}
+// the serial group's position / velocity pass, executed by ONE thread
+__device__ __forceinline__ void serial_solve_pos(const Ctx& c, uint32_t ncol, float inv_h2);
+__device__ __forceinline__ void serial_solve_vel(const Ctx& c, uint32_t ncol, float h,
+                                                 float rest_threshold);
+// put the serial pairs into (a, b) order: odd-even transposition by ONE block (call with the
+// block's threadIdx / blockDim; every thread of the block must call it).  Runs once per frame.
+__device__ __forceinline__ void serial_sort_pairs(const Ctx& c, uint32_t ncol) {
+    uint32_t first = 0;
+    const uint32_t m = serial_pairs(c, ncol, &first);
+    if (m > SFP_SERIAL_MAX && threadIdx.x == 0) atomicOr(&c.cnt->overflow, 4u);
+    if (m < 2u) return;
+    for (uint32_t round = 0; round < m; ++round) {
+        for (uint32_t i = 2u * threadIdx.x + (round & 1u); i + 1u < m; i += 2u * blockDim.x) {
+            uint2 x = c.pairs[first + i], y = c.pairs[first + i + 1u];
+            if (x.x > y.x || (x.x == y.x && x.y > y.y)) {
+                c.pairs[first + i] = y;
+                c.pairs[first + i + 1u] = x;
+            }
+        }
+        __syncthreads();
+    }
 }
 
 __device__ __forceinline__ void colour_bid_one(const Ctx& c, unsigned long long* claim, uint32_t a,
@@ -330,13 +361,11 @@ __device__ __forceinline__ uint32_t colour_take_one(const Ctx& c, const unsigned
         return UNCOLOURED;
     }
     unsigned long long m = (da ? c.mask[a] : 0ull) | (db ? c.mask[b] : 0ull);
-    int col = sfp::lowest_free(m);
-    if (col >= SFP_MAX_COLOURS) {
-        col = SFP_MAX_COLOURS - 1;
-        atomicOr(&c.cnt->overflow, 4u);
+    int col = sfp::pick_colour(m);
+    if (col != SFP_SERIAL_COLOUR) {
+        if (da) c.mask[a] |= 1ull << col;
+        if (db) c.mask[b] |= 1ull << col;
     }
-    if (da) c.mask[a] |= 1ull << col;
-    if (db) c.mask[b] |= 1ull << col;
     atomicMax(&c.cnt->n_colours, (uint32_t)col + 1u);
     return (uint32_t)col;
 }
@@ -585,6 +614,16 @@ __device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, f
         if (!(lam.x > 0.0f || lam.z > 0.0f)) continue;
         solve_vel_pair(c, k, load_pair_rec(c, k), lam, h, rest_threshold);
     }
+}
+
+__device__ __forceinline__ void serial_solve_pos(const Ctx& c, uint32_t ncol, float inv_h2) {
+    if (ncol <= SFP_SERIAL_COLOUR) return;
+    stage_solve_pos(c, SFP_SERIAL_COLOUR, inv_h2, 0u, 1u);  // one thread walks the whole group
+}
+__device__ __forceinline__ void serial_solve_vel(const Ctx& c, uint32_t ncol, float h,
+                                                 float rest_threshold) {
+    if (ncol <= SFP_SERIAL_COLOUR) return;
+    stage_solve_vel(c, SFP_SERIAL_COLOUR, h, rest_threshold, 0u, 1u);
 }
 
 }  // namespace sfpk

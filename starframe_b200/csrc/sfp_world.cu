@@ -73,6 +73,16 @@ __global__ void __launch_bounds__(TPB) k_solve_vel(Ctx c, uint32_t colour, float
     stage_solve_vel(c, colour, h, rt, gtid(), gnth());
 }
 
+__global__ void __launch_bounds__(TPB) k_serial_sort(Ctx c) {
+    serial_sort_pairs(c, vload(&c.cnt->n_colours));
+}
+__global__ void k_serial_pos(Ctx c, float inv_h2) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) serial_solve_pos(c, vload(&c.cnt->n_colours), inv_h2);
+}
+__global__ void k_serial_vel(Ctx c, float h, float rt) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) serial_solve_vel(c, vload(&c.cnt->n_colours), h, rt);
+}
+
 // ---- scene-graph state <-> solver records, on the device (AoS SfpBodyState, 32 B/body) -------
 __global__ void __launch_bounds__(TPB) k_pack_states(const float4* __restrict__ pose,
                                                      const float4* __restrict__ vel,
@@ -140,8 +150,13 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
     const uint32_t tid = gtid(), nth = gnth();
     const uint32_t ncol = vload(&c.cnt->n_colours);
     const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
-    const unsigned long long big = big_colour_mask(c, ncol), small = all & ~big;
+    const unsigned long long big = big_colour_mask(c, ncol);
+    const unsigned long long small = all & ~big & ~(1ull << SFP_SERIAL_COLOUR);
+    const bool serial = ncol > SFP_SERIAL_COLOUR;
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    // once per frame (substeps == all substeps of the frame, or 1 with per-substep broadphase):
+    // the serial group must be in (a, b) order before the first narrowphase
+    if (serial && blockIdx.x == 0) serial_sort_pairs(c, ncol);
 
     // Prefetch: the contact record of this thread's first item of the NEXT big colour does not
     // depend on anything the current phase writes, so it is loaded before the barrier and only
@@ -200,12 +215,14 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
             grid.sync();
         }
         lap(6);
-        if (small) {
-            if (blockIdx.x == 0)
+        if (small || serial) {
+            if (blockIdx.x == 0) {
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x);
                     __syncthreads();
                 }
+                if (serial && threadIdx.x == 0) serial_solve_pos(c, ncol, inv_h2);
+            }
             grid.sync();
         }
         lap(9);
@@ -220,12 +237,14 @@ __global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t 
             grid.sync();
         }
         lap(8);
-        if (small) {
-            if (blockIdx.x == 0)
+        if (small || serial) {
+            if (blockIdx.x == 0) {
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x);
                     __syncthreads();
                 }
+                if (serial && threadIdx.x == 0) serial_solve_vel(c, ncol, h, rest_threshold);
+            }
             grid.sync();
         }
         lap(9);
@@ -511,16 +530,21 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
         for (uint32_t col = 0; col < ncol; ++col) {
             uint32_t items = (k.pair_col_off[col + 1] - k.pair_col_off[col]) +
                              (k.joint_col_off[col + 1] - k.joint_col_off[col]);
-            if ((items > SFP_TAIL_ITEMS) == (pass == 0)) order.push_back(col);
+            if (col != SFP_SERIAL_COLOUR && (items > SFP_TAIL_ITEMS) == (pass == 0))
+                order.push_back(col);
         }
+    const bool serial = ncol > SFP_SERIAL_COLOUR;
+    if (serial) k_serial_sort<<<1, TPB, 0, st>>>(c);
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
     const uint32_t gb = blocks_for(w, w->n), gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
     for (uint32_t s = 0; s < substeps; ++s) {
         k_integrate<<<gb, TPB, 0, st>>>(c, h);
         k_narrowphase<<<gp, TPB, 0, st>>>(c);
         for (uint32_t col : order) k_solve_pos<<<gp, TPB, 0, st>>>(c, col, inv_h2);
+        if (serial) k_serial_pos<<<1, 32, 0, st>>>(c, inv_h2);
         k_derive<<<gb, TPB, 0, st>>>(c, inv_h);
         for (uint32_t col : order) k_solve_vel<<<gp, TPB, 0, st>>>(c, col, h, rest_threshold);
+        if (serial) k_serial_vel<<<1, 32, 0, st>>>(c, h, rest_threshold);
         w->launches += 3 + 2 * ncol;
     }
     CU(cudaGetLastError());
@@ -552,7 +576,7 @@ int check_overflow(SfpWorld* w, const Counters& k) {
         w->stats.overflow |= k.overflow;
         char buf[160];
         snprintf(buf, sizeof(buf),
-                 "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=colours>64, "
+                 "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=serial group>1024, "
                  "8=colour rounds, 16=runaway or non-finite body)",
                  k.overflow, w->cap_entries, w->cap_pairs);
         w->err = buf;

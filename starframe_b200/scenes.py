@@ -284,6 +284,26 @@ def random_soup(n: int, seed: int, pitch: float = 0.7, extent: float | None = No
     return np.concatenate([b, floor]), no_joints()
 
 
+def crowded_plank(n_riders: int = 100, seed: int = BASE_SEED + 7):
+    """One long DYNAMIC plank resting on a floor with n_riders small bodies standing on it: the
+    plank has more partners than there are colours (63), which exercises the serial group."""
+    pitch = 0.13
+    hx = 0.5 * n_riders * pitch + 0.2
+    floor = static_rect(0.0, -0.5, hx + 2.0, 0.5)
+    plank = empty_bodies(1)
+    plank["shape"], plank["hx"], plank["hy"], plank["radius"] = SHAPE_RECT, hx, 0.05, 0.01
+    plank["x"], plank["y"] = 0.0, 0.062
+    riders = empty_bodies(n_riders)
+    k = np.arange(n_riders)
+    riders["shape"] = np.where(k % 3 == 0, SHAPE_RECT, SHAPE_CIRCLE)
+    riders["radius"] = np.where(k % 3 == 0, 0.01, 0.05)
+    riders["hx"] = np.where(k % 3 == 0, 0.04, 0.0)
+    riders["hy"] = np.where(k % 3 == 0, 0.04, 0.0)
+    riders["x"] = (k - 0.5 * (n_riders - 1)) * pitch + uniform(seed, 1, n_riders, -0.005, 0.005)
+    riders["y"] = 0.062 + 0.06 + 0.052 + uniform(seed, 2, n_riders, 0.0, 0.01)
+    return np.concatenate([floor, plank, riders]), no_joints()
+
+
 CONFIGS = {
     "stack100": stack100,
     "circles10k": circles_container,

@@ -93,6 +93,22 @@ def test_small_batch_created_after_a_large_one_does_not_break_it(gpu_api):
     small.sync()
 
 
+def test_batch_serial_group(gpu_api, ref_api):
+    b, _ = scenes.crowded_plank(90)
+    n = len(b)
+    batch = sf.Batch(gpu_api, 2, n)
+    batch.upload(np.stack([b, b]))
+    r = sf.World(ref_api)
+    r.upload_bodies(b)
+    for _ in range(40):
+        batch.step()
+        r.step()
+    out = batch.download()
+    same(out[0], r.download_bodies())
+    same(out[1], r.download_bodies())
+    assert batch.stats()["n_colours"][0] == 64
+
+
 def test_batch_rejects_bad_arguments(gpu_api):
     with pytest.raises(sf.SfpError):
         sf.Batch(gpu_api, 0, 64)

@@ -111,6 +111,15 @@ def test_ropes_small(gpu_api, ref_api):
     run_and_compare(g, r, 40, every=10)
 
 
+@pytest.mark.parametrize("flags", [0, sf._ffi.FLAG_MULTI_KERNEL])
+def test_serial_group_plank(gpu_api, ref_api, flags):
+    """a body with more partners than colours: the serial group (colour 63) on the device"""
+    b, j = scenes.crowded_plank(100)
+    g, r = make_worlds(gpu_api, ref_api, b, j, flags=flags)
+    run_and_compare(g, r, 40, every=10)
+    assert g.stats()["n_colours"] == 64
+
+
 def test_step_host_roundtrip(gpu_api, ref_api):
     b, j = scenes.mixed_pile(1500)
     g, r = make_worlds(gpu_api, ref_api, b, j)

@@ -257,3 +257,26 @@ def test_rollout_metrics_pile(ref_api):
     st = w.stats()
     assert worst_pen < 0.01
     assert st["kinetic_energy"] < 1e-3 * abs(st["potential_energy"]) + 0.05
+
+
+def test_serial_group_when_a_body_has_more_partners_than_colours(ref_api):
+    """a dynamic plank carrying 100 bodies: 63 proper colours do not suffice; the remaining
+    constraints join the serial group (colour 63) and the step still works and stays put"""
+    b, j = scenes.crowded_plank(100)
+    w = world(ref_api, b, j)
+    for _ in range(120):
+        w.step()
+    pairs, pc, _ = w.get_colours()
+    st = w.stats()
+    assert st["n_colours"] == 64 and st["overflow"] == 0
+    plank = 1
+    on_plank = (pairs["a"] == plank) | (pairs["b"] == plank)
+    assert on_plank.sum() > 63
+    serial = pc == 63
+    assert serial.sum() >= on_plank.sum() - 63
+    # proper colours are proper: the plank appears at most once per colour below 63
+    cols = pc[on_plank & ~serial]
+    assert np.unique(cols).size == cols.size
+    s = w.download_bodies()
+    assert abs(s["y"][plank] - 0.06) < 5e-3 and abs(s["angle"][plank]) < 1e-3
+    assert np.all(s["y"][2:] > 0.1) and np.abs(s["vy"]).max() < 0.05  # riders rest on the plank
