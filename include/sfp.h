@@ -141,6 +141,15 @@ typedef struct SfpContact {
     float lambda_t[2];
 } SfpContact; /* 60 bytes */
 
+/* what game code hears about a collision */
+typedef struct SfpContactEvent {
+    uint32_t a, b;   /* a < b */
+    float nx, ny;    /* unit normal from a to b */
+    float px, py;    /* world-space contact point (first active point of the manifold) */
+    float impulse;   /* normal impulse applied in the last substep, N s: (ln0 + ln1) / h */
+    uint32_t points; /* active points: 1 or 2 */
+} SfpContactEvent; /* 32 bytes */
+
 typedef struct SfpStats {
     uint64_t frames;        /* frames stepped since creation */
     uint64_t body_substeps; /* sum of n_bodies * substeps */
@@ -202,6 +211,19 @@ SFP_API int32_t sfp_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t ca
 
 SFP_API int32_t sfp_get_stats(SfpWorld* w, SfpStats* out);
 SFP_API const char* sfp_last_error(SfpWorld* w);
+
+/* Replaces: the contact-event list the reference hands to game code after a step (reference
+ * file:line unavailable).  One event per candidate pair that carried a normal impulse in the
+ * last substep, compacted ON THE DEVICE (only the events cross the bus), sorted by (a, b).
+ * Same cap semantics as sfp_get_pairs. */
+SFP_API int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap,
+                                       uint32_t* n_out);
+
+/* Replaces: game code moving individual bodies between steps (teleports, kinematic control).
+ * Overwrites pose and velocity of the m bodies idx[0..m) with states[0..m); everything else
+ * (shape, mass, material, joints) is untouched.  Indices must be distinct. */
+SFP_API int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
+                                  uint32_t m);
 
 /* ---- step with host buffers (the end-to-end call the engine makes each frame) -------- */
 /* Uploads poses+velocities for n bodies (shape/material unchanged since the last full
@@ -271,6 +293,10 @@ SFP_API int32_t sfp_ref_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap,
 SFP_API int32_t sfp_ref_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap,
                                     uint32_t* joint_colours, uint32_t jcap);
 SFP_API int32_t sfp_ref_get_stats(SfpWorld* w, SfpStats* out);
+SFP_API int32_t sfp_ref_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap,
+                                           uint32_t* n_out);
+SFP_API int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
+                                      uint32_t m);
 SFP_API const char* sfp_ref_last_error(SfpWorld* w);
 SFP_API int32_t sfp_ref_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out,
                                   uint32_t n, float dt, uint32_t substeps);

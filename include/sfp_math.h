@@ -704,6 +704,31 @@ SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose
     return c;
 }
 
+/* contact event of one pair from its records (layout of SfpContactEvent in sfp.h) */
+struct EventRec {
+    uint32_t a, b;
+    float nx, ny, px, py, impulse;
+    uint32_t points;
+};
+SFP_HD bool pair_event(uint32_t a, uint32_t b, f4 ca, f4 cb, f4 p0, f4 p1, f4 lam, f4 pose_a,
+                       f4 pose_b, float inv_h, EventRec* e) {
+    uint32_t cnt = f2u(cb.y);
+    bool on0 = cnt > 0u && lam.x > 0.0f, on1 = cnt > 1u && lam.z > 0.0f;
+    if (!on0 && !on1) return false;
+    f4 pp = on0 ? p0 : p1;
+    v2 wa = mk(pose_a.x, pose_a.y) + rot(mk(pose_a.z, pose_a.w), mk(pp.x, pp.y));
+    v2 wb = mk(pose_b.x, pose_b.y) + rot(mk(pose_b.z, pose_b.w), mk(pp.z, pp.w));
+    e->a = a;
+    e->b = b;
+    e->nx = ca.x;
+    e->ny = ca.y;
+    e->px = 0.5f * (wa.x + wb.x);
+    e->py = 0.5f * (wa.y + wb.y);
+    e->impulse = ((on0 ? lam.x : 0.0f) + (on1 ? lam.z : 0.0f)) * inv_h;
+    e->points = (on0 ? 1u : 0u) + (on1 ? 1u : 0u);
+    return true;
+}
+
 /* ------------------------------------------------------------------------------------- */
 /* Integrate (A3) and velocity derivation (A7 i)                                         */
 /* ------------------------------------------------------------------------------------- */

@@ -52,6 +52,7 @@ struct SfpWorld {
     SfpStats stats;
     std::string err;
     float last_ms = 0.0f;
+    float last_h = 0.0f; /* substep length of the last frame */
     bool stepped = false;
 };
 
@@ -396,6 +397,7 @@ int frame(SfpWorld& w, float dt, uint32_t substeps) {
     w.stats.frames += 1;
     w.stats.body_substeps += (uint64_t)w.n * substeps;
     w.stepped = true;
+    w.last_h = h;
     return SFP_OK;
 }
 
@@ -550,6 +552,35 @@ int32_t sfp_ref_get_stats(SfpWorld* w, SfpStats* out) {
     energies(w->pose, w->vel, w->minv, w->p.gravity_x, w->p.gravity_y, &w->stats.kinetic_energy,
              &w->stats.potential_energy);
     *out = w->stats;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap,
+                                   uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    static_assert(sizeof(EventRec) == sizeof(SfpContactEvent), "EventRec mirrors SfpContactEvent");
+    uint32_t cnt = 0;
+    const float inv_h = w->last_h > 0.0f ? 1.0f / w->last_h : 0.0f;
+    for (size_t k = 0; k < w->contacts.size() && k < w->pairs.size(); ++k) {
+        const ContactRec& c = w->contacts[k];
+        uint32_t a = w->pairs[k].a, b = w->pairs[k].b;
+        EventRec e;
+        if (!pair_event(a, b, c.a, c.b, c.p0, c.p1, w->lambdas[k], w->pose[a], w->pose[b], inv_h, &e))
+            continue;
+        if (cnt < cap) std::memcpy(&out[cnt], &e, sizeof(e));
+        ++cnt;
+    }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
+                              uint32_t m) {
+    if (!w || (m && (!idx || !states))) return SFP_E_INVALID;
+    for (uint32_t k = 0; k < m; ++k)
+        if (idx[k] >= w->n) return SFP_E_INVALID;
+    for (uint32_t k = 0; k < m; ++k)
+        records_from_state(states[k], w->minv[idx[k]], &w->pose[idx[k]], &w->vel[idx[k]]);
     return SFP_OK;
 }
 

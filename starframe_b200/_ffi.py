@@ -70,6 +70,12 @@ CONTACT_DTYPE = np.dtype(
         ("lambda_n", "<f4", (2,)), ("lambda_t", "<f4", (2,)),
     ]
 )
+EVENT_DTYPE = np.dtype(
+    [
+        ("a", "<u4"), ("b", "<u4"), ("nx", "<f4"), ("ny", "<f4"), ("px", "<f4"), ("py", "<f4"),
+        ("impulse", "<f4"), ("points", "<u4"),
+    ]
+)
 STATS_DTYPE = np.dtype(
     [
         ("frames", "<u8"), ("body_substeps", "<u8"),
@@ -87,19 +93,20 @@ assert BODY_STATE_DTYPE.itemsize == 32
 assert PAIR_DTYPE.itemsize == 8
 assert CONTACT_DTYPE.itemsize == 60
 assert STATS_DTYPE.itemsize == 80
+assert EVENT_DTYPE.itemsize == 32
 
 # every symbol include/sfp.h declares for the product library (checked by the CPU tests)
 PRODUCT_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
+    "get_contact_events", "update_bodies", "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "step_host", "last_step_ms", "backend", "brute_pairs",
+    "get_contact_events", "update_bodies", "step_host", "last_step_ms", "backend", "brute_pairs",
 ]
 
 
@@ -152,6 +159,8 @@ class Api:
             "download_bodies": [vp, vp, u32],
             "get_pairs": [vp, vp, u32, C.POINTER(u32)],
             "get_contacts": [vp, vp, u32, C.POINTER(u32)],
+            "get_contact_events": [vp, vp, u32, C.POINTER(u32)],
+            "update_bodies": [vp, vp, vp, u32],
             "get_colours": [vp, vp, u32, vp, u32],
             "get_stats": [vp, vp],
             "step_host": [vp, vp, vp, u32, f32, u32],
@@ -294,6 +303,22 @@ class World:
             self._check(self.api.fn("get_contacts")(self.h, _ptr(out), n.value, C.byref(n)),
                         "get_contacts")
         return out
+
+    def get_contact_events(self) -> np.ndarray:
+        n = C.c_uint32(0)
+        self._check(self.api.fn("get_contact_events")(self.h, None, 0, C.byref(n)), "events")
+        out = np.zeros(n.value, dtype=EVENT_DTYPE)
+        if n.value:
+            self._check(self.api.fn("get_contact_events")(self.h, _ptr(out), n.value, C.byref(n)),
+                        "events")
+        return out
+
+    def update_bodies(self, idx: np.ndarray, states: np.ndarray):
+        i = np.ascontiguousarray(idx, dtype=np.uint32)
+        s = np.ascontiguousarray(states, dtype=BODY_STATE_DTYPE)
+        assert i.shape[0] == s.shape[0]
+        self._check(self.api.fn("update_bodies")(self.h, _ptr(i), _ptr(s), i.shape[0]),
+                    "update_bodies")
 
     def get_colours(self):
         pairs = self.get_pairs()

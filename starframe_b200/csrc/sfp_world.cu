@@ -83,6 +83,50 @@ __global__ void k_serial_vel(Ctx c, float h, float rt) {
     if (threadIdx.x == 0 && blockIdx.x == 0) serial_solve_vel(c, vload(&c.cnt->n_colours), h, rt);
 }
 
+// ---- contact events: flag -> scan -> write, so only the events cross the bus ------------------
+__global__ void __launch_bounds__(TPB) k_event_flags(Ctx c, uint32_t* __restrict__ flags) {
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = gtid(); k < P; k += gnth()) {
+        float4 cb = c.cb[k], lam = c.lam[k];
+        uint32_t cnt = __float_as_uint(cb.y);
+        flags[k] = ((cnt > 0u && lam.x > 0.0f) || (cnt > 1u && lam.z > 0.0f)) ? 1u : 0u;
+    }
+}
+__global__ void __launch_bounds__(TPB) k_event_write(Ctx c, const uint32_t* __restrict__ off,
+                                                     sfp::EventRec* __restrict__ out, float inv_h) {
+    const uint32_t P = c.cnt->n_pairs;
+    for (uint32_t k = gtid(); k < P; k += gnth()) {
+        if (off[k + 1] == off[k]) continue;
+        uint2 p = c.pairs[k];
+        sfp::EventRec e;
+        if (sfp::pair_event(p.x, p.y, ld4(c.ca, k), ld4(c.cb, k), ld4(c.cp0, k), ld4(c.cp1, k),
+                            ld4(c.lam, k), ld4(c.pose, p.x), ld4(c.pose, p.y), inv_h, &e)) {
+            uint4* o = reinterpret_cast<uint4*>(out + off[k]);
+            o[0] = make_uint4(e.a, e.b, __float_as_uint(e.nx), __float_as_uint(e.ny));
+            o[1] = make_uint4(__float_as_uint(e.px), __float_as_uint(e.py),
+                              __float_as_uint(e.impulse), e.points);
+        }
+    }
+}
+// scatter-update of individual bodies from scene-graph states
+__global__ void __launch_bounds__(TPB) k_update_bodies(const uint32_t* __restrict__ idx,
+                                                       const sfp::StateRec* __restrict__ in,
+                                                       const float2* __restrict__ minv,
+                                                       float4* __restrict__ pose,
+                                                       float4* __restrict__ vel, uint32_t m) {
+    for (uint32_t k = gtid(); k < m; k += gnth()) {
+        const uint32_t i = idx[k];
+        const float4* q = reinterpret_cast<const float4*>(in + k);
+        float4 a = q[0], b = q[1];
+        sfp::StateRec r;
+        r.x = a.x, r.y = a.y, r.c = a.z, r.s = a.w, r.vx = b.x, r.vy = b.y, r.omega = b.z, r.angle = b.w;
+        f4 p, v;
+        sfp::state_unpack(r, ld2(minv, i), &p, &v);
+        st4(pose, i, p);
+        st4(vel, i, v);
+    }
+}
+
 // ---- scene-graph state <-> solver records, on the device (AoS SfpBodyState, 32 B/body) -------
 __global__ void __launch_bounds__(TPB) k_pack_states(const float4* __restrict__ pose,
                                                      const float4* __restrict__ vel,
@@ -290,6 +334,10 @@ struct SfpWorld {
     // host mirrors
     std::vector<sfp::f2> h_minv;
     std::vector<sfp::f4> h_shape, h_mat;
+    uint32_t *d_evt_flag = nullptr, *d_evt_off = nullptr;  // cap_pairs + 1 each
+    sfp::EventRec* d_events = nullptr;                    // cap_pairs
+    uint32_t* d_idx = nullptr;                            // cap_bodies (sfp_update_bodies)
+    float last_h = 0.0f;
     SfpBodyState* pin_state = nullptr;   // pinned host staging, cap_bodies states
     sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
     uint32_t pin_cap = 0;
@@ -368,6 +416,10 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.cp1, cp, bag));
     TRY(alloc_dev(w, &c.cs, cp, bag));
     TRY(alloc_dev(w, &c.lam, cp, bag));
+    TRY(alloc_dev(w, &w->d_evt_flag, cp + 1, bag));
+    TRY(alloc_dev(w, &w->d_evt_off, cp + 1, bag));
+    TRY(alloc_dev(w, &w->d_events, cp, bag));
+    TRY(alloc_dev(w, &w->d_idx, cb, bag));
     uint32_t slots = 1024;
     while (slots < 2u * cp) slots <<= 1;
     TRY(alloc_dev(w, &w->d_tab[0], slots, bag));
@@ -780,6 +832,7 @@ int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps) {
     w->stats.frames += 1;
     w->stats.body_substeps += (uint64_t)w->n * substeps;
     w->stepped = true;
+    w->last_h = dt / (float)substeps;
     return SFP_OK;
 }
 
@@ -928,6 +981,57 @@ int32_t sfp_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap, uint32_t* n
         ++cnt;
     }
     *n_out = cnt;
+    return SFP_OK;
+}
+
+int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    static_assert(sizeof(sfp::EventRec) == sizeof(SfpContactEvent), "EventRec mirrors the ABI");
+    *n_out = 0;
+    if (!w->stepped || w->n == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    cudaStream_t st = w->stream;
+    const uint32_t gp = blocks_for(w, w->cap_pairs);
+    k_event_flags<<<gp, TPB, 0, st>>>(w->ctx, w->d_evt_flag);
+    // the scan's total goes to the spare slot behind the flags (device memory, read back below)
+    CU(scan_exclusive(w->d_evt_flag, w->d_evt_off, &w->d_cnt->n_pairs, w->cap_pairs,
+                      w->d_scan_tiles, w->d_evt_flag + w->cap_pairs, st));
+    k_event_write<<<gp, TPB, 0, st>>>(w->ctx, w->d_evt_off, w->d_events, 1.0f / w->last_h);
+    CU(cudaGetLastError());
+    uint32_t total = 0;
+    CU(cudaMemcpyAsync(&total, w->d_evt_flag + w->cap_pairs, sizeof(total), cudaMemcpyDeviceToHost, st));
+    Counters k;
+    TRY(read_counters(w, &k));  // synchronises
+    TRY(check_overflow(w, k));
+    *n_out = total;
+    const uint32_t m = std::min(total, cap);
+    if (m == 0) return SFP_OK;
+    std::vector<SfpContactEvent> ev(total);
+    CU(cudaMemcpy(ev.data(), w->d_events, sizeof(SfpContactEvent) * total, cudaMemcpyDeviceToHost));
+    std::sort(ev.begin(), ev.end(), [](const SfpContactEvent& x, const SfpContactEvent& y) {
+        return x.a != y.a ? x.a < y.a : x.b < y.b;
+    });
+    std::memcpy(out, ev.data(), sizeof(SfpContactEvent) * m);
+    return SFP_OK;
+}
+
+int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states, uint32_t m) {
+    if (!w || (m && (!idx || !states)) || m > w->n) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    for (uint32_t k = 0; k < m; ++k)
+        if (idx[k] >= w->n) return SFP_E_INVALID;
+    if (m == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
+    for (uint32_t k = 0; k < m; ++k) w->pin_state[k] = sfp::state_with_rotor(states[k]);
+    CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * m, cudaMemcpyHostToDevice,
+                       w->stream));
+    CU(cudaMemcpyAsync(w->d_idx, idx, sizeof(uint32_t) * m, cudaMemcpyHostToDevice, w->stream));
+    k_update_bodies<<<blocks_for(w, m), TPB, 0, w->stream>>>(w->d_idx, w->d_state, w->ctx.minv,
+                                                            w->ctx.pose, w->ctx.vel, m);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(w->stream));  // idx is the caller's memory
     return SFP_OK;
 }
 

@@ -120,6 +120,45 @@ def test_serial_group_plank(gpu_api, ref_api, flags):
     assert g.stats()["n_colours"] == 64
 
 
+def test_contact_events_match_oracle(gpu_api, ref_api):
+    """device-compacted contact events == the oracle's, field for field"""
+    b, j = scenes.mixed_pile(2500)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    assert len(g.get_contact_events()) == 0
+    for f in range(120):
+        g.step()
+        r.step()
+        if f % 40 == 39:
+            eg, er = g.get_contact_events(), r.get_contact_events()
+            assert len(eg) == len(er) and len(eg) > 0
+            assert eg.tobytes() == er.tobytes()
+    assert len(eg) > 1000
+
+
+def test_update_bodies_matches_oracle(gpu_api, ref_api):
+    b, j = scenes.mixed_pile(1500)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    rng = np.random.default_rng(3)
+    for round_ in range(4):
+        for _ in range(15):
+            g.step()
+            r.step()
+        idx = rng.choice(np.arange(3, len(b)), size=40, replace=False).astype(np.uint32)
+        st = r.download_bodies()[idx].copy()
+        st["y"] += 3.0
+        st["vx"] = rng.uniform(-2, 2, 40).astype(np.float32)
+        if round_ == 1:
+            st["c"] = 0.0
+            st["s"] = 0.0  # rotation given as an angle only
+        g.update_bodies(idx, st)
+        r.update_bodies(idx, st)
+    for _ in range(10):
+        g.step()
+        r.step()
+    assert_same_discrete(g, r)
+    assert_same_state(g, r)
+
+
 def test_step_host_roundtrip(gpu_api, ref_api):
     b, j = scenes.mixed_pile(1500)
     g, r = make_worlds(gpu_api, ref_api, b, j)

@@ -389,3 +389,39 @@ def test_box_stack_is_stable(ref_api):
     assert abs(top["x"]) < 1e-3
     assert abs(top["angle"]) < 1e-3
     assert np.abs(s["vy"]).max() < 0.05
+
+
+def test_contact_event_reports_the_resting_weight(ref_api):
+    """a ball resting on the floor: one event per substep-active pair, normal up, point at the
+    touching point, impulse = m g h (the weight carried over one substep)"""
+    floor = static_rect(0.0, -0.5, 5.0, 0.5)
+    ball = body(SHAPE_CIRCLE, 0.0, 0.501, r=0.5)
+    w = world(ref_api, cat(floor, ball))
+    for _ in range(90):
+        w.step()
+    ev = w.get_contact_events()
+    assert len(ev) == 1 and (ev[0]["a"], ev[0]["b"], ev[0]["points"]) == (0, 1, 1)
+    assert (ev[0]["nx"], ev[0]["ny"]) == pytest.approx((0.0, 1.0), abs=1e-6)
+    assert (ev[0]["px"], ev[0]["py"]) == pytest.approx((0.0, 0.0), abs=2e-3)
+    m = math.pi * 0.25
+    assert ev[0]["impulse"] == pytest.approx(m * G / 480.0, rel=0.05)
+
+
+def test_update_bodies_teleports_only_the_named_bodies(ref_api):
+    floor = static_rect(0.0, -0.5, 5.0, 0.5)
+    a = body(SHAPE_CIRCLE, -1.0, 0.5, r=0.5)
+    b = body(SHAPE_CIRCLE, 1.0, 0.5, r=0.5)
+    w = world(ref_api, cat(floor, a, b))
+    for _ in range(30):
+        w.step()
+    before = w.download_bodies()
+    st = before[[2]].copy()
+    st["x"], st["y"], st["vx"], st["vy"] = 3.0, 4.0, 0.0, 0.0
+    w.update_bodies(np.array([2], dtype=np.uint32), st)
+    after = w.download_bodies()
+    assert after[1].tobytes() == before[1].tobytes()
+    assert (after[2]["x"], after[2]["y"]) == (3.0, 4.0)
+    w.step()
+    assert w.download_bodies()[2]["y"] < 4.0  # it falls from its new place
+    with pytest.raises(sf.SfpError):
+        w.update_bodies(np.array([7], dtype=np.uint32), st)
