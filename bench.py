@@ -170,13 +170,15 @@ def run_single(args, rank, world_size):
     st = w.stats()
 
     # end to end through the public call with host buffers (H2D + step + D2H inside the window)
-    state = w.download_bodies()
+    # (the engine keeps its body states in two page-locked arrays from sfp_alloc_host_states)
+    buf = [api.alloc_host_states(n), api.alloc_host_states(n)]
+    buf[0][:] = w.download_bodies()
     e2e_steps = max(3, min(args.steps, 30))
-    state = w.step_host(state, DT, SUBSTEPS)
+    w.step_host(buf[0], DT, SUBSTEPS, out=buf[1])
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        state = w.step_host(state, DT, SUBSTEPS)
+    for k in range(e2e_steps):
+        w.step_host(buf[(k + 1) & 1], DT, SUBSTEPS, out=buf[k & 1])
     e2e_s = time.perf_counter() - t0
 
     t_dev_max = allreduce_max(t_dev, world_size)
@@ -217,7 +219,7 @@ def run_single(args, rank, world_size):
                                 "frac": bytes_step / (t_dev / args.steps * 1e-3) / 1e9 / peak},
         "e2e": {"value": float(n) * SUBSTEPS * e2e_steps / e2e_s, "unit": "body-substeps/s",
                 "h2d_bytes_per_step": 32 * n, "d2h_bytes_per_step": 32 * n,
-                "call": "sfp_step_host (host SfpBodyState in/out, pinned staging inside)",
+                "call": "sfp_step_host with host SfpBodyState arrays from sfp_alloc_host_states (pinned)",
                 "steps": e2e_steps},
         "gpu_launches": int(st["launches"]) * args.steps,
         "launches_per_step": int(st["launches"]),

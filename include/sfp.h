@@ -231,6 +231,12 @@ SFP_API int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBod
 SFP_API int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out,
                               uint32_t n, float dt, uint32_t substeps);
 
+/* Page-locked host arrays for sfp_step_host / sfp_download_bodies: when `in` / `out` point into
+ * memory obtained here the copies go straight over the bus (no staging memcpy on the host).
+ * Any other host memory works too, through the library's own pinned staging buffer. */
+SFP_API int32_t sfp_alloc_host_states(uint32_t n, SfpBodyState** out);
+SFP_API int32_t sfp_free_host_states(SfpBodyState* p);
+
 /* ---- batched independent worlds (BASELINE.json config 5) --------------------------- */
 /* n_worlds worlds of exactly bodies_per_world bodies each, stepped together on ONE device
  * (one process per GPU shards the world range; no collective on the data path). */

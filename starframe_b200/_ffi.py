@@ -99,7 +99,8 @@ assert EVENT_DTYPE.itemsize == 32
 PRODUCT_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "get_contact_events", "update_bodies", "step_host", "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
+    "get_contact_events", "update_bodies", "step_host", "alloc_host_states", "free_host_states",
+    "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
@@ -161,6 +162,8 @@ class Api:
             "get_contacts": [vp, vp, u32, C.POINTER(u32)],
             "get_contact_events": [vp, vp, u32, C.POINTER(u32)],
             "update_bodies": [vp, vp, vp, u32],
+            "alloc_host_states": [u32, C.POINTER(vp)],
+            "free_host_states": [vp],
             "get_colours": [vp, vp, u32, vp, u32],
             "get_stats": [vp, vp],
             "step_host": [vp, vp, vp, u32, f32, u32],
@@ -191,6 +194,18 @@ class Api:
         if self.has("backend"):
             self.fn("backend").argtypes = []
             self.fn("backend").restype = C.c_char_p
+
+    def alloc_host_states(self, n: int) -> np.ndarray:
+        """page-locked SfpBodyState array (freed when the returned array's owner is collected)"""
+        p = C.c_void_p()
+        rc = self.fn("alloc_host_states")(n, C.byref(p))
+        if rc != SFP_OK:
+            raise SfpError(rc, "alloc_host_states")
+        buf = (C.c_char * (n * BODY_STATE_DTYPE.itemsize)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=BODY_STATE_DTYPE)
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(p)
+        return arr
 
     def backend(self) -> str:
         return self.fn("backend")().decode()

@@ -188,7 +188,10 @@ __device__ __forceinline__ int next_bit(unsigned long long m, int after) {
     return r ? (__ffsll((long long)r) - 1) : 64;
 }
 
-__global__ void __launch_bounds__(TPB) k_substeps_coop(Ctx c, float h, uint32_t substeps,
+#ifndef SFP_SUB_BLOCKS
+#define SFP_SUB_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, float h, uint32_t substeps,
                                                        float rest_threshold) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
@@ -845,20 +848,45 @@ int32_t sfp_sync(SfpWorld* w) {
     return check_overflow(w, k);
 }
 
+namespace {
+// true if p is page-locked host memory the device can DMA from / to directly
+bool host_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+}  // namespace
+
+int32_t sfp_alloc_host_states(uint32_t n, SfpBodyState** out) {
+    if (!out || n == 0) return SFP_E_INVALID;
+    void* p = nullptr;
+    if (cudaMallocHost(&p, sizeof(SfpBodyState) * (size_t)n) != cudaSuccess) return SFP_E_NOMEM;
+    *out = static_cast<SfpBodyState*>(p);
+    return SFP_OK;
+}
+int32_t sfp_free_host_states(SfpBodyState* p) {
+    if (p && cudaFreeHost(p) != cudaSuccess) return SFP_E_CUDA;
+    return SFP_OK;
+}
+
 int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
     if (!w || (n && !out) || n > w->n) return SFP_E_INVALID;
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
+    const bool direct = n && host_pinned(out);
     if (n) {
         // states are packed on the device (incl. the angle), one D2H copy, no per-body host work
         k_pack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->ctx.pose, w->ctx.vel, w->d_state, n);
         CU(cudaGetLastError());
-        CU(cudaMemcpyAsync(w->pin_state, w->d_state, sizeof(SfpBodyState) * n,
+        CU(cudaMemcpyAsync(direct ? out : w->pin_state, w->d_state, sizeof(SfpBodyState) * n,
                            cudaMemcpyDeviceToHost, w->stream));
     }
     Counters k;
     TRY(read_counters(w, &k));
-    if (n) std::memcpy(out, w->pin_state, sizeof(SfpBodyState) * n);
+    if (n && !direct) std::memcpy(out, w->pin_state, sizeof(SfpBodyState) * n);
     return check_overflow(w, k);
 }
 
@@ -869,11 +897,14 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
     CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
-    std::memcpy(w->pin_state, in, sizeof(SfpBodyState) * n);
-    for (uint32_t i = 0; i < n; ++i)  // rare: a state that carries its rotation in `angle` only
-        if (!(in[i].c * in[i].c + in[i].s * in[i].s > 0.0f))
-            w->pin_state[i] = sfp::state_with_rotor(in[i]);
-    CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * n, cudaMemcpyHostToDevice,
+    bool zero_rotor = false;  // rare: a state that carries its rotation in `angle` only
+    for (uint32_t i = 0; i < n; ++i) zero_rotor |= !(in[i].c * in[i].c + in[i].s * in[i].s > 0.0f);
+    const SfpBodyState* src = in;
+    if (zero_rotor || !host_pinned(in)) {
+        for (uint32_t i = 0; i < n; ++i) w->pin_state[i] = sfp::state_with_rotor(in[i]);
+        src = w->pin_state;
+    }
+    CU(cudaMemcpyAsync(w->d_state, src, sizeof(SfpBodyState) * n, cudaMemcpyHostToDevice,
                        w->stream));
     k_unpack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->d_state, w->ctx.minv, w->ctx.pose,
                                                             w->ctx.vel, n);

@@ -170,6 +170,21 @@ def test_step_host_roundtrip(gpu_api, ref_api):
         assert np.array_equal(sg[f].view(np.uint32), sr[f].view(np.uint32)), f
 
 
+def test_step_host_with_pinned_arrays(gpu_api, ref_api):
+    """states kept in sfp_alloc_host_states memory take the direct-DMA path: same result"""
+    b, j = scenes.mixed_pile(1500)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    n = len(b)
+    buf = [gpu_api.alloc_host_states(n), gpu_api.alloc_host_states(n)]
+    buf[0][:] = g.download_bodies()
+    sr = r.download_bodies()
+    for k in range(6):
+        g.step_host(buf[k & 1], out=buf[(k + 1) & 1])
+        sr = r.step_host(sr)
+    for f in FIELDS:
+        assert np.array_equal(buf[0][f].view(np.uint32), sr[f].view(np.uint32)), f
+
+
 def test_empty_and_tiny_worlds(gpu_api, ref_api):
     for n in (0, 1, 2):
         b, j = scenes.random_soup(max(n, 1), 5)
