@@ -211,11 +211,11 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
     PairRec rec;
     uint32_t rec_k = 0;
     bool have = false;
-    auto prefetch_pos = [&](int col) {
+    auto prefetch_pos = [&](int col, uint32_t t0) {
         have = false;
         if (col >= 64) return;
         if (c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return;
-        uint32_t k = c.cnt->pair_col_off[col] + tid;
+        uint32_t k = c.cnt->pair_col_off[col] + t0;
         if (k < c.cnt->pair_col_off[col + 1]) {
             rec = load_pair_rec(c, k);
             rec_k = k;
@@ -223,10 +223,10 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         }
     };
     f4 rec_lam;
-    auto prefetch_vel = [&](int col) {
+    auto prefetch_vel = [&](int col, uint32_t t0) {
         have = false;
         if (col >= 64) return;
-        uint32_t k = c.cnt->pair_col_off[col] + tid;
+        uint32_t k = c.cnt->pair_col_off[col] + t0;
         if (k < c.cnt->pair_col_off[col + 1]) {
             rec_lam = ld4(c.lam, k);
             rec = load_pair_rec(c, k);
@@ -258,14 +258,18 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_pos_pair(c, rec_k, rec);
             stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth, have);
-            prefetch_pos(next_bit(big, col));
+            prefetch_pos(next_bit(big, col), tid);
             grid.sync();
         }
         lap(6);
         if (small || serial) {
             if (blockIdx.x == 0) {
+                // same record prefetch as above, one block wide
+                have = false;
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
-                    stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x);
+                    if (have) solve_pos_pair(c, rec_k, rec);
+                    stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x, have);
+                    prefetch_pos(next_bit(small, col), threadIdx.x);
                     __syncthreads();
                 }
                 if (serial && threadIdx.x == 0) serial_solve_pos(c, ncol, inv_h2);
@@ -280,14 +284,18 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
             stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth, have);
-            prefetch_vel(next_bit(big, col));
+            prefetch_vel(next_bit(big, col), tid);
             grid.sync();
         }
         lap(8);
         if (small || serial) {
             if (blockIdx.x == 0) {
+                have = false;
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
-                    stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x);
+                    if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
+                    stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x,
+                                    have);
+                    prefetch_vel(next_bit(small, col), threadIdx.x);
                     __syncthreads();
                 }
                 if (serial && threadIdx.x == 0) serial_solve_vel(c, ncol, h, rest_threshold);
