@@ -150,6 +150,21 @@ typedef struct SfpContactEvent {
     uint32_t points; /* active points: 1 or 2 */
 } SfpContactEvent; /* 32 bytes */
 
+/* spatial queries */
+typedef struct SfpRay {
+    float ox, oy;  /* origin */
+    float dx, dy;  /* direction, any non-zero length; t is measured in units of it */
+    float max_t;
+    uint32_t mask; /* a body can be hit iff (its category & mask) != 0 */
+    uint32_t reserved[2];
+} SfpRay; /* 32 bytes */
+
+typedef struct SfpRayHit {
+    uint32_t body; /* 0xffffffff = no hit */
+    float t;       /* hit point = origin + t * direction; 0 if the origin is inside the body */
+    float nx, ny;  /* surface normal at the hit (minus the ray direction if inside) */
+} SfpRayHit; /* 16 bytes */
+
 typedef struct SfpStats {
     uint64_t frames;        /* frames stepped since creation */
     uint64_t body_substeps; /* sum of n_bodies * substeps */
@@ -218,6 +233,15 @@ SFP_API const char* sfp_last_error(SfpWorld* w);
  * Same cap semantics as sfp_get_pairs. */
 SFP_API int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap,
                                        uint32_t* n_out);
+
+/* Replaces: the reference's ray / shape queries against the physics world (reference file:line
+ * unavailable).  Both work on the CURRENT body state.
+ * sfp_ray_cast: m rays at once, one device thread per ray walking the spatial hash (rebuilt for
+ * the current poses); closest hit per ray, ties to the lower body index.
+ * sfp_query_aabb: indices (ascending) of the bodies whose tight AABB overlaps the box. */
+SFP_API int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits);
+SFP_API int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y,
+                               uint32_t mask, uint32_t* out, uint32_t cap, uint32_t* n_out);
 
 /* Replaces: game code moving individual bodies between steps (teleports, kinematic control).
  * Overwrites pose and velocity of the m bodies idx[0..m) with states[0..m); everything else
@@ -301,6 +325,9 @@ SFP_API int32_t sfp_ref_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_
 SFP_API int32_t sfp_ref_get_stats(SfpWorld* w, SfpStats* out);
 SFP_API int32_t sfp_ref_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap,
                                            uint32_t* n_out);
+SFP_API int32_t sfp_ref_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits);
+SFP_API int32_t sfp_ref_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y,
+                                   uint32_t mask, uint32_t* out, uint32_t cap, uint32_t* n_out);
 SFP_API int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
                                       uint32_t m);
 SFP_API const char* sfp_ref_last_error(SfpWorld* w);

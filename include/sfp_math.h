@@ -1026,6 +1026,126 @@ SFP_HD void solve_manifold_velocity(BodyVel* A, BodyVel* B, v2 qa, v2 qb, v2 n, 
 }
 
 /* ------------------------------------------------------------------------------------- */
+/* Spatial queries: ray vs collider, exact for the rounded shapes     */
+/* ------------------------------------------------------------------------------------- */
+/* layout of SfpRay / SfpRayHit in sfp.h */
+struct RayRec {
+    float ox, oy, dx, dy; /* origin, direction (any non-zero length; t is in units of it) */
+    float max_t;
+    uint32_t mask;        /* category bits the ray can hit */
+    uint32_t pad[2];
+};
+struct RayHitRec {
+    uint32_t body; /* 0xffffffff: no hit */
+    float t, nx, ny;
+};
+
+/* ray o + t d vs the disc of radius r at c: smallest t in [0, tmax] where the ray ENTERS */
+SFP_HD bool ray_disc(v2 o, v2 d, v2 c, float r, float tmax, float* t, v2* n) {
+    v2 m = o - c;
+    float a = dot(d, d), b = dot(m, d), cc = dot(m, m) - r * r;
+    if (cc <= 0.0f) return false; /* origin inside: handled by the caller's inside test */
+    if (b >= 0.0f) return false;  /* pointing away */
+    float disc = b * b - a * cc;
+    if (disc < 0.0f) return false;
+    float tt = (-b - sqrtf(disc)) / a;
+    if (tt < 0.0f || tt > tmax) return false;
+    v2 hp = m + tt * d;
+    float l = len(hp);
+    *t = tt;
+    *n = (l > SFP_EPS) ? (1.0f / l) * hp : neg((1.0f / sqrtf(a)) * d);
+    return true;
+}
+
+/* ray vs the segment p-q seen from its outward side `nrm` (one offset edge of a rounded shape) */
+SFP_HD bool ray_edge(v2 o, v2 d, v2 p, v2 q, v2 nrm, float tmax, float* t) {
+    float dn = dot(d, nrm);
+    if (dn >= 0.0f) return false; /* parallel or leaving */
+    float tt = dot(p - o, nrm) / dn;
+    if (tt < 0.0f || tt > tmax) return false;
+    v2 hp = o + tt * d;
+    v2 e = q - p;
+    float u = dot(hp - p, e);
+    if (u < 0.0f || u > dot(e, e)) return false;
+    *t = tt;
+    return true;
+}
+
+/* closest hit of a ray with one collider; true if hit within [0, tmax] */
+SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, float* t_out, v2* n_out) {
+    v2 x = mk(pose.x, pose.y), q = mk(pose.z, pose.w);
+    float r = shape.z;
+    uint32_t type = shape_type(shape);
+    float dl = sqrtf(dot(d, d));
+    if (!(dl > 0.0f)) return false;
+    v2 back = neg((1.0f / dl) * d);
+    if (type == SHAPE_CIRCLE) {
+        v2 m = o - x;
+        if (dot(m, m) <= r * r) {
+            *t_out = 0.0f;
+            *n_out = back;
+            return true;
+        }
+        return ray_disc(o, d, x, r, tmax, t_out, n_out);
+    }
+    Poly P = make_poly(x, q, shape, mk(0.0f, 0.0f));
+    /* origin inside the inflated core? */
+    float smax = -3.0e38f, dmin2 = 3.0e38f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (i < P.count) {
+            v2 a, b, nn;
+            poly_edge(P, i, &a, &b, &nn);
+            smax = fmaxf(smax, dot(nn, o - a));
+            v2 e = b - a;
+            float ee = dot(e, e);
+            float u = (ee > 0.0f) ? fminf(fmaxf(dot(o - a, e) / ee, 0.0f), 1.0f) : 0.0f;
+            v2 w = o - (a + u * e);
+            dmin2 = fminf(dmin2, dot(w, w));
+        }
+    }
+    bool inside_core = (P.count > 2) && smax <= 0.0f;
+    if (inside_core || dmin2 <= r * r) {
+        *t_out = 0.0f;
+        *n_out = back;
+        return true;
+    }
+    bool hit = false;
+    float best = tmax;
+    v2 bn = back;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (i < P.count) {
+            v2 a, b, nn;
+            poly_edge(P, i, &a, &b, &nn);
+            float tt;
+            v2 off = r * nn;
+            if (ray_edge(o, d, a + off, b + off, nn, best, &tt)) {
+                hit = true;
+                best = tt;
+                bn = nn;
+            }
+            v2 cn;
+            if (r > 0.0f && ray_disc(o, d, a, r, best, &tt, &cn)) {
+                hit = true;
+                best = tt;
+                bn = cn;
+            }
+        }
+    }
+    *t_out = best;
+    *n_out = bn;
+    return hit;
+}
+
+/* tight AABB of a collider at its current pose (no margin, no sweep) */
+SFP_HD f4 tight_aabb(f4 pose, f4 shape) {
+    f4 zero;
+    zero.x = zero.y = zero.z = zero.w = 0.0f;
+    return body_aabb(pose, zero, shape, 0.0f, 0.0f, 0.0f);
+}
+
+/* ------------------------------------------------------------------------------------- */
 /* Colouring (A8) — integer only                                                         */
 /* ------------------------------------------------------------------------------------- */
 #define SFP_MAX_COLOURS 64

@@ -574,6 +574,42 @@ int32_t sfp_ref_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t c
     return SFP_OK;
 }
 
+/* brute force over every body: the device's hash walk must find the same closest hit */
+int32_t sfp_ref_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits) {
+    if (!w || (m && (!rays || !hits))) return SFP_E_INVALID;
+    static_assert(sizeof(RayRec) == sizeof(SfpRay) && sizeof(RayHitRec) == sizeof(SfpRayHit), "");
+    for (uint32_t k = 0; k < m; ++k) {
+        const SfpRay& r = rays[k];
+        SfpRayHit best = {0xffffffffu, r.max_t, 0.0f, 0.0f};
+        v2 o = mk(r.ox, r.oy), d = mk(r.dx, r.dy);
+        for (uint32_t i = 0; i < w->n; ++i) {
+            if (((f2u(w->mat[i].w) & 0xffffu) & r.mask) == 0u) continue;
+            float t;
+            v2 n;
+            if (!ray_collider(o, d, r.max_t, w->pose[i], w->shape[i], &t, &n)) continue;
+            if (best.body == 0xffffffffu || t < best.t) best = SfpRayHit{i, t, n.x, n.y};
+        }
+        if (best.body == 0xffffffffu) best.t = 0.0f;
+        hits[k] = best;
+    }
+    return SFP_OK;
+}
+
+int32_t sfp_ref_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y,
+                           uint32_t mask, uint32_t* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    f4 box = {lo_x, lo_y, hi_x, hi_y};
+    uint32_t cnt = 0;
+    for (uint32_t i = 0; i < w->n; ++i) {
+        if (((f2u(w->mat[i].w) & 0xffffu) & mask) == 0u) continue;
+        if (!aabb_overlap(tight_aabb(w->pose[i], w->shape[i]), box)) continue;
+        if (cnt < cap) out[cnt] = i;
+        ++cnt;
+    }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
 int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
                               uint32_t m) {
     if (!w || (m && (!idx || !states))) return SFP_E_INVALID;

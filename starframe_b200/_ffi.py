@@ -76,6 +76,9 @@ EVENT_DTYPE = np.dtype(
         ("impulse", "<f4"), ("points", "<u4"),
     ]
 )
+RAY_DTYPE = np.dtype([("ox", "<f4"), ("oy", "<f4"), ("dx", "<f4"), ("dy", "<f4"), ("max_t", "<f4"),
+                      ("mask", "<u4"), ("reserved", "<u4", (2,))])
+RAY_HIT_DTYPE = np.dtype([("body", "<u4"), ("t", "<f4"), ("nx", "<f4"), ("ny", "<f4")])
 STATS_DTYPE = np.dtype(
     [
         ("frames", "<u8"), ("body_substeps", "<u8"),
@@ -94,12 +97,14 @@ assert PAIR_DTYPE.itemsize == 8
 assert CONTACT_DTYPE.itemsize == 60
 assert STATS_DTYPE.itemsize == 80
 assert EVENT_DTYPE.itemsize == 32
+assert RAY_DTYPE.itemsize == 32 and RAY_HIT_DTYPE.itemsize == 16
 
 # every symbol include/sfp.h declares for the product library (checked by the CPU tests)
 PRODUCT_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "get_contact_events", "update_bodies", "step_host", "alloc_host_states", "free_host_states",
+    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host",
+    "alloc_host_states", "free_host_states",
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
@@ -107,7 +112,8 @@ PRODUCT_SYMBOLS = [
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "get_contact_events", "update_bodies", "step_host", "last_step_ms", "backend", "brute_pairs",
+    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host", "last_step_ms",
+    "backend", "brute_pairs",
 ]
 
 
@@ -162,6 +168,8 @@ class Api:
             "get_contacts": [vp, vp, u32, C.POINTER(u32)],
             "get_contact_events": [vp, vp, u32, C.POINTER(u32)],
             "update_bodies": [vp, vp, vp, u32],
+            "ray_cast": [vp, vp, u32, vp],
+            "query_aabb": [vp, f32, f32, f32, f32, u32, vp, u32, C.POINTER(u32)],
             "alloc_host_states": [u32, C.POINTER(vp)],
             "free_host_states": [vp],
             "get_colours": [vp, vp, u32, vp, u32],
@@ -327,6 +335,19 @@ class World:
             self._check(self.api.fn("get_contact_events")(self.h, _ptr(out), n.value, C.byref(n)),
                         "events")
         return out
+
+    def ray_cast(self, rays: np.ndarray) -> np.ndarray:
+        r = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(r.shape[0], dtype=RAY_HIT_DTYPE)
+        self._check(self.api.fn("ray_cast")(self.h, _ptr(r), r.shape[0], _ptr(hits)), "ray_cast")
+        return hits
+
+    def query_aabb(self, lo, hi, mask: int = 0xFFFF) -> np.ndarray:
+        n = C.c_uint32(0)
+        out = np.zeros(max(self.n, 1), dtype=np.uint32)
+        self._check(self.api.fn("query_aabb")(self.h, lo[0], lo[1], hi[0], hi[1], mask, _ptr(out),
+                                              out.shape[0], C.byref(n)), "query_aabb")
+        return out[: n.value].copy()
 
     def update_bodies(self, idx: np.ndarray, states: np.ndarray):
         i = np.ascontiguousarray(idx, dtype=np.uint32)

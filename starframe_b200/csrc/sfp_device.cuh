@@ -102,7 +102,7 @@ __device__ __forceinline__ f2 ld2(const float2* p, uint32_t i) {
 // A2 broadphase
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_t tid,
-                                                 uint32_t nth) {
+                                                 uint32_t nth, bool new_frame = true) {
     for (uint32_t i = tid; i < c.n; i += nth) {
         f4 pose = ld4(c.pose, i), vel = ld4(c.vel, i), shape = ld4(c.shape, i);
         f2 mi = ld2(c.minv, i);
@@ -114,7 +114,7 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
         c.meta[i] = make_int4(x0, y0, (int)sfp::f2u(c.mat[i].w), dyn);
         c.cell_cnt[i] = (uint32_t)(x1 - x0 + 1) * (uint32_t)(y1 - y0 + 1);
     }
-    if (tid == 0) {
+    if (tid == 0 && new_frame) {
         // per-frame counters
         c.cnt->n_colours = 0;
         c.cnt->colour_rounds = 0;

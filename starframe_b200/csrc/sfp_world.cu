@@ -83,6 +83,87 @@ __global__ void k_serial_vel(Ctx c, float h, float rt) {
     if (threadIdx.x == 0 && blockIdx.x == 0) serial_solve_vel(c, vload(&c.cnt->n_colours), h, rt);
 }
 
+// ---- spatial queries on the device hash --------------------------------------------------------
+__global__ void __launch_bounds__(TPB) k_query_aabbs(Ctx c) {
+    stage_aabb_count(c, 0.0f, gtid(), gnth(), false);  // current poses, no sweep
+}
+
+// one thread per ray: DDA through the hash cells, exact ray / collider test per entry
+__global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __restrict__ rays,
+                                                  uint32_t m, sfp::RayHitRec* __restrict__ hits,
+                                                  float cell) {
+    const uint32_t E = c.cnt->n_entries;
+    for (uint32_t k = gtid(); k < m; k += gnth()) {
+        const sfp::RayRec r = rays[k];
+        const v2 o = sfp::mk(r.ox, r.oy), d = sfp::mk(r.dx, r.dy);
+        uint32_t best_body = 0xffffffffu;
+        float best_t = r.max_t;
+        v2 best_n = sfp::mk(0.0f, 0.0f);
+        int cx = sfp::cell_coord(o.x, c.inv_cell), cy = sfp::cell_coord(o.y, c.inv_cell);
+        const int sx = d.x > 0.0f ? 1 : -1, sy = d.y > 0.0f ? 1 : -1;
+        const float inf = 3.0e38f;
+        float tmx = d.x != 0.0f ? (((float)(cx + (sx > 0 ? 1 : 0))) * cell - o.x) / d.x : inf;
+        float tmy = d.y != 0.0f ? (((float)(cy + (sy > 0 ? 1 : 0))) * cell - o.y) / d.y : inf;
+        const float tdx = d.x != 0.0f ? fabsf(cell / d.x) : inf;
+        const float tdy = d.y != 0.0f ? fabsf(cell / d.y) : inf;
+        if (!(d.x != 0.0f || d.y != 0.0f)) {
+            hits[k] = sfp::RayHitRec{0xffffffffu, 0.0f, 0.0f, 0.0f};
+            continue;
+        }
+        for (int step = 0; step < 16384; ++step) {
+            const uint32_t key = sfp::cell_key(cx, cy);
+            uint32_t lo = 0, hi = E;  // lower bound of key among the sorted entries
+            while (lo < hi) {
+                uint32_t mid = (lo + hi) >> 1;
+                if (c.ekey0[mid] < key) lo = mid + 1;
+                else hi = mid;
+            }
+            for (uint32_t e = lo; e < E && c.ekey0[e] == key; ++e) {
+                const uint32_t b = c.eval0[e];
+                if ((((uint32_t)c.meta[b].z & 0xffffu) & r.mask) == 0u) continue;
+                float t;
+                v2 n;
+                if (!sfp::ray_collider(o, d, r.max_t, ld4(c.pose, b), ld4(c.shape, b), &t, &n))
+                    continue;
+                if (best_body == 0xffffffffu || t < best_t || (t == best_t && b < best_body)) {
+                    best_body = b;
+                    best_t = t;
+                    best_n = n;
+                }
+            }
+            const float t_exit = fminf(tmx, tmy);
+            if (best_body != 0xffffffffu && best_t <= t_exit) break;  // nothing nearer ahead
+            if (t_exit > r.max_t) break;
+            if (tmx < tmy) {
+                cx += sx;
+                tmx += tdx;
+            } else {
+                cy += sy;
+                tmy += tdy;
+            }
+            if (cx < SFP_CELL_MIN || cx > SFP_CELL_MAX || cy < SFP_CELL_MIN || cy > SFP_CELL_MAX) break;
+        }
+        hits[k] = sfp::RayHitRec{best_body, best_body == 0xffffffffu ? 0.0f : best_t, best_n.x,
+                                 best_n.y};
+    }
+}
+
+__global__ void __launch_bounds__(TPB) k_box_flags(Ctx c, float4 box, uint32_t mask,
+                                                   uint32_t* __restrict__ flags) {
+    f4 bx;
+    bx.x = box.x, bx.y = box.y, bx.z = box.z, bx.w = box.w;
+    for (uint32_t i = gtid(); i < c.n; i += gnth()) {
+        bool in = (((sfp::f2u(c.mat[i].w) & 0xffffu) & mask) != 0u) &&
+                  sfp::aabb_overlap(sfp::tight_aabb(ld4(c.pose, i), ld4(c.shape, i)), bx);
+        flags[i] = in ? 1u : 0u;
+    }
+}
+__global__ void __launch_bounds__(TPB) k_box_write(Ctx c, const uint32_t* __restrict__ off,
+                                                   uint32_t* __restrict__ out) {
+    for (uint32_t i = gtid(); i < c.n; i += gnth())
+        if (off[i + 1] != off[i]) out[off[i]] = i;
+}
+
 // ---- contact events: flag -> scan -> write, so only the events cross the bus ------------------
 __global__ void __launch_bounds__(TPB) k_event_flags(Ctx c, uint32_t* __restrict__ flags) {
     const uint32_t P = c.cnt->n_pairs;
@@ -348,6 +429,9 @@ struct SfpWorld {
     uint32_t *d_evt_flag = nullptr, *d_evt_off = nullptr;  // cap_pairs + 1 each
     sfp::EventRec* d_events = nullptr;                    // cap_pairs
     uint32_t* d_idx = nullptr;                            // cap_bodies (sfp_update_bodies)
+    sfp::RayRec* d_rays = nullptr;                        // ray_cap (grow-only)
+    sfp::RayHitRec* d_hits = nullptr;
+    uint32_t ray_cap = 0;
     float last_h = 0.0f;
     SfpBodyState* pin_state = nullptr;   // pinned host staging, cap_bodies states
     sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
@@ -728,6 +812,8 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->d_hist) cudaFree(w->d_hist);
     if (w->d_cnt) cudaFree(w->d_cnt);
     if (w->pin_state) cudaFreeHost(w->pin_state);
+    if (w->d_rays) cudaFree(w->d_rays);
+    if (w->d_hits) cudaFree(w->d_hits);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
     if (w->ev_bp) cudaEventDestroy(w->ev_bp);
@@ -1052,6 +1138,70 @@ int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap, 
         return x.a != y.a ? x.a < y.a : x.b < y.b;
     });
     std::memcpy(out, ev.data(), sizeof(SfpContactEvent) * m);
+    return SFP_OK;
+}
+
+int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits) {
+    if (!w || (m && (!rays || !hits))) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    static_assert(sizeof(sfp::RayRec) == sizeof(SfpRay) && sizeof(sfp::RayHitRec) == sizeof(SfpRayHit),
+                  "ray records mirror the ABI");
+    if (m == 0) return SFP_OK;
+    if (w->n == 0) {
+        for (uint32_t k = 0; k < m; ++k) hits[k] = SfpRayHit{0xffffffffu, 0.0f, 0.0f, 0.0f};
+        return SFP_OK;
+    }
+    CU(cudaSetDevice(w->device));
+    cudaStream_t st = w->stream;
+    if (m > w->ray_cap) {
+        CU(cudaStreamSynchronize(st));
+        if (w->d_rays) cudaFree(w->d_rays);
+        if (w->d_hits) cudaFree(w->d_hits);
+        w->d_rays = nullptr;
+        w->d_hits = nullptr;
+        w->ray_cap = 0;
+        CU(cudaMalloc(&w->d_rays, sizeof(sfp::RayRec) * (size_t)m));
+        CU(cudaMalloc(&w->d_hits, sizeof(sfp::RayHitRec) * (size_t)m));
+        w->ray_cap = m;
+    }
+    // spatial hash of the CURRENT poses (the frame's own hash is swept and one frame old);
+    // it reuses the broadphase buffers, which are scratch between frames
+    Ctx& c = w->ctx;
+    const uint32_t gb = blocks_for(w, w->n);
+    k_query_aabbs<<<gb, TPB, 0, st>>>(c);
+    CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
+                      &w->d_cnt->n_entries, st));
+    k_emit_entries<<<gb, TPB, 0, st>>>(c);
+    TRY(sort_entries(w));
+    CU(cudaMemcpyAsync(w->d_rays, rays, sizeof(SfpRay) * (size_t)m, cudaMemcpyHostToDevice, st));
+    k_ray_cast<<<blocks_for(w, m), TPB, 0, st>>>(c, w->d_rays, m, w->d_hits, w->p.cell_size);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(hits, w->d_hits, sizeof(SfpRayHit) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    Counters k;
+    TRY(read_counters(w, &k));
+    return check_overflow(w, k);
+}
+
+int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y, uint32_t mask,
+                       uint32_t* out, uint32_t cap, uint32_t* n_out) {
+    if (!w || !n_out || (cap && !out)) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    *n_out = 0;
+    if (w->n == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    cudaStream_t st = w->stream;
+    const uint32_t gb = blocks_for(w, w->n);
+    k_box_flags<<<gb, TPB, 0, st>>>(w->ctx, make_float4(lo_x, lo_y, hi_x, hi_y), mask, w->d_evt_flag);
+    CU(scan_exclusive(w->d_evt_flag, w->d_evt_off, &w->d_cnt->n_bodies, w->cap_bodies,
+                      w->d_scan_tiles, w->d_evt_flag + w->cap_pairs, st));
+    k_box_write<<<gb, TPB, 0, st>>>(w->ctx, w->d_evt_off, w->d_idx);
+    CU(cudaGetLastError());
+    uint32_t total = 0;
+    CU(cudaMemcpyAsync(&total, w->d_evt_flag + w->cap_pairs, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    *n_out = total;
+    const uint32_t mm = std::min(total, cap);
+    if (mm) CU(cudaMemcpy(out, w->d_idx, sizeof(uint32_t) * mm, cudaMemcpyDeviceToHost));
     return SFP_OK;
 }
 

@@ -1,0 +1,133 @@
+"""Spatial queries: ray casts and AABB queries.  CPU tier: closed-form
+answers on the oracle.  GPU tier: the device's hash walk returns exactly what the oracle's brute
+force over all bodies returns."""
+import math
+
+import numpy as np
+import pytest
+
+import starframe_b200 as sf
+from starframe_b200 import _ffi, scenes
+from starframe_b200._ffi import RAY_DTYPE, SHAPE_CAPSULE, SHAPE_CIRCLE, SHAPE_RECT
+
+NONE = 0xFFFFFFFF
+
+
+def body(shape, x, y, angle=0.0, hx=0.0, hy=0.0, r=0.0, **kw):
+    b = scenes.empty_bodies(1)
+    b["shape"], b["x"], b["y"], b["angle"] = shape, x, y, angle
+    b["hx"], b["hy"], b["radius"] = hx, hy, r
+    for k, v in kw.items():
+        b[k] = v
+    return b
+
+
+def ray(ox, oy, dx, dy, max_t=100.0, mask=0xFFFF):
+    r = np.zeros(1, dtype=RAY_DTYPE)
+    r["ox"], r["oy"], r["dx"], r["dy"], r["max_t"], r["mask"] = ox, oy, dx, dy, max_t, mask
+    return r
+
+
+def world(api, bodies):
+    w = sf.World(api, gravity_y=0.0)
+    w.upload_bodies(bodies)
+    return w
+
+
+def test_ray_known_answers(ref_api):
+    bodies = np.concatenate([
+        body(SHAPE_CIRCLE, 5.0, 0.0, r=1.0),                       # 0
+        body(SHAPE_RECT, 0.0, 5.0, hx=1.0, hy=0.5),                # 1 sharp box
+        body(SHAPE_CAPSULE, -5.0, 0.0, hx=1.0, r=0.5),             # 2 along x
+        body(SHAPE_RECT, 0.0, -5.0, hx=1.0, hy=1.0, r=0.5),        # 3 rounded box
+        body(SHAPE_CIRCLE, 9.0, 0.0, r=1.0, category=4),           # 4 behind 0, other layer
+    ])
+    w = world(ref_api, bodies)
+    rays = np.concatenate([
+        ray(0, 0, 1, 0),                   # circle 0 at x = 4
+        ray(0, 0, 0, 2),                   # box 1 bottom face at y = 4.5, direction length 2
+        ray(0, 0, -1, 0),                  # capsule 2 end cap at x = -3.5
+        ray(-5, 3, 0, -1),                 # capsule 2 side at y = 0.5
+        ray(3, -8, -1, 1),                 # rounded corner of 3: centre (1,-6), r 0.5
+        ray(5.2, 0.1, 1, 0),               # inside circle 0
+        ray(0, 0, 1, 0, max_t=3.5),        # too short
+        ray(0, 0, 1, 0, mask=4),           # only layer 4: passes 0, hits 4 at x = 8
+        ray(0, 0, 1, 1, max_t=50),         # nothing on the diagonal
+    ])
+    h = w.ray_cast(rays)
+    assert (h[0]["body"], h[0]["t"]) == (0, pytest.approx(4.0, abs=1e-6))
+    assert (h[0]["nx"], h[0]["ny"]) == pytest.approx((-1.0, 0.0), abs=1e-6)
+    assert (h[1]["body"], h[1]["t"]) == (1, pytest.approx(2.25, abs=1e-6))
+    assert (h[1]["nx"], h[1]["ny"]) == pytest.approx((0.0, -1.0), abs=1e-6)
+    assert (h[2]["body"], h[2]["t"]) == (2, pytest.approx(3.5, abs=1e-6))
+    assert (h[3]["body"], h[3]["t"]) == (2, pytest.approx(2.5, abs=1e-6))
+    assert (h[3]["nx"], h[3]["ny"]) == pytest.approx((0.0, 1.0), abs=1e-6)
+    # ray from (3,-8) along (-1,1) passes through (1,-6)'s disc: enters at distance 0.5 before it
+    t4 = 2.0 - 0.5 / math.sqrt(2.0)
+    assert (h[4]["body"], h[4]["t"]) == (3, pytest.approx(t4, abs=1e-5))
+    s = math.sqrt(0.5)
+    assert (h[4]["nx"], h[4]["ny"]) == pytest.approx((s, -s), abs=1e-5)
+    assert (h[5]["body"], h[5]["t"]) == (0, 0.0)
+    assert (h[5]["nx"], h[5]["ny"]) == pytest.approx((-1.0, 0.0), abs=1e-6)
+    assert h[6]["body"] == NONE
+    assert (h[7]["body"], h[7]["t"]) == (4, pytest.approx(8.0, abs=1e-6))
+    assert h[8]["body"] == NONE
+
+
+def test_query_aabb_known_answers(ref_api):
+    bodies = np.concatenate([
+        body(SHAPE_CIRCLE, 0.0, 0.0, r=1.0),
+        body(SHAPE_RECT, 3.0, 0.0, angle=math.pi / 4, hx=1.0, hy=1.0),  # rotated: half extent 1.414
+        body(SHAPE_CAPSULE, 0.0, 4.0, hx=1.0, r=0.25, category=2),
+    ])
+    w = world(ref_api, bodies)
+    assert w.query_aabb((0.9, -0.1), (1.7, 0.1)).tolist() == [0, 1]   # 3 - 1.414 = 1.586 < 1.7
+    assert w.query_aabb((1.1, -0.1), (1.5, 0.1)).tolist() == []
+    assert w.query_aabb((-5, -5), (5, 5)).tolist() == [0, 1, 2]
+    assert w.query_aabb((-5, -5), (5, 5), mask=2).tolist() == [2]
+
+
+def random_rays(n, seed, extent_x, extent_y):
+    rng = np.random.default_rng(seed)
+    r = np.zeros(n, dtype=RAY_DTYPE)
+    r["ox"] = rng.uniform(-extent_x, extent_x, n)
+    r["oy"] = rng.uniform(-1.0, extent_y, n)
+    ang = rng.uniform(0, 2 * np.pi, n)
+    ln = rng.uniform(0.2, 3.0, n)
+    r["dx"], r["dy"] = np.cos(ang) * ln, np.sin(ang) * ln
+    r["max_t"] = rng.uniform(0.5, 40.0, n)
+    r["mask"] = np.where(rng.uniform(size=n) < 0.8, 0xFFFF, 1 << rng.integers(0, 4, n))
+    r[: n // 20]["dx"] = 0.0  # axis-aligned rays too
+    r[n // 20: n // 10]["dy"] = 0.0
+    return r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene", ["pile", "soup"])
+def test_ray_cast_and_box_query_match_oracle(gpu_api, ref_api, scene):
+    if scene == "pile":
+        b, j = scenes.mixed_pile(4000)
+        ex, ey = 26.0, 30.0
+    else:
+        b, j = scenes.random_soup(900, 5)
+        ex, ey = 12.0, 22.0
+    g, r = sf.World(gpu_api), sf.World(ref_api)
+    for w in (g, r):
+        w.upload_bodies(b)
+        w.set_joints(j)
+    rays = random_rays(3000, 11, ex, ey)
+    for frames in (0, 40, 80):
+        for _ in range(frames):
+            g.step()
+            r.step()
+        hg, hr = g.ray_cast(rays), r.ray_cast(rays)
+        assert (hr["body"] != NONE).sum() > 500
+        assert hg.tobytes() == hr.tobytes()
+        for lo, hi in (((-3.0, 0.0), (2.0, 4.0)), ((-50.0, -5.0), (50.0, 0.4)), ((5.0, 5.0), (5.1, 5.1))):
+            assert np.array_equal(g.query_aabb(lo, hi), r.query_aabb(lo, hi))
+    # a query must not disturb the simulation: keep stepping, still bit-identical
+    for _ in range(10):
+        g.step()
+        r.step()
+    assert g.download_bodies().tobytes() == r.download_bodies().tobytes()
+    assert np.array_equal(g.get_pairs(), r.get_pairs())
