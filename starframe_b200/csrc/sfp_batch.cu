@@ -16,6 +16,7 @@
 //
 // Reference: none for batching — north_star: "batched independent worlds are partitioned across
 // the 8 GPUs of one box, with NCCL used only to gather statistics".
+#include <cuda_pipeline.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -274,6 +275,49 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         return r ? (__ffsll((long long)r) - 1) : 64;
     };
     const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    // colour order as a list, and a per-thread shared-memory slot into which the contact record
+    // of this thread's first item of the NEXT colour is copied asynchronously (cp.async, no
+    // registers held across the barrier): after the barrier only shared-memory reads remain
+    // before the solve, instead of two dependent L2 / HBM round trips.
+    __shared__ uint8_t s_order[SFP_MAX_COLOURS];
+    __shared__ uint32_t s_nord;
+    __shared__ float4 s_rec[4][BTPB];
+    __shared__ float4 s_lam[BTPB];
+    __shared__ uint2 s_pair[BTPB];
+    if (tid == 0) {
+        uint32_t k = 0;
+        for (int pass = 0; pass < 2; ++pass) {
+            const unsigned long long m = pass ? small : big;
+            for (int col = next_bit(m, -1); col < 64; col = next_bit(m, col)) s_order[k++] = (uint8_t)col;
+        }
+        s_nord = k;
+    }
+    __syncthreads();
+    const uint32_t nord = s_nord;
+    auto issue = [&](uint32_t oi, bool with_lam) {
+        if (oi >= nord) return false;
+        const uint32_t col = s_order[oi];
+        const uint32_t k = c.cnt->pair_col_off[col] + tid;
+        if (k >= c.cnt->pair_col_off[col + 1]) return false;
+        __pipeline_memcpy_async(&s_rec[0][tid], &c.ca[k], 16);
+        __pipeline_memcpy_async(&s_rec[1][tid], &c.cb[k], 16);
+        __pipeline_memcpy_async(&s_rec[2][tid], &c.cp0[k], 16);
+        __pipeline_memcpy_async(&s_rec[3][tid], &c.cp1[k], 16);
+        __pipeline_memcpy_async(&s_pair[tid], &c.pairs[k], 8);
+        if (with_lam) __pipeline_memcpy_async(&s_lam[tid], &c.lam[k], 16);
+        __pipeline_commit();
+        return true;
+    };
+    auto take = [&]() {
+        PairRec r;
+        r.p = s_pair[tid];
+        float4 a = s_rec[0][tid], b = s_rec[1][tid], q0 = s_rec[2][tid], q1 = s_rec[3][tid];
+        r.ca.x = a.x, r.ca.y = a.y, r.ca.z = a.z, r.ca.w = a.w;
+        r.cb.x = b.x, r.cb.y = b.y, r.cb.z = b.z, r.cb.w = b.w;
+        r.q0.x = q0.x, r.q0.y = q0.y, r.q0.z = q0.z, r.q0.w = q0.w;
+        r.q1.x = q1.x, r.q1.y = q1.y, r.q1.z = q1.z, r.q1.w = q1.w;
+        return r;
+    };
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
         __syncthreads();
@@ -281,10 +325,16 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         stage_narrowphase(c, tid, nth);
         __syncthreads();
         LAP(5);
-        for (int pass = 0; pass < 2; ++pass) {
-            const unsigned long long m = pass ? small : big;
-            for (int col = next_bit(m, -1); col < 64; col = next_bit(m, col)) {
-                stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth);
+        {
+            bool have = issue(0, false);
+            for (uint32_t oi = 0; oi < nord; ++oi) {
+                const uint32_t col = s_order[oi];
+                if (have) {
+                    __pipeline_wait_prior(0);
+                    solve_pos_pair(c, c.cnt->pair_col_off[col] + tid, take());
+                }
+                stage_solve_pos(c, col, inv_h2, tid, nth, have);
+                have = issue(oi + 1, false);
                 __syncthreads();
             }
         }
@@ -296,10 +346,19 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         stage_derive(c, inv_h, tid, nth);
         __syncthreads();
         LAP(7);
-        for (int pass = 0; pass < 2; ++pass) {
-            const unsigned long long m = pass ? small : big;
-            for (int col = next_bit(m, -1); col < 64; col = next_bit(m, col)) {
-                stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth);
+        {
+            bool have = issue(0, true);
+            for (uint32_t oi = 0; oi < nord; ++oi) {
+                const uint32_t col = s_order[oi];
+                if (have) {
+                    __pipeline_wait_prior(0);
+                    float4 l = s_lam[tid];
+                    f4 lam;
+                    lam.x = l.x, lam.y = l.y, lam.z = l.z, lam.w = l.w;
+                    solve_vel_pair(c, c.cnt->pair_col_off[col] + tid, take(), lam, h, rest_threshold);
+                }
+                stage_solve_vel(c, col, h, rest_threshold, tid, nth, have);
+                have = issue(oi + 1, true);
                 __syncthreads();
             }
         }
