@@ -53,29 +53,36 @@ class ClockSampler:
     def __init__(self, index: int):
         self.index = index
         self.rows = []
-        self._stop = threading.Event()
+        self._proc = None
         self._t = threading.Thread(target=self._run, daemon=True)
 
     def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(
-                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                     "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                parts = [x.strip() for x in out.strip().split(",")]
+        # one long-lived nvidia-smi streaming a line every 50 ms (start-up of a fresh
+        # nvidia-smi per sample costs more than the whole timed region)
+        try:
+            self._proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "50"], stdout=subprocess.PIPE, text=True)
+            for line in self._proc.stdout:
+                parts = [x.strip() for x in line.strip().split(",")]
                 if len(parts) >= 6:
                     self.rows.append(parts)
-            except Exception:
-                pass
-            self._stop.wait(0.2)
+        except Exception:
+            pass
 
     def __enter__(self):
         self._t.start()
+        time.sleep(0.25)  # let the first samples arrive before the timed region starts
+        self.rows.clear()
         return self
 
     def __exit__(self, *a):
-        self._stop.set()
-        self._t.join(timeout=6)
+        try:
+            if self._proc:
+                self._proc.terminate()
+        except Exception:
+            pass
+        self._t.join(timeout=3)
 
     def summary(self):
         if not self.rows:
@@ -229,7 +236,61 @@ def run_single(args, rank, world_size):
     }
     if rank == 0 and not args.no_cpu_baseline and world_size == 1:
         out["cpu_baseline"] = cpu_baseline_single(bodies, joints, settled, args.cpu_frames)
+    if rank == 0 and world_size == 1 and not args.no_other_configs and args.workload == "pile100k":
+        # the other single-GPU configs of BASELINE.json, measured the same way (short runs);
+        # they are parity-test cases first, these lines are context for the headline
+        del w
+        out["other_configs"] = {name: quick_config(name, args) for name in ("circles10k", "ropes2k")}
+        out["other_configs"]["worlds512_1gpu"] = quick_worlds(args)
     return out
+
+
+def quick_config(name, args, frames=30):
+    import torch
+
+    import starframe_b200 as sf
+
+    bodies, joints = make_scene(name)
+    w = sf.World(sf.product_api(), device=torch.cuda.current_device())
+    w.upload_bodies(bodies)
+    w.set_joints(joints)
+    for _ in range(args.settle):
+        w.step(DT, SUBSTEPS)
+    w.sync()
+    t = 0.0
+    for _ in range(frames):
+        w.step(DT, SUBSTEPS)
+        w.sync()
+        t += w.last_step_ms()
+    st = w.stats()
+    n = len(bodies)
+    return {"bodies": n, "value": n * SUBSTEPS * frames / (t * 1e-3), "unit": "body-substeps/s",
+            "ms_per_step": t / frames, "pairs_per_body": st["n_pairs"] / n,
+            "contacts_per_body": st["n_contacts"] / n, "joints_per_body": st["n_joints"] / n,
+            "colours": st["n_colours"]}
+
+
+def quick_worlds(args, frames=20):
+    import torch
+
+    import starframe_b200 as sf
+    from starframe_b200 import scenes
+
+    nw = args.worlds_per_gpu
+    b = sf.Batch(sf.product_api(), nw, BODIES_PER_WORLD, device=torch.cuda.current_device())
+    b.upload(scenes.worlds(nw, BODIES_PER_WORLD))
+    for _ in range(args.settle):
+        b.step(DT, SUBSTEPS)
+    b.sync()
+    t = 0.0
+    for _ in range(frames):
+        b.step(DT, SUBSTEPS)
+        b.sync()
+        t += b.last_step_ms()
+    n = nw * BODIES_PER_WORLD
+    return {"bodies": n, "worlds": nw, "value": n * SUBSTEPS * frames / (t * 1e-3),
+            "unit": "body-substeps/s", "ms_per_step": t / frames,
+            "note": "the per-GPU share of the N>1 workload, for the scaling curve's N=1 point"}
 
 
 def cpu_baseline_single(bodies, joints, settled_state, frames):
@@ -465,7 +526,7 @@ def world_range(rank, worlds_per_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=60)
+    ap.add_argument("--steps", type=int, default=120)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None)
@@ -473,6 +534,7 @@ def main():
     ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
     ap.add_argument("--cpu-frames", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
