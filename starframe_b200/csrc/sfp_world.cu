@@ -422,6 +422,14 @@ struct SfpWorld {
     unsigned long long* d_tab[2] = {nullptr, nullptr};
     uint32_t tab_slots = 0;
     uint32_t colour_age = 0;  // colourings since the last upload (warm start, sfp_math.h)
+    // the frame's launch sequence captured as CUDA graphs (one per (dt, substeps, table parity,
+    // warm) combination); falls back to plain launches if capture is refused
+    struct FrameGraph {
+        cudaGraphExec_t exec = nullptr;
+        uint32_t dt_bits = 0, substeps = 0, parity = 0, warm = 0, launches = 0;
+    } graphs[4];
+    uint32_t graph_next = 0;
+    bool graphs_ok = true, capturing = false;
     Counters* d_cnt = nullptr;
     // host mirrors
     std::vector<sfp::f2> h_minv;
@@ -607,7 +615,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     k_pair_write<<<ge, TPB, 0, st>>>(c);
     CU(cudaGetLastError());
     w->launches += 4 + 3 + 3 + 12;
-    if (mark) CU(cudaEventRecord(w->ev_bp, st));
+    if (mark) CU(cudaEventRecordWithFlags(w->ev_bp, st, w->capturing ? cudaEventRecordExternal : 0));
 
     // warm start: read last frame's table, build this frame's in the other one
     c.warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
@@ -650,7 +658,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
     w->launches += 7 + (w->nj ? 3 : 0);
-    if (mark) CU(cudaEventRecord(w->ev_col, st));
+    if (mark) CU(cudaEventRecordWithFlags(w->ev_col, st, w->capturing ? cudaEventRecordExternal : 0));
     return SFP_OK;
 }
 
@@ -710,6 +718,63 @@ int frame(SfpWorld* w, float dt, uint32_t substeps) {
     }
     TRY(broadphase_and_colour(w, dt));
     return run_substeps(w, h, substeps);
+}
+
+void drop_graphs(SfpWorld* w) {
+    for (auto& g : w->graphs) {
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+        g = SfpWorld::FrameGraph();
+    }
+}
+
+// one cudaGraphLaunch per frame instead of ~30 kernel launches
+int frame_graphed(SfpWorld* w, float dt, uint32_t substeps) {
+    const bool direct = !w->graphs_ok || w->n == 0 ||
+                        (w->p.flags & (SFP_FLAG_MULTI_KERNEL | SFP_FLAG_BROADPHASE_EVERY_SUBSTEP));
+    if (direct) return frame(w, dt, substeps);
+    const uint32_t dt_bits = sfp::f2u(dt), parity = w->colour_age & 1u;
+    const uint32_t warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+    for (auto& g : w->graphs)
+        if (g.exec && g.dt_bits == dt_bits && g.substeps == substeps && g.parity == parity &&
+            g.warm == warm) {
+            CU(cudaGraphLaunch(g.exec, w->stream));
+            w->colour_age += 1;
+            w->launches = g.launches;
+            return SFP_OK;
+        }
+    // capture
+    const uint32_t age0 = w->colour_age;
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(w->stream, cudaStreamCaptureModeThreadLocal);
+    int rc = SFP_E_CUDA;
+    if (e == cudaSuccess) {
+        w->capturing = true;
+        rc = frame(w, dt, substeps);
+        w->capturing = false;
+        e = cudaStreamEndCapture(w->stream, &graph);
+    }
+    cudaGraphExec_t exec = nullptr;
+    if (rc == SFP_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (rc != SFP_OK || e != cudaSuccess || !exec) {
+        // capture refused (e.g. a driver without cooperative-launch capture): plain launches
+        cudaGetLastError();
+        w->graphs_ok = false;
+        w->sticky = SFP_OK;
+        w->err.clear();
+        w->colour_age = age0;
+        return frame(w, dt, substeps);
+    }
+    auto& slot = w->graphs[w->graph_next++ & 3u];
+    if (slot.exec) cudaGraphExecDestroy(slot.exec);
+    slot.exec = exec;
+    slot.dt_bits = dt_bits;
+    slot.substeps = substeps;
+    slot.parity = parity;
+    slot.warm = warm;
+    slot.launches = w->launches;
+    CU(cudaGraphLaunch(exec, w->stream));
+    return SFP_OK;
 }
 
 int read_counters(SfpWorld* w, Counters* out) {
@@ -806,6 +871,7 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (!w) return SFP_OK;
     cudaSetDevice(w->device);
     if (w->stream) cudaStreamSynchronize(w->stream);
+    drop_graphs(w);
     free_bag(w->body_allocs);
     free_bag(w->joint_allocs);
     if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
@@ -839,6 +905,7 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
         return SFP_E_INVALID;
     }
     CU(cudaSetDevice(w->device));
+    drop_graphs(w);
     TRY(ensure_body_capacity(w, n));
     std::vector<sfp::f4> pose(n), vel(n);
     w->h_minv.resize(n);
@@ -888,6 +955,7 @@ int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
             return SFP_E_INVALID;
         }
     CU(cudaSetDevice(w->device));
+    drop_graphs(w);
     TRY(ensure_joint_capacity(w, nj));
     std::vector<uint2> jb(nj);
     std::vector<float4> ja(nj), jp(nj);
@@ -922,7 +990,7 @@ int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps) {
     CU(cudaSetDevice(w->device));
     CU(cudaEventRecord(w->ev0, w->stream));
     w->launches = 0;
-    int rc = frame(w, dt, substeps);
+    int rc = frame_graphed(w, dt, substeps);
     if (rc != SFP_OK) return rc;
     CU(cudaEventRecord(w->ev1, w->stream));
     w->timed = true;
