@@ -145,7 +145,8 @@ inline cudaError_t scan_exclusive(const uint32_t* in, uint32_t* out, const uint3
 }
 
 // ---- radix sort pass ----------------------------------------------------------------------
-// hist layout: hist[digit * n_blocks + block]  (digit-major so one scan yields global bases)
+// hist layout: hist[block * 256 + digit]; every scatter block derives its own global bases from
+// it (a coalesced sweep over the live blocks + one block scan), so no separate scan launch
 static __global__ void __launch_bounds__(RADIX_THREADS)
 k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_ptr, int shift,
              uint32_t* __restrict__ hist) {
@@ -162,55 +163,7 @@ k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_p
         }
     }
     __syncthreads();
-    hist[threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
-}
-
-// one block: exclusive scan over the digit-major histogram, restricted to the blocks that hold
-// live keys (the grid is sized for the buffer capacity, the live count is usually far smaller).
-// Warp w owns digits w, w+32, ...: it sums each of its rows, the 256 row sums are scanned by
-// warp 0, then every warp rewrites its rows as running offsets.
-static __global__ void __launch_bounds__(1024)
-k_radix_scan(uint32_t* __restrict__ hist, uint32_t n_blocks, const uint32_t* __restrict__ n_ptr) {
-    __shared__ uint32_t row_base[RADIX_BINS];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t n = *n_ptr;
-    const uint32_t live = min(n_blocks, (n + RADIX_TILE - 1) / RADIX_TILE);
-    for (int d = warp; d < RADIX_BINS; d += 32) {
-        const uint32_t* row = hist + (size_t)d * n_blocks;
-        uint32_t s = 0;
-        for (uint32_t b = lane; b < live; b += 32) s += row[b];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) row_base[d] = s;
-    }
-    __syncthreads();
-    if (warp == 0) {
-        // exclusive scan of 256 row sums: 8 consecutive per lane
-        uint32_t v[8], s = 0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            v[k] = row_base[lane * 8 + k];
-            s += v[k];
-        }
-        uint32_t ex = warp_incl_scan(s, lane) - s;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            row_base[lane * 8 + k] = ex;
-            ex += v[k];
-        }
-    }
-    __syncthreads();
-    for (int d = warp; d < RADIX_BINS; d += 32) {
-        uint32_t* row = hist + (size_t)d * n_blocks;
-        uint32_t run = row_base[d];
-        for (uint32_t b0 = 0; b0 < live; b0 += 32) {
-            uint32_t b = b0 + lane;
-            uint32_t v = (b < live) ? row[b] : 0u;
-            uint32_t inc = warp_incl_scan(v, lane);
-            if (b < live) row[b] = run + inc - v;
-            run += __shfl_sync(0xffffffffu, inc, 31);
-        }
-    }
+    hist[blockIdx.x * RADIX_BINS + threadIdx.x] = h[threadIdx.x];
 }
 
 // stable scatter.  vals_in == nullptr means "value = source index" (used to build permutations)
@@ -221,6 +174,7 @@ k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
                 const uint32_t* __restrict__ hist_scanned) {
     __shared__ uint32_t wcnt[RADIX_WARPS][RADIX_BINS];
     __shared__ uint32_t gbase[RADIX_BINS];
+    __shared__ uint32_t scan_sm[9];
     const uint32_t n = *n_ptr;
     const uint32_t base = blockIdx.x * RADIX_TILE;
     if (base >= n) return;
@@ -260,7 +214,19 @@ k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
             wcnt[w][threadIdx.x] = run;
             run += t;
         }
-        gbase[threadIdx.x] = hist_scanned[threadIdx.x * gridDim.x + blockIdx.x];
+        // global base of (this block, digit): all keys with a smaller digit, plus the keys with
+        // this digit in earlier blocks
+        const uint32_t live = (n + RADIX_TILE - 1) / RADIX_TILE;
+        uint32_t before = 0, total = 0;
+#pragma unroll 8
+        for (uint32_t b = 0; b < live; ++b) {
+            uint32_t v = hist_scanned[b * RADIX_BINS + threadIdx.x];
+            total += v;
+            before += (b < blockIdx.x) ? v : 0u;
+        }
+        uint32_t all;
+        uint32_t ex = block_excl_scan(total, &all, scan_sm);
+        gbase[threadIdx.x] = ex + before;
     }
     __syncthreads();
 #pragma unroll
@@ -283,7 +249,6 @@ inline cudaError_t radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, 
                               uint32_t* hist, cudaStream_t st) {
     uint32_t nb = radix_blocks(cap);
     k_radix_hist<<<nb, RADIX_THREADS, 0, st>>>(keys_in, n_ptr, shift, hist);
-    k_radix_scan<<<1, 1024, 0, st>>>(hist, nb, n_ptr);
     k_radix_scatter<<<nb, RADIX_THREADS, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n_ptr,
                                                   shift, hist);
     return cudaGetLastError();

@@ -614,7 +614,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       &w->d_cnt->n_pairs, st));
     k_pair_write<<<ge, TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 4 + 3 + 3 + 12;
+    w->launches += 4 + 3 + 3 + 8;
     if (mark) CU(cudaEventRecordWithFlags(w->ev_bp, st, w->capturing ? cudaEventRecordExternal : 0));
 
     // warm start: read last frame's table, build this frame's in the other one
@@ -657,7 +657,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       0, w->d_hist, st));
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 7 + (w->nj ? 3 : 0);
+    w->launches += 5 + (w->nj ? 2 : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_col, st, w->capturing ? cudaEventRecordExternal : 0));
     return SFP_OK;
 }
