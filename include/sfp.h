@@ -53,8 +53,22 @@ enum {
 enum {
     SFP_SHAPE_CIRCLE = 0,  /* point core + radius                                        */
     SFP_SHAPE_CAPSULE = 1, /* segment core (-hx,0)..(+hx,0) in body frame + radius       */
-    SFP_SHAPE_RECT = 2     /* rectangle core [-hx,hx]x[-hy,hy] + rounding radius         */
+    SFP_SHAPE_RECT = 2,    /* rectangle core [-hx,hx]x[-hy,hy] + rounding radius         */
+    SFP_SHAPE_POLYGON = 3  /* convex polygon core (3..8 vertices) + rounding radius: the
+                              vertices come from the table set with sfp_set_polygons;
+                              SfpBodyDesc.shape = SFP_SHAPE_POLYGON | (table index << 8);
+                              hx, hy are ignored                                          */
 };
+#define SFP_POLYGON_MAX_VERTS 8
+
+/* one entry of the polygon table: body-frame vertices, counter-clockwise, strictly convex, with
+ * the centroid at the origin (within 1e-3 of the polygon's size) */
+typedef struct SfpPolygon {
+    uint32_t count; /* 3..8 */
+    uint32_t reserved;
+    float x[SFP_POLYGON_MAX_VERTS];
+    float y[SFP_POLYGON_MAX_VERTS];
+} SfpPolygon; /* 72 bytes */
 
 enum {
     SFP_BODY_STATIC = 1u /* infinite mass; never moved by the solver */
@@ -198,6 +212,11 @@ SFP_API int32_t sfp_destroy(SfpWorld* w);
  * step (AoS in, converted to SoA device buffers inside).  Replaces all bodies. */
 SFP_API int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n);
 
+/* Replaces: the vertex data of the reference's convex-polygon colliders (reference file:line
+ * unavailable).  Replaces the whole table; call it BEFORE uploading bodies that use
+ * SFP_SHAPE_POLYGON.  Bodies already uploaded keep the indices they were given. */
+SFP_API int32_t sfp_set_polygons(SfpWorld* w, const SfpPolygon* polys, uint32_t n);
+
 /* Replaces: registration of the reference's distance / rope constraints. Replaces all joints. */
 SFP_API int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n);
 
@@ -314,6 +333,7 @@ SFP_API int32_t sfp_ref_create(const SfpParams* params, SfpWorld** out);
 SFP_API int32_t sfp_ref_destroy(SfpWorld* w);
 SFP_API int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n);
 SFP_API int32_t sfp_ref_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t n);
+SFP_API int32_t sfp_ref_set_polygons(SfpWorld* w, const SfpPolygon* polys, uint32_t n);
 SFP_API int32_t sfp_ref_step(SfpWorld* w, float dt, uint32_t substeps);
 SFP_API int32_t sfp_ref_sync(SfpWorld* w);
 SFP_API int32_t sfp_ref_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n);

@@ -39,8 +39,77 @@ inline bool params_valid(const SfpParams& p) {
            p.solver_order <= SFP_ORDER_REFERENCE;
 }
 
-inline bool desc_valid(const SfpBodyDesc& d) {
-    if (d.shape > SFP_SHAPE_RECT) return false;
+/* host copy of the polygon table: validated input + derived records */
+struct PolyTable {
+    std::vector<SfpPolygon> polys;
+    std::vector<f4> recs;      /* 8 f4 per polygon: vertices then edge normals (device layout) */
+    std::vector<float> bound;  /* largest vertex distance from the origin */
+    std::vector<double> area, perimeter, inertia_per_density; /* of the core polygon */
+};
+
+/* validates and derives; returns the index of the first bad polygon or -1 */
+inline long build_poly_table(const SfpPolygon* polys, uint32_t n, PolyTable* t) {
+    t->polys.assign(polys, polys + n);
+    t->recs.assign((size_t)n * 8u, f4{0.0f, 0.0f, 0.0f, 0.0f});
+    t->bound.assign(n, 0.0f);
+    t->area.assign(n, 0.0);
+    t->perimeter.assign(n, 0.0);
+    t->inertia_per_density.assign(n, 0.0);
+    for (uint32_t k = 0; k < n; ++k) {
+        const SfpPolygon& p = polys[k];
+        if (p.count < 3 || p.count > SFP_POLYGON_MAX_VERTS) return k;
+        double area2 = 0.0, cx = 0.0, cy = 0.0, inert = 0.0, per = 0.0;
+        float bound = 0.0f;
+        for (uint32_t i = 0; i < p.count; ++i) {
+            uint32_t j = (i + 1) % p.count, l = (i + 2) % p.count;
+            if (!std::isfinite(p.x[i]) || !std::isfinite(p.y[i])) return k;
+            double ex = (double)p.x[j] - p.x[i], ey = (double)p.y[j] - p.y[i];
+            double fx = (double)p.x[l] - p.x[j], fy = (double)p.y[l] - p.y[j];
+            if (!(ex * fy - ey * fx > 0.0)) return k; /* not CCW / not strictly convex */
+            double cr = (double)p.x[i] * p.y[j] - (double)p.x[j] * p.y[i];
+            area2 += cr;
+            cx += (p.x[i] + p.x[j]) * cr;
+            cy += (p.y[i] + p.y[j]) * cr;
+            inert += cr * ((double)p.x[i] * p.x[i] + (double)p.x[i] * p.x[j] + (double)p.x[j] * p.x[j] +
+                           (double)p.y[i] * p.y[i] + (double)p.y[i] * p.y[j] + (double)p.y[j] * p.y[j]);
+            per += std::sqrt(ex * ex + ey * ey);
+            bound = std::max(bound, sqrtf(p.x[i] * p.x[i] + p.y[i] * p.y[i]));
+        }
+        if (!(area2 > 0.0)) return k;
+        cx /= 3.0 * area2;
+        cy /= 3.0 * area2;
+        if (std::sqrt(cx * cx + cy * cy) > 1.0e-3 * bound) return k; /* centroid must be the origin */
+        t->bound[k] = bound;
+        t->area[k] = 0.5 * area2;
+        t->perimeter[k] = per;
+        t->inertia_per_density[k] = inert / 12.0;
+        /* device records: vertices (pairs), then unit edge normals; unused slots repeat */
+        float vx[8], vy[8], nx[8], ny[8];
+        for (uint32_t i = 0; i < 8; ++i) {
+            uint32_t a = i % p.count, b = (a + 1) % p.count;
+            vx[i] = p.x[a];
+            vy[i] = p.y[a];
+            float ex = p.x[b] - p.x[a], ey = p.y[b] - p.y[a];
+            float inv = 1.0f / sqrtf(ex * ex + ey * ey);
+            nx[i] = ey * inv;
+            ny[i] = -ex * inv;
+        }
+        for (uint32_t i = 0; i < 4; ++i) {
+            t->recs[(size_t)k * 8 + i] = f4{vx[2 * i], vy[2 * i], vx[2 * i + 1], vy[2 * i + 1]};
+            t->recs[(size_t)k * 8 + 4 + i] = f4{nx[2 * i], ny[2 * i], nx[2 * i + 1], ny[2 * i + 1]};
+        }
+    }
+    return -1;
+}
+
+inline bool desc_valid(const SfpBodyDesc& d, const PolyTable* polys = nullptr) {
+    const uint32_t type = d.shape & 0xffu;
+    if (type > SFP_SHAPE_POLYGON) return false;
+    if (type == SFP_SHAPE_POLYGON) {
+        if (!polys || (d.shape >> 8) >= polys->polys.size()) return false;
+    } else if (d.shape >> 8) {
+        return false;
+    }
     const float f[] = {d.x, d.y, d.angle, d.vx, d.vy, d.omega, d.hx, d.hy, d.radius,
                        d.density, d.mu_s, d.mu_d, d.restitution};
     for (float v : f)
@@ -51,16 +120,17 @@ inline bool desc_valid(const SfpBodyDesc& d) {
     if (!is_static && !(d.density > 0.0f)) return false;
     /* a dynamic collider needs a positive area */
     if (!is_static) {
-        if (d.shape == SFP_SHAPE_CIRCLE && !(d.radius > 0.0f)) return false;
-        if (d.shape == SFP_SHAPE_CAPSULE && !(d.radius > 0.0f)) return false;
-        if (d.shape == SFP_SHAPE_RECT && !((d.hx + d.radius) > 0.0f && (d.hy + d.radius) > 0.0f))
+        if (type == SFP_SHAPE_CIRCLE && !(d.radius > 0.0f)) return false;
+        if (type == SFP_SHAPE_CAPSULE && !(d.radius > 0.0f)) return false;
+        if (type == SFP_SHAPE_RECT && !((d.hx + d.radius) > 0.0f && (d.hy + d.radius) > 0.0f))
             return false;
     }
     return true;
 }
 
 /* solid-shape mass and moment of inertia about the centre (double, then rounded once) */
-inline void mass_properties(const SfpBodyDesc& d, float* inv_mass, float* inv_inertia) {
+inline void mass_properties(const SfpBodyDesc& d, float* inv_mass, float* inv_inertia,
+                            const PolyTable* polys = nullptr) {
     if (d.flags & SFP_BODY_STATIC) {
         *inv_mass = 0.0f;
         *inv_inertia = 0.0f;
@@ -68,7 +138,14 @@ inline void mass_properties(const SfpBodyDesc& d, float* inv_mass, float* inv_in
     }
     const double pi = 3.14159265358979323846;
     double rho = d.density, r = d.radius, m = 0.0, I = 0.0;
-    if (d.shape == SFP_SHAPE_CIRCLE) {
+    if ((d.shape & 0xffu) == SFP_SHAPE_POLYGON) {
+        /* core polygon exactly; the rounding rim (perimeter * r + pi r^2) adds mass, and the
+         * inertia is scaled by the same ratio */
+        const uint32_t k = d.shape >> 8;
+        double core = polys->area[k], rim = polys->perimeter[k] * r + pi * r * r;
+        m = rho * (core + rim);
+        I = rho * polys->inertia_per_density[k] * (core + rim) / core;
+    } else if (d.shape == SFP_SHAPE_CIRCLE) {
         m = rho * pi * r * r;
         I = 0.5 * m * r * r;
     } else if (d.shape == SFP_SHAPE_CAPSULE) {
@@ -87,8 +164,8 @@ inline void mass_properties(const SfpBodyDesc& d, float* inv_mass, float* inv_in
     *inv_inertia = (float)(1.0 / I);
 }
 
-inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4* shape,
-                           f4* mat) {
+inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4* shape, f4* mat,
+                           const PolyTable* polys = nullptr) {
     pose->x = d.x;
     pose->y = d.y;
     pose->z = cosf(d.angle);
@@ -102,11 +179,19 @@ inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4
     vel->y = is_static ? 0.0f : d.vy;
     vel->z = is_static ? 0.0f : d.omega;
     vel->w = 0.0f;
-    mass_properties(d, &minv->x, &minv->y);
-    shape->x = (d.shape == SFP_SHAPE_CIRCLE) ? 0.0f : d.hx;
-    shape->y = (d.shape == SFP_SHAPE_RECT) ? d.hy : 0.0f;
-    shape->z = d.radius;
-    shape->w = u2f(d.shape);
+    mass_properties(d, &minv->x, &minv->y, polys);
+    if ((d.shape & 0xffu) == SFP_SHAPE_POLYGON) {
+        const uint32_t k = d.shape >> 8;
+        shape->x = polys->bound[k]; /* half extents = bounding radius: conservative boxes */
+        shape->y = polys->bound[k];
+        shape->z = d.radius;
+        shape->w = u2f((uint32_t)SFP_SHAPE_POLYGON | (polys->polys[k].count << 2) | (k << 8));
+    } else {
+        shape->x = (d.shape == SFP_SHAPE_CIRCLE) ? 0.0f : d.hx;
+        shape->y = (d.shape == SFP_SHAPE_RECT) ? d.hy : 0.0f;
+        shape->z = d.radius;
+        shape->w = u2f(d.shape);
+    }
     mat->x = d.mu_s;
     mat->y = d.mu_d;
     mat->z = d.restitution;

@@ -22,8 +22,12 @@
 
 #if defined(__CUDACC__)
 #define SFP_HD __host__ __device__ __forceinline__
+/* for the rarely taken heavy paths (8-vertex polygons): kept out of line so that their
+ * registers and code do not weigh on the kernels' common path */
+#define SFP_HD_COLD static __host__ __device__ __noinline__
 #else
 #define SFP_HD static inline
+#define SFP_HD_COLD static inline
 #endif
 
 namespace sfp {
@@ -247,34 +251,62 @@ SFP_HD bool layers_collide(uint32_t la, uint32_t lb) {
 #define SFP_LINEAR_SLOP 0.005f
 #define SFP_EPS 1.0e-9f
 
-/* Convex core with 2 (capsule) or 4 (rectangle) vertices.  One runtime-sized type and ONE copy
- * of each routine below serve every shape pair: per-(NA,NB) template instances made the
- * narrowphase 84 KB of SASS, and the batched kernel (three CTAs per SM in different stages)
- * spent most of its stall cycles waiting for instruction fetch.  Loops run to 4 with a
- * `i < count` predicate so the vertex arrays stay in registers. */
-struct Poly {
-    v2 v[4]; /* CCW vertices, relative to the frame origin */
-    v2 n[4]; /* outward normal of edge v[i] -> v[(i+1)%count]  */
+/* Convex core with 2 (capsule), 4 (rectangle) or up to 8 (general convex polygon) vertices.
+ * One runtime-sized type and ONE copy of each routine per vertex capacity serve every shape
+ * pair: per-(NA,NB) template instances made the narrowphase 84 KB of SASS, and the batched
+ * kernel (three CTAs per SM in different stages) spent most of its stall cycles waiting for
+ * instruction fetch.  Loops run to MV with an `i < count` predicate so the vertex arrays stay
+ * in registers.  MV = 4 serves capsules and rectangles; MV = 8 is instantiated only for pairs
+ * that involve a general polygon. */
+#define SFP_POLY_VERTS 8
+enum { SHAPE_POLYGON = 3 };
+template <int MV>
+struct PolyT {
+    v2 v[MV]; /* CCW vertices, relative to the frame origin */
+    v2 n[MV]; /* outward normal of edge v[i] -> v[(i+1)%count]  */
     int count;
     float r;
 };
+typedef PolyT<4> Poly;
 
-/* world-space core polygon of a capsule / rectangle collider, translated by -origin */
-SFP_HD Poly make_poly(v2 pos, v2 q, f4 shape, v2 origin) {
-    Poly p;
+/* shape.w bits of a general polygon: type (2) | vertex count (4) << 2 | table index << 8;
+ * the table holds, per polygon, 4 x f4 of vertices (x0,y0,x1,y1 ...) then 4 x f4 of edge
+ * normals, all in the body frame */
+SFP_HD uint32_t poly_count(f4 shape) { return (f2u(shape.w) >> 2) & 15u; }
+SFP_HD uint32_t poly_index(f4 shape) { return f2u(shape.w) >> 8; }
+
+/* world-space core polygon of a capsule / rectangle / polygon collider, translated by -origin */
+template <int MV>
+SFP_HD PolyT<MV> make_poly_t(v2 pos, v2 q, f4 shape, v2 origin, const f4* table) {
+    PolyT<MV> p;
     v2 c = pos - origin;
     v2 ax = mk(q.x * shape.x, q.y * shape.x);  /* R * (hx, 0) */
     p.r = shape.z;
-    if (shape_type(shape) == SHAPE_CAPSULE) {
+    const uint32_t type = shape_type(shape);
+    if (MV > 4 && type == SHAPE_POLYGON) {
+        const f4* rec = table + (size_t)poly_index(shape) * 8u;
+        p.count = (int)poly_count(shape);
+#pragma unroll
+        for (int k = 0; k < MV / 2; ++k) {
+            f4 vv = rec[k], nn = rec[4 + k];
+            p.v[2 * k] = c + rot(q, mk(vv.x, vv.y));
+            p.v[2 * k + 1] = c + rot(q, mk(vv.z, vv.w));
+            p.n[2 * k] = rot(q, mk(nn.x, nn.y));
+            p.n[2 * k + 1] = rot(q, mk(nn.z, nn.w));
+        }
+        return p;
+    }
+    if (type == SHAPE_CAPSULE) {
         p.count = 2;
         p.v[0] = c - ax;
         p.v[1] = c + ax;
-        p.v[2] = p.v[0];
-        p.v[3] = p.v[1];
         p.n[0] = mk(q.y, -q.x);
         p.n[1] = mk(-q.y, q.x);
-        p.n[2] = p.n[0];
-        p.n[3] = p.n[1];
+#pragma unroll
+        for (int k = 2; k < MV; ++k) {
+            p.v[k] = p.v[k & 1];
+            p.n[k] = p.n[k & 1];
+        }
     } else {
         v2 ay = mk(-q.y * shape.y, q.x * shape.y); /* R * (0, hy) */
         p.count = 4;
@@ -286,6 +318,11 @@ SFP_HD Poly make_poly(v2 pos, v2 q, f4 shape, v2 origin) {
         p.n[1] = mk(q.x, q.y);
         p.n[2] = mk(-q.y, q.x);
         p.n[3] = mk(-q.x, -q.y);
+#pragma unroll
+        for (int k = 4; k < MV; ++k) {
+            p.v[k] = p.v[k & 3];
+            p.n[k] = p.n[k & 3];
+        }
     }
     return p;
 }
@@ -326,13 +363,14 @@ SFP_HD Manifold collide_points(v2 ca, float ra, v2 cb, float rb, float margin) {
 }
 
 /* edge e of P: its two vertices and its normal (register-resident selection) */
-SFP_HD void poly_edge(const Poly& P, int e, v2* a, v2* b, v2* n) {
+template <int MV>
+SFP_HD void poly_edge(const PolyT<MV>& P, int e, v2* a, v2* b, v2* n) {
     int e2 = (e + 1 == P.count) ? 0 : e + 1;
     *a = P.v[0];
     *b = P.v[0];
     *n = P.n[0];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i == e) {
             *a = P.v[i];
             *n = P.n[i];
@@ -342,12 +380,13 @@ SFP_HD void poly_edge(const Poly& P, int e, v2* a, v2* b, v2* n) {
 }
 
 /* polygon core P vs point core c.  Normal returned points from P to the point. */
-SFP_HD Manifold collide_poly_point(const Poly& P, v2 c, float rc, float margin) {
+template <int MV>
+SFP_HD Manifold collide_poly_point(const PolyT<MV>& P, v2 c, float rc, float margin) {
     Manifold m = manifold_none();
     float best = -3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i < P.count) {
             float s = dot(P.n[i], c - P.v[i]);
             if (s > best) {
@@ -389,15 +428,16 @@ SFP_HD Manifold collide_poly_point(const Poly& P, v2 c, float rc, float margin) 
 }
 
 /* max over edges of P1 of the min over vertices of P2 of the signed distance */
-SFP_HD float max_separation(const Poly& P1, const Poly& P2, int* edge) {
+template <int MV>
+SFP_HD float max_separation(const PolyT<MV>& P1, const PolyT<MV>& P2, int* edge) {
     float best = -3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i < P1.count) {
             float si = 3.0e38f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < MV; ++j) {
                 if (j < P2.count) {
                     float sij = dot(P1.n[i], P2.v[j] - P1.v[i]);
                     si = fminf(si, sij);
@@ -439,11 +479,12 @@ SFP_HD void segment_fractions(v2 p1, v2 q1, v2 p2, v2 q2, float* f1, float* f2) 
 }
 
 /* edge of P whose normal is most anti-parallel to n */
-SFP_HD int incident_edge(const Poly& P, v2 n) {
+template <int MV>
+SFP_HD int incident_edge(const PolyT<MV>& P, v2 n) {
     float best = 3.0e38f;
     int bi = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i < P.count) {
             float d = dot(P.n[i], n);
             if (d < best) {
@@ -459,7 +500,8 @@ SFP_HD int incident_edge(const Poly& P, v2 n) {
  * the cores are disjoint and the closest features are two vertices the result is one point
  * with a vertex-vertex normal, otherwise the incident edge is clipped against the reference
  * face's side planes (1 or 2 points). */
-SFP_HD Manifold collide_polys(const Poly& A, const Poly& B, float margin) {
+template <int MV>
+SFP_HD Manifold collide_polys(const PolyT<MV>& A, const PolyT<MV>& B, float margin) {
     Manifold m = manifold_none();
     int ea = 0, eb = 0;
     float sa = max_separation(A, B, &ea);
@@ -615,23 +657,42 @@ SFP_HD Manifold manifold_flip(Manifold m) {
 }
 
 /* dispatch on the two shape types; everything is expressed relative to A's position */
-SFP_HD Manifold collide(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float margin) {
-    v2 xa = mk(pose_a.x, pose_a.y), qa = mk(pose_a.z, pose_a.w);
-    v2 xb = mk(pose_b.x, pose_b.y), qb = mk(pose_b.z, pose_b.w);
-    uint32_t ta = shape_type(shape_a), tb = shape_type(shape_b);
+template <int MV>
+SFP_HD Manifold collide_cores(v2 xa, v2 qa, f4 shape_a, v2 xb, v2 qb, f4 shape_b, float margin,
+                              const f4* table) {
+    const uint32_t ta = shape_type(shape_a), tb = shape_type(shape_b);
     v2 cb = xb - xa;
     v2 zero = mk(0.0f, 0.0f);
-    if (ta == SHAPE_CIRCLE && tb == SHAPE_CIRCLE)
-        return collide_points(zero, shape_a.z, cb, shape_b.z, margin);
     if (ta == SHAPE_CIRCLE || tb == SHAPE_CIRCLE) {
         /* one call site: the polygon is whichever body is not the circle */
         const bool a_round = ta == SHAPE_CIRCLE;
-        Poly P = make_poly(a_round ? xb : xa, a_round ? qb : qa, a_round ? shape_b : shape_a, xa);
-        Manifold m = collide_poly_point(P, a_round ? zero : cb, a_round ? shape_a.z : shape_b.z,
-                                        margin);
+        PolyT<MV> P = make_poly_t<MV>(a_round ? xb : xa, a_round ? qb : qa,
+                                      a_round ? shape_b : shape_a, xa, table);
+        Manifold m = collide_poly_point<MV>(P, a_round ? zero : cb,
+                                            a_round ? shape_a.z : shape_b.z, margin);
         return a_round ? manifold_flip(m) : m;
     }
-    return collide_polys(make_poly(xa, qa, shape_a, xa), make_poly(xb, qb, shape_b, xa), margin);
+    return collide_polys<MV>(make_poly_t<MV>(xa, qa, shape_a, xa, table),
+                             make_poly_t<MV>(xb, qb, shape_b, xa, table), margin);
+}
+
+SFP_HD_COLD Manifold collide_cores_polygon(v2 xa, v2 qa, f4 shape_a, v2 xb, v2 qb, f4 shape_b,
+                                           float margin, const f4* table) {
+    return collide_cores<SFP_POLY_VERTS>(xa, qa, shape_a, xb, qb, shape_b, margin, table);
+}
+
+/* POLYS = false compiles the general-polygon path out (kernels of worlds that hold none) */
+template <bool POLYS>
+SFP_HD Manifold collide(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float margin,
+                        const f4* table) {
+    v2 xa = mk(pose_a.x, pose_a.y), qa = mk(pose_a.z, pose_a.w);
+    v2 xb = mk(pose_b.x, pose_b.y), qb = mk(pose_b.z, pose_b.w);
+    uint32_t ta = shape_type(shape_a), tb = shape_type(shape_b);
+    if (ta == SHAPE_CIRCLE && tb == SHAPE_CIRCLE)
+        return collide_points(mk(0.0f, 0.0f), shape_a.z, xb - xa, shape_b.z, margin);
+    if (POLYS && table != nullptr && (ta == SHAPE_POLYGON || tb == SHAPE_POLYGON))
+        return collide_cores_polygon(xa, qa, shape_a, xb, qb, shape_b, margin, table);
+    return collide_cores<4>(xa, qa, shape_a, xb, qb, shape_b, margin, table);
 }
 
 /* ------------------------------------------------------------------------------------- */
@@ -645,14 +706,15 @@ struct ContactRec {
     f4 s;  /* sep0, sep1 at narrowphase time, 0, 0              */
 };
 
-/* 0..8: (type of a) * 3 + (type of b); pairs are bucketed by it so that a warp runs one
- * narrowphase routine instead of up to nine */
+/* 0..15: (type of a) * 4 + (type of b); pairs are bucketed by it so that a warp runs one
+ * narrowphase routine instead of several */
 SFP_HD uint32_t pair_type_key(f4 shape_a, f4 shape_b) {
-    return shape_type(shape_a) * 3u + shape_type(shape_b);
+    return shape_type(shape_a) * 4u + shape_type(shape_b);
 }
 
+template <bool POLYS>
 SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
-                              f4 shape_b, f4 mat_b, float margin) {
+                              f4 shape_b, f4 mat_b, float margin, const f4* table) {
     ContactRec c;
     {
         /* bounding-circle reject: most candidate pairs of a frame are not touching in a given
@@ -668,7 +730,7 @@ SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose
             return c;
         }
     }
-    Manifold m = collide(pose_a, shape_a, pose_b, shape_b, margin);
+    Manifold m = collide<POLYS>(pose_a, shape_a, pose_b, shape_b, margin, table);
     v2 qa = mk(pose_a.z, pose_a.w), qb = mk(pose_b.z, pose_b.w);
     v2 dab = mk(pose_b.x - pose_a.x, pose_b.y - pose_a.y);
     c.a.x = m.n.x;
@@ -1071,31 +1133,17 @@ SFP_HD bool ray_edge(v2 o, v2 d, v2 p, v2 q, v2 nrm, float tmax, float* t) {
     return true;
 }
 
-/* closest hit of a ray with one collider; true if hit within [0, tmax] */
-SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, float* t_out, v2* n_out) {
-    v2 x = mk(pose.x, pose.y), q = mk(pose.z, pose.w);
-    float r = shape.z;
-    uint32_t type = shape_type(shape);
-    float dl = sqrtf(dot(d, d));
-    if (!(dl > 0.0f)) return false;
-    v2 back = neg((1.0f / dl) * d);
-    if (type == SHAPE_CIRCLE) {
-        v2 m = o - x;
-        if (dot(m, m) <= r * r) {
-            *t_out = 0.0f;
-            *n_out = back;
-            return true;
-        }
-        return ray_disc(o, d, x, r, tmax, t_out, n_out);
-    }
-    Poly P = make_poly(x, q, shape, mk(0.0f, 0.0f));
+/* closest hit of a ray with an inflated convex core */
+template <int MV>
+SFP_HD bool ray_poly(v2 o, v2 d, float tmax, const PolyT<MV>& P, v2 back, float* t_out, v2* n_out) {
+    const float r = P.r;
     /* origin inside the inflated core? */
     float smax = -3.0e38f, dmin2 = 3.0e38f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i < P.count) {
             v2 a, b, nn;
-            poly_edge(P, i, &a, &b, &nn);
+            poly_edge<MV>(P, i, &a, &b, &nn);
             smax = fmaxf(smax, dot(nn, o - a));
             v2 e = b - a;
             float ee = dot(e, e);
@@ -1114,10 +1162,10 @@ SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, float* t_out
     float best = tmax;
     v2 bn = back;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MV; ++i) {
         if (i < P.count) {
             v2 a, b, nn;
-            poly_edge(P, i, &a, &b, &nn);
+            poly_edge<MV>(P, i, &a, &b, &nn);
             float tt;
             v2 off = r * nn;
             if (ray_edge(o, d, a + off, b + off, nn, best, &tt)) {
@@ -1136,6 +1184,36 @@ SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, float* t_out
     *t_out = best;
     *n_out = bn;
     return hit;
+}
+
+SFP_HD_COLD bool ray_polygon(v2 o, v2 d, float tmax, v2 x, v2 q, f4 shape, const f4* table, v2 back,
+                             float* t_out, v2* n_out) {
+    return ray_poly<SFP_POLY_VERTS>(
+        o, d, tmax, make_poly_t<SFP_POLY_VERTS>(x, q, shape, mk(0.0f, 0.0f), table), back, t_out,
+        n_out);
+}
+
+/* closest hit of a ray with one collider; true if hit within [0, tmax] */
+SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f4* table, float* t_out,
+                         v2* n_out) {
+    v2 x = mk(pose.x, pose.y), q = mk(pose.z, pose.w);
+    float r = shape.z;
+    uint32_t type = shape_type(shape);
+    float dl = sqrtf(dot(d, d));
+    if (!(dl > 0.0f)) return false;
+    v2 back = neg((1.0f / dl) * d);
+    if (type == SHAPE_CIRCLE) {
+        v2 m = o - x;
+        if (dot(m, m) <= r * r) {
+            *t_out = 0.0f;
+            *n_out = back;
+            return true;
+        }
+        return ray_disc(o, d, x, r, tmax, t_out, n_out);
+    }
+    if (type == SHAPE_POLYGON) return ray_polygon(o, d, tmax, x, q, shape, table, back, t_out, n_out);
+    return ray_poly<4>(o, d, tmax, make_poly_t<4>(x, q, shape, mk(0.0f, 0.0f), table), back, t_out,
+                       n_out);
 }
 
 /* tight AABB of a collider at its current pose (no margin, no sweep) */

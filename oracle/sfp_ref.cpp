@@ -38,6 +38,7 @@ struct SfpWorld {
     std::vector<f4> pose, prev, vel, shape, mat;
     std::vector<f2> minv;
     std::vector<SfpJointDesc> joints;
+    PolyTable polys; /* general convex polygons (sfp_ref_set_polygons) */
     /* per frame */
     std::vector<SfpPair> pairs;          /* sorted by (a,b) */
     std::vector<uint32_t> pair_colour;   /* aligned with pairs */
@@ -331,8 +332,8 @@ void substep(SfpWorld& w, float h) {
     float maxpen = 0.0f;
     for (uint32_t k = 0; k < P; ++k) {
         uint32_t a = w.pairs[k].a, b = w.pairs[k].b;
-        w.contacts[k] = narrowphase(w.pose[a], w.vel[a], w.shape[a], w.mat[a], w.pose[b], w.vel[b],
-                                    w.shape[b], w.mat[b], w.p.contact_margin);
+        w.contacts[k] = narrowphase<true>(w.pose[a], w.vel[a], w.shape[a], w.mat[a], w.pose[b], w.vel[b],
+                                    w.shape[b], w.mat[b], w.p.contact_margin, w.polys.recs.data());
         uint32_t cnt = f2u(w.contacts[k].b.y);
         npts += cnt;
         nman += cnt > 0 ? 1u : 0u;
@@ -438,7 +439,7 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
         return SFP_E_CAPACITY;
     }
     for (uint32_t i = 0; i < n; ++i)
-        if (!desc_valid(bodies[i])) {
+        if (!desc_valid(bodies[i], &w->polys)) {
             w->err = "invalid body desc at index " + std::to_string(i);
             return SFP_E_INVALID;
         }
@@ -456,7 +457,8 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
     w->minv.resize(n);
     uint32_t ndyn = 0;
     for (uint32_t i = 0; i < n; ++i) {
-        body_from_desc(bodies[i], &w->pose[i], &w->vel[i], &w->minv[i], &w->shape[i], &w->mat[i]);
+        body_from_desc(bodies[i], &w->pose[i], &w->vel[i], &w->minv[i], &w->shape[i], &w->mat[i],
+                       &w->polys);
         w->prev[i] = w->pose[i];
         ndyn += is_dynamic(*w, i) ? 1u : 0u;
     }
@@ -470,6 +472,19 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
     w->prev_joint_colour.clear();
     w->colour_age = 0;
     w->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_ref_set_polygons(SfpWorld* w, const SfpPolygon* polys, uint32_t n) {
+    if (!w || (n && !polys)) return SFP_E_INVALID;
+    PolyTable t;
+    long bad = build_poly_table(polys, n, &t);
+    if (bad >= 0) {
+        w->err = "invalid polygon at index " + std::to_string(bad) +
+                 " (3..8 vertices, counter-clockwise, strictly convex, centroid at the origin)";
+        return SFP_E_INVALID;
+    }
+    w->polys = std::move(t);
     return SFP_OK;
 }
 
@@ -586,7 +601,8 @@ int32_t sfp_ref_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit*
             if (((f2u(w->mat[i].w) & 0xffffu) & r.mask) == 0u) continue;
             float t;
             v2 n;
-            if (!ray_collider(o, d, r.max_t, w->pose[i], w->shape[i], &t, &n)) continue;
+            if (!ray_collider(o, d, r.max_t, w->pose[i], w->shape[i], w->polys.recs.data(), &t, &n))
+                continue;
             if (best.body == 0xffffffffu || t < best.t) best = SfpRayHit{i, t, n.x, n.y};
         }
         if (best.body == 0xffffffffu) best.t = 0.0f;

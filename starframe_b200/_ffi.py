@@ -22,7 +22,7 @@ SFP_E_CAPACITY = -3
 SFP_E_NCCL = -4
 SFP_E_NOMEM = -5
 
-SHAPE_CIRCLE, SHAPE_CAPSULE, SHAPE_RECT = 0, 1, 2
+SHAPE_CIRCLE, SHAPE_CAPSULE, SHAPE_RECT, SHAPE_POLYGON = 0, 1, 2, 3
 BODY_STATIC = 1
 ORDER_COLOUR, ORDER_REFERENCE = 0, 1
 JOINT_DISTANCE, JOINT_ROPE = 0, 1
@@ -76,6 +76,8 @@ EVENT_DTYPE = np.dtype(
         ("impulse", "<f4"), ("points", "<u4"),
     ]
 )
+POLYGON_DTYPE = np.dtype([("count", "<u4"), ("reserved", "<u4"), ("x", "<f4", (8,)),
+                          ("y", "<f4", (8,))])
 RAY_DTYPE = np.dtype([("ox", "<f4"), ("oy", "<f4"), ("dx", "<f4"), ("dy", "<f4"), ("max_t", "<f4"),
                       ("mask", "<u4"), ("reserved", "<u4", (2,))])
 RAY_HIT_DTYPE = np.dtype([("body", "<u4"), ("t", "<f4"), ("nx", "<f4"), ("ny", "<f4")])
@@ -98,10 +100,12 @@ assert CONTACT_DTYPE.itemsize == 60
 assert STATS_DTYPE.itemsize == 80
 assert EVENT_DTYPE.itemsize == 32
 assert RAY_DTYPE.itemsize == 32 and RAY_HIT_DTYPE.itemsize == 16
+assert POLYGON_DTYPE.itemsize == 72
 
 # every symbol include/sfp.h declares for the product library (checked by the CPU tests)
 PRODUCT_SYMBOLS = [
-    "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
+    "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
+    "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
     "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host",
     "alloc_host_states", "free_host_states",
@@ -110,7 +114,8 @@ PRODUCT_SYMBOLS = [
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
-    "default_params", "create", "destroy", "upload_bodies", "set_joints", "step", "sync",
+    "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
+    "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
     "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host", "last_step_ms",
     "backend", "brute_pairs",
@@ -161,6 +166,7 @@ class Api:
             "destroy": [vp],
             "upload_bodies": [vp, vp, u32],
             "set_joints": [vp, vp, u32],
+            "set_polygons": [vp, vp, u32],
             "step": [vp, f32, u32],
             "sync": [vp],
             "download_bodies": [vp, vp, u32],
@@ -284,6 +290,10 @@ class World:
         b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE)
         self._check(self.api.fn("upload_bodies")(self.h, _ptr(b), b.shape[0]), "upload_bodies")
         self.n = int(b.shape[0])
+
+    def set_polygons(self, polys: np.ndarray):
+        p = np.ascontiguousarray(polys, dtype=POLYGON_DTYPE)
+        self._check(self.api.fn("set_polygons")(self.h, _ptr(p), p.shape[0]), "set_polygons")
 
     def set_joints(self, joints: np.ndarray):
         j = np.ascontiguousarray(joints, dtype=JOINT_DESC_DTYPE)

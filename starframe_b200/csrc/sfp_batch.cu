@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         stage_integrate(c, h, tid, nth);
         __syncthreads();
         LAP(4);
-        stage_narrowphase(c, tid, nth);
+        stage_narrowphase<false>(c, tid, nth);  // batched worlds hold no general polygons
         __syncthreads();
         LAP(5);
         {

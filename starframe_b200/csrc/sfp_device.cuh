@@ -48,6 +48,7 @@ struct Ctx {
     float4 *pose, *prev, *vel;
     const float4 *shape, *mat;
     const float2* minv;
+    const float4* polytab;  // general-polygon table, 8 float4 per polygon (sfp_math.h), or null
     // broadphase
     float4* aabb;
     int4* meta;  // cx0, cy0, layer bits, dynamic flag
@@ -448,15 +449,17 @@ __device__ __forceinline__ void stage_integrate(const Ctx& c, float h, uint32_t 
 // ---------------------------------------------------------------------------------------
 // A4 narrowphase: one thread per candidate pair (colour-sorted order)
 // ---------------------------------------------------------------------------------------
+template <bool POLYS>
 __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, uint32_t nth) {
     const uint32_t P = c.cnt->n_pairs;
     uint32_t npts = 0, nman = 0;
     float maxpen = 0.0f;
     for (uint32_t k = tid; k < P; k += nth) {
         uint2 p = c.pairs[k];
-        sfp::ContactRec r = sfp::narrowphase(ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x),
+        sfp::ContactRec r = sfp::narrowphase<POLYS>(ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x),
                                              ld4(c.mat, p.x), ld4(c.pose, p.y), ld4(c.vel, p.y),
-                                             ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin);
+                                             ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin,
+                                             reinterpret_cast<const sfp::f4*>(c.polytab));
         uint32_t cnt = sfp::f2u(r.b.y);
         st4(c.cb, k, r.b);
         if (cnt) {  // an empty manifold is fully described by count == 0

@@ -62,7 +62,10 @@ __global__ void __launch_bounds__(TPB) k_gather(Ctx c) { stage_gather(c, gtid(),
 __global__ void __launch_bounds__(TPB) k_integrate(Ctx c, float h) {
     stage_integrate(c, h, gtid(), gnth());
 }
-__global__ void __launch_bounds__(TPB) k_narrowphase(Ctx c) { stage_narrowphase(c, gtid(), gnth()); }
+template <bool POLYS>
+__global__ void __launch_bounds__(TPB) k_narrowphase(Ctx c) {
+    stage_narrowphase<POLYS>(c, gtid(), gnth());
+}
 __global__ void __launch_bounds__(TPB) k_solve_pos(Ctx c, uint32_t colour, float inv_h2) {
     stage_solve_pos(c, colour, inv_h2, gtid(), gnth());
 }
@@ -123,7 +126,8 @@ __global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __re
                 if ((((uint32_t)c.meta[b].z & 0xffffu) & r.mask) == 0u) continue;
                 float t;
                 v2 n;
-                if (!sfp::ray_collider(o, d, r.max_t, ld4(c.pose, b), ld4(c.shape, b), &t, &n))
+                if (!sfp::ray_collider(o, d, r.max_t, ld4(c.pose, b), ld4(c.shape, b),
+                                       reinterpret_cast<const sfp::f4*>(c.polytab), &t, &n))
                     continue;
                 if (best_body == 0xffffffffu || t < best_t || (t == best_t && b < best_body)) {
                     best_body = b;
@@ -272,6 +276,9 @@ __device__ __forceinline__ int next_bit(unsigned long long m, int after) {
 #ifndef SFP_SUB_BLOCKS
 #define SFP_SUB_BLOCKS 2
 #endif
+// POLYS: the variant that can collide general polygons (bigger, more registers); the host
+// launches it only for worlds that hold at least one polygon body
+template <bool POLYS>
 __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, float h, uint32_t substeps,
                                                        float rest_threshold) {
     cg::grid_group grid = cg::this_grid();
@@ -332,7 +339,7 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         stage_integrate(c, h, tid, nth);
         grid.sync();
         lap(4);
-        stage_narrowphase(c, tid, nth);
+        stage_narrowphase<POLYS>(c, tid, nth);
         grid.sync();
         lap(5);
         have = false;
@@ -432,6 +439,8 @@ struct SfpWorld {
     bool graphs_ok = true, capturing = false;
     Counters* d_cnt = nullptr;
     // host mirrors
+    sfp::PolyTable polys;
+    float4* d_polytab = nullptr;
     std::vector<sfp::f2> h_minv;
     std::vector<sfp::f4> h_shape, h_mat;
     uint32_t *d_evt_flag = nullptr, *d_evt_off = nullptr;  // cap_pairs + 1 each
@@ -444,7 +453,8 @@ struct SfpWorld {
     SfpBodyState* pin_state = nullptr;   // pinned host staging, cap_bodies states
     sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
     uint32_t pin_cap = 0;
-    int coop_max_colour = 0, coop_max_substep = 0, n_sm = 0;
+    int coop_max_colour = 0, coop_max_substep = 0, coop_max_substep_poly = 0, n_sm = 0;
+    bool has_polygons = false;
     SfpStats stats;
     std::string err;
     int32_t sticky = SFP_OK;
@@ -675,7 +685,11 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
                                              blocks_for(w, 4ull * w->n + w->nj));
         void* args[] = {&c, &h, &substeps, &rest_threshold};
         w->launches += 1;
-        return launch_coop(w, (const void*)k_substeps_coop, blocks, args);
+        if (w->has_polygons) {
+            blocks = std::min<uint32_t>(blocks, (uint32_t)w->coop_max_substep_poly);
+            return launch_coop(w, (const void*)k_substeps_coop<true>, blocks, args);
+        }
+        return launch_coop(w, (const void*)k_substeps_coop<false>, blocks, args);
     }
     Counters k;
     TRY(read_counters(w, &k));
@@ -694,7 +708,8 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
     const uint32_t gb = blocks_for(w, w->n), gp = blocks_for(w, (uint64_t)w->cap_pairs + w->nj);
     for (uint32_t s = 0; s < substeps; ++s) {
         k_integrate<<<gb, TPB, 0, st>>>(c, h);
-        k_narrowphase<<<gp, TPB, 0, st>>>(c);
+        if (w->has_polygons) k_narrowphase<true><<<gp, TPB, 0, st>>>(c);
+        else k_narrowphase<false><<<gp, TPB, 0, st>>>(c);
         for (uint32_t col : order) k_solve_pos<<<gp, TPB, 0, st>>>(c, col, inv_h2);
         if (serial) k_serial_pos<<<1, 32, 0, st>>>(c, inv_h2);
         k_derive<<<gb, TPB, 0, st>>>(c, inv_h);
@@ -853,10 +868,14 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
         cudaSuccess)
         return fail("occupancy(colour)", e);
     w->coop_max_colour = std::max(1, per_sm) * w->n_sm;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop, TPB, 0)) !=
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<false>, TPB, 0)) !=
         cudaSuccess)
         return fail("occupancy(substeps)", e);
     w->coop_max_substep = std::max(1, per_sm) * w->n_sm;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<true>, TPB, 0)) !=
+        cudaSuccess)
+        return fail("occupancy(substeps, polygons)", e);
+    w->coop_max_substep_poly = std::max(1, per_sm) * w->n_sm;
     w->ctx.gx = p.gravity_x;
     w->ctx.gy = p.gravity_y;
     w->ctx.inv_cell = 1.0f / p.cell_size;
@@ -880,6 +899,7 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->pin_state) cudaFreeHost(w->pin_state);
     if (w->d_rays) cudaFree(w->d_rays);
     if (w->d_hits) cudaFree(w->d_hits);
+    if (w->d_polytab) cudaFree(w->d_polytab);
     if (w->ev0) cudaEventDestroy(w->ev0);
     if (w->ev1) cudaEventDestroy(w->ev1);
     if (w->ev_bp) cudaEventDestroy(w->ev_bp);
@@ -896,7 +916,7 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
         return SFP_E_CAPACITY;
     }
     for (uint32_t i = 0; i < n; ++i)
-        if (!sfp::desc_valid(bodies[i])) {
+        if (!sfp::desc_valid(bodies[i], &w->polys)) {
             w->err = "invalid body desc at index " + std::to_string(i);
             return SFP_E_INVALID;
         }
@@ -912,11 +932,14 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     w->h_shape.resize(n);
     w->h_mat.resize(n);
     uint32_t ndyn = 0;
+    bool polys_used = false;
     for (uint32_t i = 0; i < n; ++i) {
         sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &w->h_minv[i], &w->h_shape[i],
-                            &w->h_mat[i]);
+                            &w->h_mat[i], &w->polys);
         ndyn += (w->h_minv[i].x > 0.0f || w->h_minv[i].y > 0.0f) ? 1u : 0u;
+        polys_used |= (bodies[i].shape & 0xffu) == SFP_SHAPE_POLYGON;
     }
+    w->has_polygons = polys_used;
     Ctx& c = w->ctx;
     cudaStream_t st = w->stream;
     CU(cudaStreamSynchronize(st));
@@ -943,6 +966,30 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     w->stats.n_dynamic = ndyn;
     w->colour_age = 0;
     w->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_set_polygons(SfpWorld* w, const SfpPolygon* polys, uint32_t n) {
+    if (!w || (n && !polys)) return SFP_E_INVALID;
+    sfp::PolyTable t;
+    long bad = sfp::build_poly_table(polys, n, &t);
+    if (bad >= 0) {
+        w->err = "invalid polygon at index " + std::to_string(bad) +
+                 " (3..8 vertices, counter-clockwise, strictly convex, centroid at the origin)";
+        return SFP_E_INVALID;
+    }
+    CU(cudaSetDevice(w->device));
+    CU(cudaStreamSynchronize(w->stream));
+    drop_graphs(w);  // the table pointer is a kernel argument
+    if (w->d_polytab) cudaFree(w->d_polytab);
+    w->d_polytab = nullptr;
+    if (n) {
+        CU(cudaMalloc(&w->d_polytab, sizeof(float4) * 8u * (size_t)n));
+        CU(cudaMemcpy(w->d_polytab, t.recs.data(), sizeof(float4) * 8u * (size_t)n,
+                      cudaMemcpyHostToDevice));
+    }
+    w->ctx.polytab = w->d_polytab;
+    w->polys = std::move(t);
     return SFP_OK;
 }
 

@@ -19,7 +19,7 @@ import numpy as np
 
 from . import _ffi
 from ._ffi import (BODY_DESC_DTYPE, BODY_STATIC, JOINT_DESC_DTYPE, JOINT_DISTANCE, JOINT_ROPE,
-                   SHAPE_CAPSULE, SHAPE_CIRCLE, SHAPE_RECT, Api, World)
+                   POLYGON_DTYPE, SHAPE_CAPSULE, SHAPE_CIRCLE, SHAPE_POLYGON, SHAPE_RECT, Api, World)
 
 LIB_PATH = os.environ.get(
     "SFP_B200_LIB",
@@ -52,6 +52,14 @@ class Collider:
     material: Material = field(default_factory=Material)
     layer: int = 1
     mask: int = 0xFFFF
+    points: tuple | None = None  # general convex polygon: CCW body-frame vertices (3..8)
+
+    @staticmethod
+    def new_polygon(points, r: float = 0.0) -> "Collider":
+        """Convex polygon (counter-clockwise, 3..8 vertices) with rounding radius r.  The
+        vertices are re-centred on the polygon's centroid: the body's position is its centre of
+        mass."""
+        return Collider(SHAPE_POLYGON, 0.0, 0.0, r, points=tuple(map(tuple, points)))
 
     @staticmethod
     def new_circle(r: float) -> "Collider":
@@ -114,6 +122,7 @@ class Physics:
         self._world = World(self._api, gravity_x=gravity[0], gravity_y=gravity[1], **params)
         self._bodies: list[np.void] = []
         self._joints: list[np.void] = []
+        self._polygons: list[np.void] = []
         self._dirty = True
 
     # -- scene building ---------------------------------------------------------------
@@ -123,6 +132,11 @@ class Physics:
         d["vx"], d["vy"], d["omega"] = body.vx, body.vy, body.omega
         d["hx"], d["hy"], d["radius"] = collider.hx, collider.hy, collider.radius
         d["shape"] = collider.shape
+        if collider.shape == SHAPE_POLYGON:
+            from .scenes import polygon
+
+            self._polygons.append(polygon(collider.points)[0])
+            d["shape"] = SHAPE_POLYGON | ((len(self._polygons) - 1) << 8)
         d["density"] = body.density
         d["mu_s"] = collider.material.static_friction
         d["mu_d"] = collider.material.dynamic_friction
@@ -179,6 +193,8 @@ class Physics:
                       else np.zeros(0, dtype=BODY_DESC_DTYPE))
             # joints first cleared so a shrinking body set never leaves dangling references
             self._world.set_joints(np.zeros(0, dtype=JOINT_DESC_DTYPE))
+            if self._polygons:
+                self._world.set_polygons(np.array(self._polygons, dtype=POLYGON_DTYPE))
             self._world.upload_bodies(bodies)
             joints = (np.array(self._joints, dtype=JOINT_DESC_DTYPE) if self._joints
                       else np.zeros(0, dtype=JOINT_DESC_DTYPE))

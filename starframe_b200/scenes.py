@@ -10,8 +10,8 @@ from __future__ import annotations
 
 import numpy as np
 
-from ._ffi import (BODY_DESC_DTYPE, BODY_STATIC, JOINT_DESC_DTYPE, JOINT_DISTANCE, SHAPE_CAPSULE,
-                   SHAPE_CIRCLE, SHAPE_RECT)
+from ._ffi import (BODY_DESC_DTYPE, BODY_STATIC, JOINT_DESC_DTYPE, JOINT_DISTANCE, POLYGON_DTYPE,
+                   SHAPE_CAPSULE, SHAPE_CIRCLE, SHAPE_POLYGON, SHAPE_RECT)
 
 BASE_SEED = 20261106
 
@@ -282,6 +282,51 @@ def random_soup(n: int, seed: int, pitch: float = 0.7, extent: float | None = No
     b["mask"] = np.where(lay == 3, 0x7, 0xFFFF).astype(np.uint16)
     floor = static_rect(0.0, -0.5, 0.5 * cols * pitch + 2.0, 0.5)
     return np.concatenate([b, floor]), no_joints()
+
+
+def polygon(points) -> np.ndarray:
+    """One SfpPolygon from CCW points, re-centred on its centroid (as the ABI requires)."""
+    pts = np.asarray(points, dtype=np.float64)
+    x, y = pts[:, 0], pts[:, 1]
+    xn, yn = np.roll(x, -1), np.roll(y, -1)
+    cr = x * yn - xn * y
+    a2 = cr.sum()
+    cx, cy = ((x + xn) * cr).sum() / (3 * a2), ((y + yn) * cr).sum() / (3 * a2)
+    p = np.zeros(1, dtype=POLYGON_DTYPE)
+    p["count"] = len(pts)
+    p["x"][0, : len(pts)] = x - cx
+    p["y"][0, : len(pts)] = y - cy
+    return p
+
+
+def regular_polygon(n_verts: int, radius: float, phase: float = 0.0) -> np.ndarray:
+    a = phase + 2 * np.pi * np.arange(n_verts) / n_verts
+    return polygon(np.stack([radius * np.cos(a), radius * np.sin(a)], axis=1))
+
+
+def polygon_table(seed: int = BASE_SEED + 8) -> np.ndarray:
+    """a small palette: triangle, irregular quad, pentagon, hexagon, heptagon, octagon, sliver"""
+    return np.concatenate([
+        regular_polygon(3, 0.18), polygon([(-0.2, -0.1), (0.15, -0.14), (0.22, 0.08), (-0.1, 0.15)]),
+        regular_polygon(5, 0.16, 0.3), regular_polygon(6, 0.15), regular_polygon(7, 0.17, 0.1),
+        regular_polygon(8, 0.14), polygon([(-0.3, -0.04), (0.3, -0.04), (0.3, 0.04), (-0.3, 0.04)]),
+    ])
+
+
+def polygon_pile(n: int = 1500, seed: int = BASE_SEED + 8, cols: int | None = None):
+    """mixed pile in which ~half of the bodies are general convex polygons (with and without
+    rounding).  Returns (bodies, joints, polygons)."""
+    table = polygon_table(seed)
+    b, j = mixed_pile(n, seed=seed, cols=cols)
+    k = np.arange(len(b)) >= 3
+    pick = uniform(seed, 30, len(b)) < 0.5
+    which = (uniform(seed, 31, len(b)) * len(table)).astype(np.uint32).clip(0, len(table) - 1)
+    sel = k & pick
+    b["shape"] = np.where(sel, SHAPE_POLYGON | (which << 8), b["shape"])
+    b["radius"] = np.where(sel, np.where(uniform(seed, 32, len(b)) < 0.5, 0.0, 0.02), b["radius"])
+    b["hx"] = np.where(sel, 0.0, b["hx"])
+    b["hy"] = np.where(sel, 0.0, b["hy"])
+    return b, j, table
 
 
 def crowded_plank(n_riders: int = 100, seed: int = BASE_SEED + 7):

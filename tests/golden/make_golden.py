@@ -19,7 +19,13 @@ import starframe_b200 as sf  # noqa: E402
 from oracle import loader  # noqa: E402
 from starframe_b200 import scenes  # noqa: E402
 
+def _polys():
+    b, j, table = scenes.polygon_pile(500)
+    return b, j, table
+
+
 CASES = {
+    "polygons500_f120": (_polys, 120),
     "stack100_f90": (lambda: scenes.stack100(), 90),
     "soup300_f40": (lambda: scenes.random_soup(300, 77, pitch=0.55), 40),
     "pile800_f150": (lambda: scenes.mixed_pile(800), 150),
@@ -28,8 +34,10 @@ CASES = {
 }
 
 
-def run(api, bodies, joints, frames):
+def run(api, bodies, joints, frames, polygons=None):
     w = sf.World(api)
+    if polygons is not None:
+        w.set_polygons(polygons)
     w.upload_bodies(bodies)
     w.set_joints(joints)
     for _ in range(frames):
@@ -45,10 +53,12 @@ def run(api, bodies, joints, frames):
 def main():
     api = loader.api()
     for name, (make, frames) in CASES.items():
-        bodies, joints = make()
-        out = run(api, bodies, joints, frames)
+        made = make()
+        bodies, joints = made[0], made[1]
+        polygons = made[2] if len(made) > 2 else np.zeros(0, dtype=sf._ffi.POLYGON_DTYPE)
+        out = run(api, bodies, joints, frames, polygons)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), bodies=bodies, joints=joints,
-                            frames=np.int64(frames), **out)
+                            polygons=polygons, frames=np.int64(frames), **out)
         print(name, len(bodies), "bodies", len(out["pairs"]), "pairs", out["counts"].tolist())
 
 
