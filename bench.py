@@ -242,6 +242,10 @@ def run_single(args, rank, world_size):
         del w
         out["other_configs"] = {name: quick_config(name, args) for name in ("circles10k", "ropes2k")}
         out["other_configs"]["worlds512_1gpu"] = quick_worlds(args)
+        if not args.no_scale_point:
+            # the scale at which HBM bandwidth, not phase latency, bounds
+            # the step (state + pair data several times the L2)
+            out["scale_point"] = scale_point(args)
     return out
 
 
@@ -268,6 +272,37 @@ def quick_config(name, args, frames=30):
             "ms_per_step": t / frames, "pairs_per_body": st["n_pairs"] / n,
             "contacts_per_body": st["n_contacts"] / n, "joints_per_body": st["n_joints"] / n,
             "colours": st["n_colours"]}
+
+
+def scale_point(args, name="shelves4000000", settle=200, frames=10):
+    import torch
+
+    import starframe_b200 as sf
+
+    bodies, joints = make_scene(name)
+    n = len(bodies)
+    w = sf.World(sf.product_api(), device=torch.cuda.current_device())
+    w.upload_bodies(bodies)
+    for _ in range(settle):
+        w.step(DT, SUBSTEPS)
+    w.sync()
+    t = t_sub = 0.0
+    for _ in range(frames):
+        w.step(DT, SUBSTEPS)
+        w.sync()
+        br = w.last_step_breakdown_ms()
+        t += br["step"]
+        t_sub += br["substeps"]
+    st = w.stats()
+    peak, _ = peaks()
+    b_sub = b_alg(n, st["n_pairs"], st["n_contacts"], 0, whole_step=False) * n * SUBSTEPS
+    b_all = b_alg(n, st["n_pairs"], st["n_contacts"], 0) * n * SUBSTEPS
+    return {"workload": name, "bodies": n, "value": n * SUBSTEPS * frames / (t * 1e-3),
+            "unit": "body-substeps/s", "ms_per_step": t / frames,
+            "state_mbytes": n * 88 / 1e6, "pairs_per_body": st["n_pairs"] / n,
+            "contacts_per_body": st["n_contacts"] / n, "colours": st["n_colours"],
+            "roofline_substep_kernel_frac": b_sub / (t_sub / frames * 1e-3) / 1e9 / peak,
+            "roofline_whole_step_frac": b_all / (t / frames * 1e-3) / 1e9 / peak}
 
 
 def quick_worlds(args, frames=20):
@@ -535,6 +570,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--no-scale-point", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))

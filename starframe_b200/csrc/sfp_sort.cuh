@@ -166,6 +166,34 @@ k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_p
     hist[blockIdx.x * RADIX_BINS + threadIdx.x] = h[threadIdx.x];
 }
 
+// Above RADIX_INLINE_BLOCKS live blocks the per-block sweep over the histogram would be
+// quadratic in the block count, so one block per digit scans that digit's column in place and
+// leaves the column total behind the histogram (hist[n_blocks * 256 + digit]).
+constexpr uint32_t RADIX_INLINE_BLOCKS = 512;
+static __global__ void __launch_bounds__(256)
+k_radix_colscan(uint32_t* __restrict__ hist, uint32_t n_blocks, const uint32_t* __restrict__ n_ptr) {
+    __shared__ uint32_t sm[9];
+    __shared__ uint32_t carry;
+    const uint32_t n = *n_ptr;
+    const uint32_t live = min(n_blocks, (n + RADIX_TILE - 1) / RADIX_TILE);
+    if (live <= RADIX_INLINE_BLOCKS) return;
+    const uint32_t d = blockIdx.x;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < live; base += 256) {
+        uint32_t b = base + threadIdx.x;
+        uint32_t v = (b < live) ? hist[(size_t)b * RADIX_BINS + d] : 0u;
+        uint32_t total;
+        uint32_t ex = block_excl_scan(v, &total, sm);
+        uint32_t c0 = carry;
+        if (b < live) hist[(size_t)b * RADIX_BINS + d] = c0 + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c0 + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) hist[(size_t)n_blocks * RADIX_BINS + d] = carry;
+}
+
 // stable scatter.  vals_in == nullptr means "value = source index" (used to build permutations)
 static __global__ void __launch_bounds__(RADIX_THREADS)
 k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
@@ -218,11 +246,17 @@ k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
         // this digit in earlier blocks
         const uint32_t live = (n + RADIX_TILE - 1) / RADIX_TILE;
         uint32_t before = 0, total = 0;
+        if (live > RADIX_INLINE_BLOCKS) {
+            // many blocks: k_radix_colscan already turned each digit's column into running sums
+            before = hist_scanned[blockIdx.x * RADIX_BINS + threadIdx.x];
+            total = hist_scanned[(size_t)gridDim.x * RADIX_BINS + threadIdx.x];
+        } else {
 #pragma unroll 8
-        for (uint32_t b = 0; b < live; ++b) {
-            uint32_t v = hist_scanned[b * RADIX_BINS + threadIdx.x];
-            total += v;
-            before += (b < blockIdx.x) ? v : 0u;
+            for (uint32_t b = 0; b < live; ++b) {
+                uint32_t v = hist_scanned[b * RADIX_BINS + threadIdx.x];
+                total += v;
+                before += (b < blockIdx.x) ? v : 0u;
+            }
         }
         uint32_t all;
         uint32_t ex = block_excl_scan(total, &all, scan_sm);
@@ -249,6 +283,7 @@ inline cudaError_t radix_pass(const uint32_t* keys_in, const uint32_t* vals_in, 
                               uint32_t* hist, cudaStream_t st) {
     uint32_t nb = radix_blocks(cap);
     k_radix_hist<<<nb, RADIX_THREADS, 0, st>>>(keys_in, n_ptr, shift, hist);
+    if (nb > RADIX_INLINE_BLOCKS) k_radix_colscan<<<RADIX_BINS, 256, 0, st>>>(hist, nb, n_ptr);
     k_radix_scatter<<<nb, RADIX_THREADS, 0, st>>>(keys_in, vals_in, keys_out, vals_out, n_ptr,
                                                   shift, hist);
     return cudaGetLastError();

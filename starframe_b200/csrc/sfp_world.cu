@@ -547,7 +547,7 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     uint32_t biggest = std::max(std::max(ce, cp), std::max(cb, w->cap_joints)) + 1;
     w->hist_blocks = radix_blocks(biggest);
     CU(cudaMalloc(&w->d_scan_tiles, sizeof(uint32_t) * (biggest / SCAN_TILE + 4)));
-    CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * (size_t)w->hist_blocks));
+    CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * ((size_t)w->hist_blocks + 1)));
     if (w->pin_state) cudaFreeHost(w->pin_state);
     w->pin_state = nullptr;
     CU(cudaMallocHost(&w->pin_state, sizeof(SfpBodyState) * cb));
@@ -577,7 +577,7 @@ int ensure_joint_capacity(SfpWorld* w, uint32_t nj) {
     if (radix_blocks(cj + 1) > w->hist_blocks) {
         if (w->d_hist) cudaFree(w->d_hist);
         w->hist_blocks = radix_blocks(cj + 1);
-        CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * (size_t)w->hist_blocks));
+        CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * ((size_t)w->hist_blocks + 1)));
     }
     return SFP_OK;
 }
@@ -624,7 +624,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       &w->d_cnt->n_pairs, st));
     k_pair_write<<<ge, TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 4 + 3 + 3 + 8;
+    w->launches += 4 + 3 + 3 + 8 + (radix_blocks(w->cap_entries) > RADIX_INLINE_BLOCKS ? 4 : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_bp, st, w->capturing ? cudaEventRecordExternal : 0));
 
     // warm start: read last frame's table, build this frame's in the other one
@@ -667,7 +667,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       0, w->d_hist, st));
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 5 + (w->nj ? 2 : 0);
+    w->launches += 5 + (w->nj ? 2 : 0) + (radix_blocks(w->cap_pairs) > RADIX_INLINE_BLOCKS ? 2 : 0) +
+                   ((w->nj && radix_blocks(w->cap_joints) > RADIX_INLINE_BLOCKS) ? 1 : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_col, st, w->capturing ? cudaEventRecordExternal : 0));
     return SFP_OK;
 }
