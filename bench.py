@@ -145,8 +145,15 @@ def run_single(args, rank, world_size):
     w = sf.World(api, device=torch.cuda.current_device())
     w.upload_bodies(bodies)
     w.set_joints(joints)
-    for _ in range(args.settle):
+    # SURVEY.md §8d also asks for the free-fall window, frames [0,60): broadphase dominant
+    ff_frames, ff_ms, ff_pairs = min(60, args.settle), 0.0, 0
+    for k in range(args.settle):
         w.step(DT, SUBSTEPS)
+        if k < ff_frames:
+            w.sync()
+            ff_ms += w.last_step_ms()
+            if k == ff_frames - 1:
+                ff_pairs = w.stats()["n_pairs"]
     w.sync()
     settled = w.download_bodies()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -217,6 +224,7 @@ def run_single(args, rank, world_size):
             "bound": "hbm", "kernel": "k_substeps_coop (all 8 substeps of a frame, one launch)",
             "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
             "peak_source": peak_src, "traffic": ncu_traffic(args.workload),
+            "peak_nominal": 8000.0, "frac_nominal": ach / 8000.0,
             "algorithmic_bytes_per_launch": bytes_sub,
             "note": "algorithmic bytes = (136 + 72 p + 344 c + 116 j) * N * S, SURVEY.md §8d; "
                     "the kernel is grid-sync latency bound, not bandwidth bound (DESIGN.md)",
@@ -233,6 +241,11 @@ def run_single(args, rank, world_size):
         "clocks": clk.summary(),
         "stats": {k: st[k] for k in ("n_pairs", "n_contacts", "n_manifolds", "max_penetration",
                                      "kinetic_energy")},
+        "free_fall_window": {"frames": f"[0,{ff_frames})",
+                             "value": float(n) * SUBSTEPS * ff_frames / (ff_ms * 1e-3) if ff_ms else None,
+                             "unit": "body-substeps/s",
+                             "ms_per_step": ff_ms / ff_frames if ff_frames else None,
+                             "pairs_per_body_at_end": ff_pairs / n},
     }
     if rank == 0 and not args.no_cpu_baseline and world_size == 1:
         out["cpu_baseline"] = cpu_baseline_single(bodies, joints, settled, args.cpu_frames)
@@ -417,6 +430,7 @@ def run_worlds(args, rank, world_size):
         "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one CTA per world, whole frame)",
                      "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                      "peak_source": peak_src, "traffic": ncu_traffic("worlds512"),
+                     "peak_nominal": 8000.0, "frac_nominal": ach / 8000.0,
                      "algorithmic_bytes_per_launch": bytes_step,
                      "note": "traffic < algorithmic bytes: the per-substep re-reads the algorithmic "
                              "count charges (bodies, pair lists) are served from shared memory / "
