@@ -551,10 +551,14 @@ __device__ __forceinline__ void solve_pos_joint(const Ctx& c, uint32_t k, float 
 
 // items of one colour: its joints first, then its pairs.  `skip_first`: the caller has
 // already handled item `tid` (from a prefetched record).
+// `joff` / `poff`: the colour offsets (Counters::joint_col_off / pair_col_off, or a copy of them
+// that is cheaper to reach: a load from global memory after a grid-wide barrier is an L2 round
+// trip, and it would sit in front of every phase)
 __device__ __forceinline__ void stage_solve_pos(const Ctx& c, uint32_t colour, float inv_h2,
-                                                uint32_t tid, uint32_t nth, bool skip_first = false) {
-    const uint32_t j0 = c.cnt->joint_col_off[colour], j1 = c.cnt->joint_col_off[colour + 1];
-    const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
+                                                uint32_t tid, uint32_t nth, bool skip_first,
+                                                const uint32_t* joff, const uint32_t* poff) {
+    const uint32_t j0 = joff[colour], j1 = joff[colour + 1];
+    const uint32_t p0 = poff[colour], p1 = poff[colour + 1];
     const uint32_t nj = j1 - j0, total = nj + (p1 - p0);
     for (uint32_t t = skip_first ? tid + nth : tid; t < total; t += nth) {
         if (t < nj) {
@@ -570,6 +574,12 @@ __device__ __forceinline__ void stage_solve_pos(const Ctx& c, uint32_t colour, f
             solve_pos_pair(c, k, load_pair_rec(c, k));
         }
     }
+}
+
+__device__ __forceinline__ void stage_solve_pos(const Ctx& c, uint32_t colour, float inv_h2,
+                                                uint32_t tid, uint32_t nth, bool skip_first = false) {
+    stage_solve_pos(c, colour, inv_h2, tid, nth, skip_first, c.cnt->joint_col_off,
+                    c.cnt->pair_col_off);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -610,13 +620,19 @@ __device__ __forceinline__ void solve_vel_pair(const Ctx& c, uint32_t k, const P
 
 __device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, float h,
                                                 float rest_threshold, uint32_t tid, uint32_t nth,
-                                                bool skip_first = false) {
-    const uint32_t p0 = c.cnt->pair_col_off[colour], p1 = c.cnt->pair_col_off[colour + 1];
+                                                bool skip_first, const uint32_t* poff) {
+    const uint32_t p0 = poff[colour], p1 = poff[colour + 1];
     for (uint32_t k = p0 + (skip_first ? tid + nth : tid); k < p1; k += nth) {
         f4 lam = ld4(c.lam, k);
         if (!(lam.x > 0.0f || lam.z > 0.0f)) continue;
         solve_vel_pair(c, k, load_pair_rec(c, k), lam, h, rest_threshold);
     }
+}
+
+__device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, float h,
+                                                float rest_threshold, uint32_t tid, uint32_t nth,
+                                                bool skip_first = false) {
+    stage_solve_vel(c, colour, h, rest_threshold, tid, nth, skip_first, c.cnt->pair_col_off);
 }
 
 __device__ __forceinline__ void serial_solve_pos(const Ctx& c, uint32_t ncol, float inv_h2) {

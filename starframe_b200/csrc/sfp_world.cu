@@ -292,6 +292,13 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
     // once per frame (substeps == all substeps of the frame, or 1 with per-substep broadphase):
     // the serial group must be in (a, b) order before the first narrowphase
     if (serial && blockIdx.x == 0) serial_sort_pairs(c, ncol);
+    // the colour offsets, once per launch, where every phase can reach them without an L2 trip
+    __shared__ uint32_t s_poff[SFP_MAX_COLOURS + 1], s_joff[SFP_MAX_COLOURS + 1];
+    for (uint32_t i = threadIdx.x; i <= (uint32_t)SFP_MAX_COLOURS; i += blockDim.x) {
+        s_poff[i] = c.cnt->pair_col_off[i];
+        s_joff[i] = c.cnt->joint_col_off[i];
+    }
+    __syncthreads();
 
     // Prefetch: the contact record of this thread's first item of the NEXT big colour does not
     // depend on anything the current phase writes, so it is loaded before the barrier and only
@@ -302,9 +309,9 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
     auto prefetch_pos = [&](int col, uint32_t t0) {
         have = false;
         if (col >= 64) return;
-        if (c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return;
-        uint32_t k = c.cnt->pair_col_off[col] + t0;
-        if (k < c.cnt->pair_col_off[col + 1]) {
+        if (s_joff[col + 1] != s_joff[col]) return;
+        uint32_t k = s_poff[col] + t0;
+        if (k < s_poff[col + 1]) {
             rec = load_pair_rec(c, k);
             rec_k = k;
             have = true;
@@ -314,8 +321,8 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
     auto prefetch_vel = [&](int col, uint32_t t0) {
         have = false;
         if (col >= 64) return;
-        uint32_t k = c.cnt->pair_col_off[col] + t0;
-        if (k < c.cnt->pair_col_off[col + 1]) {
+        uint32_t k = s_poff[col] + t0;
+        if (k < s_poff[col + 1]) {
             rec_lam = ld4(c.lam, k);
             rec = load_pair_rec(c, k);
             rec_k = k;
@@ -345,7 +352,7 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         have = false;
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_pos_pair(c, rec_k, rec);
-            stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth, have);
+            stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth, have, s_joff, s_poff);
             prefetch_pos(next_bit(big, col), tid);
             grid.sync();
         }
@@ -356,7 +363,8 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
                 have = false;
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     if (have) solve_pos_pair(c, rec_k, rec);
-                    stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x, have);
+                    stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x, have, s_joff,
+                                    s_poff);
                     prefetch_pos(next_bit(small, col), threadIdx.x);
                     __syncthreads();
                 }
@@ -371,7 +379,7 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         have = false;
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
-            stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth, have);
+            stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth, have, s_poff);
             prefetch_vel(next_bit(big, col), tid);
             grid.sync();
         }
@@ -382,7 +390,7 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
                     stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x,
-                                    have);
+                                    have, s_poff);
                     prefetch_vel(next_bit(small, col), threadIdx.x);
                     __syncthreads();
                 }
