@@ -283,6 +283,12 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
                                                        float rest_threshold) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
+    // A colour's constraints go to threads in warp-sized runs dealt round-robin over the BLOCKS
+    // (run r -> block r % gridDim, warp r / gridDim), not block after block: a phase lasts as
+    // long as its slowest warp, and a colour of a few thousand constraints would otherwise fill
+    // every warp of a few SMs (16 warps contending for issue slots and the L1) while the rest of
+    // the GPU idles.  Which thread solves which constraint does not change any result.
+    const uint32_t stid = ((threadIdx.x >> 5) * gridDim.x + blockIdx.x) * 32u + (threadIdx.x & 31u);
     const uint32_t ncol = vload(&c.cnt->n_colours);
     const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
     const unsigned long long big = big_colour_mask(c, ncol);
@@ -341,6 +347,12 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
             t_prev = t;
         }
     };
+#ifdef SFP_PHASE_PROBE
+    uint32_t ph = 0;
+    long long pr_dur = 0, pr_wait0 = 0;
+    for (uint32_t i = tid; i < 512u; i += nth) c.cnt->round_flags[i] = 0u;
+    grid.sync();
+#endif
     lap(-1);
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
@@ -350,12 +362,71 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         grid.sync();
         lap(5);
         have = false;
+#ifdef SFP_PHASE_PROBE
+        // development probe (scripts/phase_probe.py).  Per big position phase: the slowest and
+        // fastest block's work time (cycles from leaving the previous barrier to arriving at
+        // this one) in round_flags[ph] / [256 + ph]; over all busy warps of all phases, the
+        // sum and maximum of the gather / compute / store / rest segments in [480..495].
+        for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
+            long long ts = clock64(), t1 = ts, t2 = ts, t3 = ts;
+            bool busy = false;
+            if (have) {
+                uint32_t cnt = sfp::f2u(rec.cb.y);
+                f4 lam;
+                lam.x = lam.y = lam.z = lam.w = 0.0f;
+                if (cnt > 0) {
+                    busy = true;
+                    sfp::BodyPos A = load_pos(c, rec.p.x), B = load_pos(c, rec.p.y);
+                    asm volatile("" ::"f"(A.x.x), "f"(B.x.x), "f"(A.d.x), "f"(B.d.x), "f"(A.im), "f"(B.im));
+                    t1 = clock64();
+                    lam = sfp::solve_contact_manifold(
+                        &A, &B, sfp::mk(rec.ca.x, rec.ca.y), cnt, sfp::mk(rec.q0.x, rec.q0.y),
+                        sfp::mk(rec.q0.z, rec.q0.w), sfp::mk(rec.q1.x, rec.q1.y),
+                        sfp::mk(rec.q1.z, rec.q1.w), rec.ca.z);
+                    asm volatile("" ::"f"(A.x.x), "f"(B.x.x), "f"(A.q.x), "f"(B.q.x), "f"(lam.x), "f"(lam.y));
+                    t2 = clock64();
+                    store_pos(c, rec.p.x, A);
+                    store_pos(c, rec.p.y, B);
+                }
+                st4(c.lam, rec_k, lam);
+                t3 = clock64();
+            }
+            stage_solve_pos(c, (uint32_t)col, inv_h2, stid, nth, have, s_joff, s_poff);
+            prefetch_pos(next_bit(big, col), stid);
+            long long t4 = clock64();
+            if (__any_sync(0xffffffffu, busy) && (threadIdx.x & 31u) == 0u) {
+                // lane 0's clock reads bracket the whole warp's (divergent) execution
+                uint32_t seg[4] = {(uint32_t)(t1 - ts), (uint32_t)(t2 - t1), (uint32_t)(t3 - t2),
+                                   (uint32_t)(t4 - t3)};
+                for (int k = 0; k < 4; ++k) {
+                    atomicAdd(&c.cnt->round_flags[480 + k], seg[k] >> 4);
+                    atomicMax(&c.cnt->round_flags[484 + k], seg[k]);
+                }
+                atomicAdd(&c.cnt->round_flags[488], 1u);
+            }
+            __syncthreads();
+            long long ta = clock64();
+            if (threadIdx.x == 0 && ph < 224u) {
+                uint32_t wk = (uint32_t)(ta - ts);
+                atomicMax(&c.cnt->round_flags[ph], wk);
+                atomicMax(&c.cnt->round_flags[256 + ph], 0xffffffffu - wk);
+            }
+            grid.sync();
+            long long te = clock64();
+            if (tid == 0) {
+                pr_dur += te - ts;
+                pr_wait0 += te - ta;
+            }
+            ++ph;
+        }
+#else
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_pos_pair(c, rec_k, rec);
-            stage_solve_pos(c, (uint32_t)col, inv_h2, tid, nth, have, s_joff, s_poff);
-            prefetch_pos(next_bit(big, col), tid);
+            stage_solve_pos(c, (uint32_t)col, inv_h2, stid, nth, have, s_joff, s_poff);
+            prefetch_pos(next_bit(big, col), stid);
             grid.sync();
         }
+#endif
         lap(6);
         if (small || serial) {
             if (blockIdx.x == 0) {
@@ -379,8 +450,8 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         have = false;
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
-            stage_solve_vel(c, (uint32_t)col, h, rest_threshold, tid, nth, have, s_poff);
-            prefetch_vel(next_bit(big, col), tid);
+            stage_solve_vel(c, (uint32_t)col, h, rest_threshold, stid, nth, have, s_poff);
+            prefetch_vel(next_bit(big, col), stid);
             grid.sync();
         }
         lap(8);
@@ -403,6 +474,19 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
     if (tid == 0) {
         for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
         c.cnt->stage_cycles[0] = (unsigned long long)__popcll(big);
+#ifdef SFP_PHASE_PROBE
+        unsigned long long smax = 0, smin = 0;
+        uint32_t np = ph < 224u ? ph : 224u;
+        for (uint32_t i = 0; i < np; ++i) {
+            smax += vload(&c.cnt->round_flags[i]);
+            smin += 0xffffffffu - vload(&c.cnt->round_flags[256 + i]);
+        }
+        c.cnt->stage_cycles[1] = smax;
+        c.cnt->stage_cycles[2] = smin;
+        c.cnt->stage_cycles[3] = np;
+        c.cnt->stage_cycles[4] = (unsigned long long)pr_dur;
+        c.cnt->stage_cycles[5] = (unsigned long long)pr_wait0;
+#endif
     }
 }
 
@@ -1409,6 +1493,15 @@ __attribute__((visibility("default"))) int32_t sfp_debug_stage_ns(SfpWorld* w, u
     Counters k;
     TRY(read_counters(w, &k));
     for (int i = 0; i < 10; ++i) out[i] = k.stage_cycles[i];
+    return SFP_OK;
+}
+
+// development aid: the 512 scratch words the colouring rounds (and the probe build) write
+__attribute__((visibility("default"))) int32_t sfp_debug_round_flags(SfpWorld* w, uint32_t out[512]) {
+    if (!w || !out) return SFP_E_INVALID;
+    Counters k;
+    TRY(read_counters(w, &k));
+    for (int i = 0; i < 512; ++i) out[i] = k.round_flags[i];
     return SFP_OK;
 }
 
