@@ -64,6 +64,24 @@ SFP_HD v2 rot_advance(v2 q, float dtheta) {
     float inv = 1.0f / sqrtf(c * c + s * s);
     return mk(c * inv, s * inv);
 }
+/* The same rotation for the positional corrections of the solver, where it sits on every
+ * constraint's dependent chain: renormalised with one Newton step of 1/sqrt (q * (1.5 - 0.5 |q|^2))
+ * instead of sqrtf and a division.  |q + dtheta perp q|^2 = 1 + dtheta^2, so the length error
+ * left behind is 3/8 dtheta^4 < 4e-7 for the |dtheta| <= 0.03 this branch accepts (the step is
+ * self-correcting: it measures the length it is given), and integrate_body() renormalises
+ * exactly once per substep anyway.  Larger corrections (light bodies on a taut joint) take the
+ * exact routine: the Newton step diverges beyond |dtheta| ~ 0.8. */
+SFP_HD v2 rot_nudge(v2 q, float dtheta) {
+#ifdef SFP_EXACT_NUDGE
+    return rot_advance(q, dtheta);
+#else
+    if (!(dtheta * dtheta <= 1.0e-3f)) return rot_advance(q, dtheta);
+    float c = q.x - dtheta * q.y;
+    float s = q.y + dtheta * q.x;
+    float k = 1.5f - 0.5f * (c * c + s * s);
+    return mk(c * k, s * k);
+#endif
+}
 /* tan of the angle from qp to q */
 SFP_HD float rot_delta_tan(v2 q, v2 qp) {
     float sd = q.y * qp.x - q.x * qp.y;
@@ -848,8 +866,8 @@ SFP_HD void apply_pos(BodyPos* A, BodyPos* B, v2 ra, v2 rb, v2 P) {
     B->d = B->d + ub;
     float da = -(A->ii * cross(ra, P));
     float db = B->ii * cross(rb, P);
-    if (A->ii > 0.0f) A->q = rot_advance(A->q, da);
-    if (B->ii > 0.0f) B->q = rot_advance(B->q, db);
+    if (A->ii > 0.0f) A->q = rot_nudge(A->q, da);
+    if (B->ii > 0.0f) B->q = rot_nudge(B->q, db);
 }
 
 /* 2x2 (or 1x1) non-penetration solve of a manifold at the bodies' current poses; adds the
@@ -874,8 +892,9 @@ SFP_HD void solve_manifold_normal(BodyPos* A, BodyPos* B, v2 n, uint32_t count, 
         float det = a00 * a11 - a01 * a01;
         if (det > 1.0e-3f * (a00 * a11)) {
             /* both active */
-            float x0 = (a11 * d0 - a01 * d1) / det;
-            float x1 = (a00 * d1 - a01 * d0) / det;
+            float inv = 1.0f / det; /* one division on the chain, not two */
+            float x0 = (a11 * d0 - a01 * d1) * inv;
+            float x1 = (a00 * d1 - a01 * d0) * inv;
             if (x0 >= 0.0f && x1 >= 0.0f) {
                 l0 = x0;
                 l1 = x1;
@@ -903,8 +922,8 @@ SFP_HD void solve_manifold_normal(BodyPos* A, BodyPos* B, v2 n, uint32_t count, 
         B->d = B->d + ub;
         float da = -(A->ii * (ka0 * l0 + ka1 * l1));
         float db = B->ii * (kb0 * l0 + kb1 * l1);
-        if (A->ii > 0.0f) A->q = rot_advance(A->q, da);
-        if (B->ii > 0.0f) B->q = rot_advance(B->q, db);
+        if (A->ii > 0.0f) A->q = rot_nudge(A->q, da);
+        if (B->ii > 0.0f) B->q = rot_nudge(B->q, db);
     }
     *l0_acc = *l0_acc + l0;
     *l1_acc = *l1_acc + l1;
@@ -935,8 +954,9 @@ SFP_HD f4 solve_contact_manifold(BodyPos* A, BodyPos* B, v2 n, uint32_t count, v
     if (count > 1u && lam.x > 0.0f && lam.z > 0.0f) {
         v2 dp = B->d - A->d;
         v2 dpt = dp - dot(dp, n) * n;
-        float tl = len(dpt);
         float wl = A->im + B->im;
+#ifdef SFP_EXACT_NUDGE
+        float tl = len(dpt);
         if (tl > SFP_EPS && wl > 0.0f) {
             float dlt = tl / wl;
             if (dlt < mu_s * (lam.x + lam.z)) {
@@ -950,6 +970,24 @@ SFP_HD f4 solve_contact_manifold(BodyPos* A, BodyPos* B, v2 n, uint32_t count, v
                 lam.w = 0.5f * dlt;
             }
         }
+#else
+        /* the multiplier is |dpt| / wl and the correction P = -dpt / wl: the bodies only need
+         * 1 / wl (known before the normal solve) and the cone test compares squares, so no
+         * square root or second division stands between the normal solve and the body update */
+        float tl2 = dot(dpt, dpt);
+        float lim = mu_s * (lam.x + lam.z) * wl;
+        if (tl2 > SFP_EPS * SFP_EPS && wl > 0.0f && tl2 < lim * lim) {
+            v2 P = (-1.0f / wl) * dpt;
+            v2 ua = A->im * P, ub = B->im * P;
+            A->x = A->x - ua;
+            A->d = A->d - ua;
+            B->x = B->x + ub;
+            B->d = B->d + ub;
+            float dlt = sqrtf(tl2) / wl;
+            lam.y = 0.5f * dlt;
+            lam.w = 0.5f * dlt;
+        }
+#endif
     }
     return lam;
 }
@@ -1037,26 +1075,29 @@ SFP_HD void solve_manifold_velocity(BodyVel* A, BodyVel* B, v2 qa, v2 qb, v2 n, 
         float det2 = k00 * k11 - k01 * k01;
         float p0 = 0.0f, p1 = 0.0f, pt = 0.0f;
         if (det2 > 1.0e-3f * (k00 * k11)) {
-            /* 3x3 by cofactors */
+            /* 3x3 by cofactors; the two reciprocals are independent of each other and of the
+             * right-hand sides, so no division waits for another one */
+            float inv2 = 1.0f / det2;
             float c00 = k11 * ktt - k1t * k1t, c01 = k0t * k1t - k01 * ktt;
             float c02 = k01 * k1t - k0t * k11;
             float det3 = k00 * c00 + k01 * c01 + k0t * c02;
             if (det3 > 1.0e-4f * (k00 * k11 * ktt)) {
+                float inv3 = 1.0f / det3;
                 float c11 = k00 * ktt - k0t * k0t, c12 = k01 * k0t - k00 * k1t;
                 float c22 = det2;
-                float ptf = (c02 * b0 + c12 * b1 + c22 * bt) / det3;
+                float ptf = (c02 * b0 + c12 * b1 + c22 * bt) * inv3;
                 pt = coulomb(ptf, lam.x + lam.z, mu_s, mu_d, h);
                 if (pt == ptf) {
-                    p0 = (c00 * b0 + c01 * b1 + c02 * bt) / det3;
-                    p1 = (c01 * b0 + c11 * b1 + c12 * bt) / det3;
+                    p0 = (c00 * b0 + c01 * b1 + c02 * bt) * inv3;
+                    p1 = (c01 * b0 + c11 * b1 + c12 * bt) * inv3;
                 } else {
                     float r0 = b0 - k0t * pt, r1 = b1 - k1t * pt;
-                    p0 = (k11 * r0 - k01 * r1) / det2;
-                    p1 = (k00 * r1 - k01 * r0) / det2;
+                    p0 = (k11 * r0 - k01 * r1) * inv2;
+                    p1 = (k00 * r1 - k01 * r0) * inv2;
                 }
             } else {
-                p0 = (k11 * b0 - k01 * b1) / det2;
-                p1 = (k00 * b1 - k01 * b0) / det2;
+                p0 = (k11 * b0 - k01 * b1) * inv2;
+                p1 = (k00 * b1 - k01 * b0) * inv2;
             }
         } else if (k00 > 0.0f) {
             p0 = b0 / k00;
