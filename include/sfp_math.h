@@ -724,10 +724,15 @@ struct ContactRec {
     f4 s;  /* sep0, sep1 at narrowphase time, 0, 0              */
 };
 
-/* 0..15: (type of a) * 4 + (type of b); pairs are bucketed by it so that a warp runs one
- * narrowphase routine instead of several */
+/* 0..3: which narrowphase routine a pair runs — both circles / one circle / neither / a general
+ * polygon involved.  Pairs are bucketed by (colour, this class) so that a warp runs one routine
+ * instead of several; colour (6 bits) and class (SFP_TYPE_BITS) make an 8-bit sort key, one
+ * radix pass. */
+#define SFP_TYPE_BITS 2
 SFP_HD uint32_t pair_type_key(f4 shape_a, f4 shape_b) {
-    return shape_type(shape_a) * 4u + shape_type(shape_b);
+    uint32_t ta = shape_type(shape_a), tb = shape_type(shape_b);
+    if (ta == 3u || tb == 3u) return 3u;
+    return (ta != 0u ? 1u : 0u) + (tb != 0u ? 1u : 0u);
 }
 
 template <bool POLYS>

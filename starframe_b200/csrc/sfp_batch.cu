@@ -143,11 +143,11 @@ __device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint
     (void)smem9;
 }
 
-// bucket pairs by (colour, shape-type pair): counting sort on the 10-bit key written by
+// bucket pairs by (colour, narrowphase class): counting sort on the 8-bit key written by
 // stage_colour_take.  Ranks inside a bin come from a shared-memory cursor (integer atomics): the
 // order INSIDE a (colour, type) bin is therefore arbitrary, which changes no result — constraints
 // of one colour touch disjoint bodies — only which contact slot a pair happens to use.
-constexpr int BUCKET_BINS = SFP_MAX_COLOURS * 16;
+constexpr int BUCKET_BINS = SFP_MAX_COLOURS << SFP_TYPE_BITS;
 __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
     __shared__ uint32_t bins[BUCKET_BINS];
     const uint32_t tid = threadIdx.x, nth = blockDim.x;
@@ -173,7 +173,7 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
     }
     __syncthreads();
     for (uint32_t col = tid; col <= SFP_MAX_COLOURS; col += nth) {
-        c.cnt->pair_col_off[col] = (col < SFP_MAX_COLOURS) ? bins[col * 16] : P;
+        c.cnt->pair_col_off[col] = (col < SFP_MAX_COLOURS) ? bins[col << SFP_TYPE_BITS] : P;
         c.cnt->joint_col_off[col] = 0;
     }
     __syncthreads();

@@ -259,7 +259,7 @@ __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, ui
             if ((slot & SFP_CTAB_KEYMASK) == key) {
                 uint32_t col = (uint32_t)(slot >> 44) - 1u;
                 colour_keep(c, p.x, p.y, col);
-                c.pcol[k] = (col << 4) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+                c.pcol[k] = (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
                 break;
             }
             h = (h + 1u) & c.tab_mask;
@@ -279,7 +279,7 @@ __device__ __forceinline__ void stage_colour_record(const Ctx& c, uint32_t tid, 
         uint32_t key16 = c.pcol[k];
         if (key16 == UNCOLOURED) continue;
         uint2 p = c.pairs_raw[k];
-        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, key16 >> 4);
+        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, key16 >> SFP_TYPE_BITS);
         uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
         while (atomicCAS(&c.tab_new[h], 0ull, packed) != 0ull) h = (h + 1u) & c.tab_mask;
     }
@@ -384,7 +384,7 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
             // sort key: colour in the high bits, shape-type pair in the low 4 (narrowphase
             // coherence inside a colour bucket)
             if (col != UNCOLOURED)
-                col = (col << 4) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+                col = (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
             c.pcol[k] = col;
         }
     for (uint32_t k = tid; k < c.nj; k += nth)
@@ -411,7 +411,7 @@ __device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_
     const uint32_t P = c.cnt->n_pairs;
     for (uint32_t i = tid; i < P; i += nth) {
         c.pairs[i] = c.pairs_raw[c.pperm[i]];
-        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off, 4);
+        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off, SFP_TYPE_BITS);
     }
     if (P == 0 && tid == 0)
         for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->pair_col_off[cc] = 0;

@@ -169,7 +169,7 @@ k_radix_hist(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ n_p
 // Above RADIX_INLINE_BLOCKS live blocks the per-block sweep over the histogram would be
 // quadratic in the block count, so one block per digit scans that digit's column in place and
 // leaves the column total behind the histogram (hist[n_blocks * 256 + digit]).
-constexpr uint32_t RADIX_INLINE_BLOCKS = 512;
+constexpr uint32_t RADIX_INLINE_BLOCKS = 32;
 static __global__ void __launch_bounds__(256)
 k_radix_colscan(uint32_t* __restrict__ hist, uint32_t n_blocks, const uint32_t* __restrict__ n_ptr) {
     __shared__ uint32_t sm[9];

@@ -243,12 +243,21 @@ __global__ void __launch_bounds__(TPB) k_unpack_states(const sfp::StateRec* __re
 __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
+    // wall time of the parts (ns, thread 0) -> stage_cycles[1..3]: init + warm, rounds, record
+    unsigned long long t0 = 0, t1 = 0, t2 = 0;
+    auto now = [&]() {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        return t;
+    };
+    if (tid == 0) t0 = now();
     stage_colour_init(c, tid, nth);
     grid.sync();
     if (c.warm) {
         stage_colour_warm(c, tid, nth);
         grid.sync();
     }
+    if (tid == 0) t1 = now();
     uint32_t round = 0;
     for (; round < (uint32_t)MAX_ROUNDS; ++round) {
         stage_colour_bid(c, round, tid, nth);
@@ -258,7 +267,13 @@ __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
         if (vload(&c.cnt->round_flags[round]) == 0u) break;
     }
     if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+    if (tid == 0) t2 = now();
     stage_colour_record(c, tid, nth);
+    if (tid == 0) {
+        c.cnt->stage_cycles[1] = t1 - t0;
+        c.cnt->stage_cycles[2] = t2 - t1;
+        c.cnt->stage_cycles[3] = now() - t2;
+    }
 }
 
 // Colours are split into BIG ones (more than SFP_TAIL_ITEMS constraints: one grid-wide phase
@@ -749,17 +764,15 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
         k_colour_record<<<gp, TPB, 0, st>>>(c);
         w->launches += 1;
     }
-    // stable LSD sort of the pairs by (colour, shape-type pair): key = colour << 4 | type, 10 bits
-    CU(radix_pass(c.pcol, nullptr, c.pkey_tmp, c.pval_tmp, &w->d_cnt->n_pairs, w->cap_pairs, 0,
+    // stable sort of the pairs by (colour, narrowphase class): an 8-bit key, one radix pass
+    CU(radix_pass(c.pcol, nullptr, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs, 0,
                   w->d_hist, st));
-    CU(radix_pass(c.pkey_tmp, c.pval_tmp, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs,
-                  8, w->d_hist, st));
     if (w->nj)
         CU(radix_pass(c.jcol, nullptr, c.jcol_sorted, c.jperm, &w->d_cnt->n_joints, w->cap_joints,
                       0, w->d_hist, st));
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 5 + (w->nj ? 2 : 0) + (radix_blocks(w->cap_pairs) > RADIX_INLINE_BLOCKS ? 2 : 0) +
+    w->launches += 3 + (w->nj ? 2 : 0) + (radix_blocks(w->cap_pairs) > RADIX_INLINE_BLOCKS ? 1 : 0) +
                    ((w->nj && radix_blocks(w->cap_joints) > RADIX_INLINE_BLOCKS) ? 1 : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_col, st, w->capturing ? cudaEventRecordExternal : 0));
     return SFP_OK;
