@@ -33,7 +33,8 @@ struct Counters {
     uint32_t n_colours, colour_rounds;
     uint32_t overflow;
     uint32_t n_contacts, n_manifolds, maxpen_bits;
-    uint32_t pad[2];
+    uint32_t n_unc;  // length of Ctx::unc (pairs still uncoloured after the warm start)
+    uint32_t pad[1];
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
     uint32_t round_flags[MAX_ROUNDS];
@@ -59,8 +60,10 @@ struct Ctx {
     // colouring
     unsigned long long *mask, *claim0, *claim1;
     uint32_t *pcol, *jcol;
+    // pairs that the warm start left uncoloured, in any order (null: the rounds walk all pairs);
+    // after a warm start that is a few per cent of the pairs
+    uint32_t* unc;
     uint32_t *pcol_sorted, *pperm, *jcol_sorted, *jperm;
-    uint32_t *pkey_tmp, *pval_tmp;  // ping-pong buffers of the two-pass (type, colour) sort
     // colour tables (sfp_math.h, SFP_CTAB_*): last frame's (read) and this frame's (built)
     unsigned long long *tab_old, *tab_new;
     uint32_t tab_mask;  // slots - 1 (power of two)
@@ -224,6 +227,12 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
         c.claim1[i] = SFP_NO_CLAIM;
     }
     for (uint32_t k = tid; k < P; k += nth) c.pcol[k] = UNCOLOURED;
+    if (c.unc) {
+        // no warm start: every pair is on the list; warm start: stage_colour_warm appends
+        if (!c.warm)
+            for (uint32_t k = tid; k < P; k += nth) c.unc[k] = k;
+        if (tid == 0) c.cnt->n_unc = c.warm ? 0u : P;
+    }
     for (uint32_t k = tid; k < c.nj; k += nth) {
         uint2 jb = c.jbod_in[k];
         bool dyn = (c.meta[jb.x].w | c.meta[jb.y].w) != 0;
@@ -249,20 +258,37 @@ __device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b
 __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, uint32_t nth) {
     if (!c.warm) return;
     const uint32_t P = c.cnt->n_pairs;
-    for (uint32_t k = tid; k < P; k += nth) {
-        uint2 p = c.pairs_raw[k];
-        const unsigned long long key = sfp::ctab_key(p.x, p.y);
-        uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
-        for (;;) {
-            unsigned long long slot = c.tab_old[h];
-            if (slot == 0ull) break;
-            if ((slot & SFP_CTAB_KEYMASK) == key) {
-                uint32_t col = (uint32_t)(slot >> 44) - 1u;
-                colour_keep(c, p.x, p.y, col);
-                c.pcol[k] = (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
-                break;
+    // (whole warps walk the loop together: the append below is warp-aggregated)
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t base = tid - lane; base < P; base += nth) {
+        const uint32_t k = base + lane;
+        bool found = k >= P;  // lanes past the end have nothing to append
+        if (k < P) {
+            uint2 p = c.pairs_raw[k];
+            const unsigned long long key = sfp::ctab_key(p.x, p.y);
+            uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
+            for (;;) {
+                unsigned long long slot = c.tab_old[h];
+                if (slot == 0ull) break;
+                if ((slot & SFP_CTAB_KEYMASK) == key) {
+                    uint32_t col = (uint32_t)(slot >> 44) - 1u;
+                    colour_keep(c, p.x, p.y, col);
+                    c.pcol[k] = (col << SFP_TYPE_BITS) |
+                                sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+                    found = true;
+                    break;
+                }
+                h = (h + 1u) & c.tab_mask;
             }
-            h = (h + 1u) & c.tab_mask;
+        }
+        if (c.unc) {
+            const uint32_t miss = __ballot_sync(0xffffffffu, !found);
+            if (miss) {
+                uint32_t at = 0;
+                if (lane == 0) at = atomicAdd(&c.cnt->n_unc, (uint32_t)__popc(miss));
+                at = __shfl_sync(0xffffffffu, at, 0);
+                if (!found) c.unc[at + __popc(miss & ((1u << lane) - 1u))] = k;
+            }
         }
     }
     for (uint32_t k = tid; k < c.nj; k += nth) {
@@ -335,12 +361,14 @@ __device__ __forceinline__ void colour_bid_one(const Ctx& c, unsigned long long*
 __device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, uint32_t tid,
                                                  uint32_t nth) {
     unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
-    const uint32_t P = c.cnt->n_pairs;
-    for (uint32_t k = tid; k < P; k += nth)
+    const uint32_t P = c.unc ? c.cnt->n_unc : c.cnt->n_pairs;
+    for (uint32_t i = tid; i < P; i += nth) {
+        const uint32_t k = c.unc ? c.unc[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
             colour_bid_one(c, claim, p.x, p.y, sfp::pair_priority(p.x, p.y));
         }
+    }
     for (uint32_t k = tid; k < c.nj; k += nth)
         if (c.jcol[k] == UNCOLOURED) {
             uint2 p = c.jbod_in[k];
@@ -375,18 +403,20 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
                                                   uint32_t nth) {
     unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
     unsigned long long* next_claim = (round & 1u) ? c.claim0 : c.claim1;
-    const uint32_t P = c.cnt->n_pairs;
-    for (uint32_t k = tid; k < P; k += nth)
+    const uint32_t P = c.unc ? c.cnt->n_unc : c.cnt->n_pairs;
+    for (uint32_t i = tid; i < P; i += nth) {
+        const uint32_t k = c.unc ? c.unc[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
             uint32_t col = colour_take_one(c, claim, next_claim, p.x, p.y,
                                            sfp::pair_priority(p.x, p.y), round);
-            // sort key: colour in the high bits, shape-type pair in the low 4 (narrowphase
-            // coherence inside a colour bucket)
+            // sort key: colour in the high bits, narrowphase class in the low ones (coherence
+            // inside a colour bucket)
             if (col != UNCOLOURED)
                 col = (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
             c.pcol[k] = col;
         }
+    }
     for (uint32_t k = tid; k < c.nj; k += nth)
         if (c.jcol[k] == UNCOLOURED) {
             uint2 p = c.jbod_in[k];

@@ -626,10 +626,9 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.pairs_raw, cp, bag));
     TRY(alloc_dev(w, &c.pairs, cp, bag));
     TRY(alloc_dev(w, &c.pcol, cp, bag));
+    TRY(alloc_dev(w, &c.unc, cp, bag));
     TRY(alloc_dev(w, &c.pcol_sorted, cp, bag));
     TRY(alloc_dev(w, &c.pperm, cp, bag));
-    TRY(alloc_dev(w, &c.pkey_tmp, cp, bag));
-    TRY(alloc_dev(w, &c.pval_tmp, cp, bag));
     TRY(alloc_dev(w, &c.ca, cp, bag));
     TRY(alloc_dev(w, &c.cb, cp, bag));
     TRY(alloc_dev(w, &c.cp0, cp, bag));
@@ -741,8 +740,12 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     w->colour_age += 1;
     CU(cudaMemsetAsync(c.tab_new, 0, sizeof(unsigned long long) * w->tab_slots, st));
     if (!multi) {
-        uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_colour,
-                                             blocks_for(w, 4ull * w->n + w->nj));
+        // a grid barrier costs 1.2 us with 2-3 CTAs per SM and ~3 us with 8, and the kernel is a
+        // dozen barriers around loops that are short for a 100 k-body world (measured: 3 CTAs
+        // per SM best there, 8 best for 4 M bodies) — so the grid grows with the world
+        const uint32_t full = blocks_for(w, 4ull * w->n + w->nj);
+        const uint32_t want = std::min<uint32_t>(full, std::max<uint32_t>(3u * (uint32_t)w->n_sm, full / 8u));
+        uint32_t blocks = std::min<uint32_t>((uint32_t)w->coop_max_colour, want);
         void* args[] = {&c};
         TRY(launch_coop(w, (const void*)k_colour_coop, blocks, args));
         w->launches += 1;
