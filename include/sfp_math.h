@@ -229,6 +229,8 @@ SFP_HD int cell_coord(float x, float inv_cell) {
  * covers more than SFP_MAX_CELLS_PER_BODY cells (a runaway body; the caller raises the
  * overflow flag): such a body takes no part in the broadphase. */
 #define SFP_MAX_CELLS_PER_BODY 16384
+#define SFP_KEY_BITS 12
+#define SFP_KEY_SPAN (1 << SFP_KEY_BITS)
 SFP_HD bool cell_range(f4 bb, float inv_cell, int* x0, int* y0, int* x1, int* y1) {
     bool finite = (bb.x - bb.x == 0.0f) && (bb.y - bb.y == 0.0f) && (bb.z - bb.z == 0.0f) &&
                   (bb.w - bb.w == 0.0f);
@@ -237,7 +239,8 @@ SFP_HD bool cell_range(f4 bb, float inv_cell, int* x0, int* y0, int* x1, int* y1
     *x1 = cell_coord(bb.z, inv_cell);
     *y1 = cell_coord(bb.w, inv_cell);
     long long cells = (long long)(*x1 - *x0 + 1) * (long long)(*y1 - *y0 + 1);
-    if (!finite || cells > SFP_MAX_CELLS_PER_BODY || cells <= 0) {
+    if (!finite || cells > SFP_MAX_CELLS_PER_BODY || cells <= 0 ||
+        *x1 - *x0 >= SFP_KEY_SPAN || *y1 - *y0 >= SFP_KEY_SPAN) {
         *x1 = *x0 - 1;
         *y1 = *y0 - 1;
         return false;
@@ -245,12 +248,21 @@ SFP_HD bool cell_range(f4 bb, float inv_cell, int* x0, int* y0, int* x1, int* y1
     return true;
 }
 
-/* 32-bit cell key: row-major over the clamped 65536 x 65536 cell lattice */
+/* 24-bit cell key (three 8-bit radix passes): the cell coordinates modulo SFP_KEY_SPAN = 4096,
+ * row-major.  Cells 4096 apart share a key, which only adds candidates that fail the AABB test;
+ * a body's own cells never alias (cell_range refuses spans of 4096 cells or more).  The pair
+ * rule "reported from the cell holding the larger of the two lower corners" is evaluated
+ * modulo the span as well (same_cell). */
 SFP_HD uint32_t cell_key(int cx, int cy) {
-    return ((uint32_t)(cy - SFP_CELL_MIN) << 16) | (uint32_t)(cx - SFP_CELL_MIN);
+    return (((uint32_t)cy & (SFP_KEY_SPAN - 1u)) << SFP_KEY_BITS) | ((uint32_t)cx & (SFP_KEY_SPAN - 1u));
 }
-SFP_HD int key_cx(uint32_t key) { return (int)(key & 0xffffu) + SFP_CELL_MIN; }
-SFP_HD int key_cy(uint32_t key) { return (int)(key >> 16) + SFP_CELL_MIN; }
+SFP_HD int key_cx(uint32_t key) { return (int)(key & (SFP_KEY_SPAN - 1u)); }
+SFP_HD int key_cy(uint32_t key) { return (int)(key >> SFP_KEY_BITS); }
+/* is the cell with true coordinates (x, y) the one a key with (key_cx, key_cy) stands for? */
+SFP_HD bool same_cell(int x, int y, int kcx, int kcy) {
+    return (((uint32_t)x & (SFP_KEY_SPAN - 1u)) == (uint32_t)kcx) &&
+           (((uint32_t)y & (SFP_KEY_SPAN - 1u)) == (uint32_t)kcy);
+}
 
 SFP_HD bool aabb_overlap(f4 a, f4 b) {
     return a.x <= b.z && b.x <= a.z && a.y <= b.w && b.y <= a.w;

@@ -117,7 +117,7 @@ int broadphase(SfpWorld& w, float dt) {
             for (size_t v = u + 1; v < j; ++v) {
                 uint32_t a = entries[u].body, b = entries[v].body;
                 if (a == b) continue;
-                if (std::max(cx0[a], cx0[b]) != cx || std::max(cy0[a], cy0[b]) != cy) continue;
+                if (!same_cell(std::max(cx0[a], cx0[b]), std::max(cy0[a], cy0[b]), cx, cy)) continue;
                 if (!aabb_overlap(aabb[a], aabb[b])) continue;
                 if (!pair_allowed(w, a, b)) continue;
                 SfpPair p = {std::min(a, b), std::max(a, b)};

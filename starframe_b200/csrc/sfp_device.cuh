@@ -125,7 +125,9 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
     }
 }
 
-// (cell, body) entries.  A body covering few cells writes them itself; a body covering many
+// (cell, body) entries, written to the SECOND buffer pair: the three radix passes that follow
+// (24-bit key) ping-pong 1 -> 0 -> 1 -> 0 and leave the sorted list in ekey0 / eval0.
+// A body covering few cells writes them itself; a body covering many
 // (the floor of a pile covers thousands) is handed to its whole warp, 32 cells per step.
 __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, uint32_t nth) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -144,8 +146,8 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
             for (int cy = y0; cy <= y1; ++cy)
                 for (int cx = x0; cx <= x1; ++cx) {
                     if (o < c.cap_entries) {
-                        c.ekey0[o] = sfp::cell_key(cx, cy);
-                        c.eval0[o] = i;
+                        c.ekey1[o] = sfp::cell_key(cx, cy);
+                        c.eval1[o] = i;
                     }
                     ++o;
                 }
@@ -163,8 +165,8 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
             for (uint32_t k = lane; k < bcnt; k += 32u) {
                 uint32_t pos = bo + k;
                 if (pos < c.cap_entries) {
-                    c.ekey0[pos] = sfp::cell_key(bx0 + (int)(k % w), by0 + (int)(k / w));
-                    c.eval0[pos] = bi;
+                    c.ekey1[pos] = sfp::cell_key(bx0 + (int)(k % w), by0 + (int)(k / w));
+                    c.eval1[pos] = bi;
                 }
             }
         }
@@ -181,7 +183,7 @@ __device__ __forceinline__ bool pair_test(const Ctx& c, int cx, int cy, uint32_t
     if (a == b) return false;
     int4 mb = c.meta[b];
     if ((ma.w | mb.w) == 0) return false;
-    if (max(ma.x, mb.x) != cx || max(ma.y, mb.y) != cy) return false;
+    if (!sfp::same_cell(max(ma.x, mb.x), max(ma.y, mb.y), cx, cy)) return false;
     if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
     return sfp::aabb_overlap(bba, ld4(c.aabb, b));
 }

@@ -694,15 +694,18 @@ uint32_t blocks_for(const SfpWorld* w, uint64_t items) {
     return (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(b, cap));
 }
 
+constexpr int SFP_KEY_PASSES = (2 * SFP_KEY_BITS + 7) / 8;
+static_assert(SFP_KEY_PASSES % 2 == 1, "stage_emit_entries writes buffer 1; an odd pass count ends in buffer 0");
 int sort_entries(SfpWorld* w) {
     Ctx& c = w->ctx;
     const uint32_t* n_ptr = &w->d_cnt->n_entries;
     // the hist grid must match between hist and scatter: radix_pass derives it from cap
-    for (int pass = 0; pass < 4; ++pass) {
-        const uint32_t* ki = (pass & 1) ? c.ekey1 : c.ekey0;
-        const uint32_t* vi = (pass & 1) ? c.eval1 : c.eval0;
-        uint32_t* ko = (pass & 1) ? c.ekey0 : c.ekey1;
-        uint32_t* vo = (pass & 1) ? c.eval0 : c.eval1;
+    for (int pass = 0; pass < SFP_KEY_PASSES; ++pass) {
+        const bool back = (pass & 1) != 0;  // 1 -> 0 -> 1 -> 0: sorted entries end in ekey0 / eval0
+        const uint32_t* ki = back ? c.ekey0 : c.ekey1;
+        const uint32_t* vi = back ? c.eval0 : c.eval1;
+        uint32_t* ko = back ? c.ekey1 : c.ekey0;
+        uint32_t* vo = back ? c.eval1 : c.eval0;
         CU(radix_pass(ki, vi, ko, vo, n_ptr, w->cap_entries, pass * 8, w->d_hist, w->stream));
     }
     return SFP_OK;
@@ -730,7 +733,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                       &w->d_cnt->n_pairs, st));
     k_pair_write<<<ge, TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 4 + 3 + 3 + 8 + (radix_blocks(w->cap_entries) > RADIX_INLINE_BLOCKS ? 4 : 0);
+    w->launches += 4 + 3 + 3 + 2 * SFP_KEY_PASSES +
+                   (radix_blocks(w->cap_entries) > RADIX_INLINE_BLOCKS ? SFP_KEY_PASSES : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_bp, st, w->capturing ? cudaEventRecordExternal : 0));
 
     // warm start: read last frame's table, build this frame's in the other one
