@@ -747,24 +747,28 @@ SFP_HD uint32_t pair_type_key(f4 shape_a, f4 shape_b) {
     return (ta != 0u ? 1u : 0u) + (tb != 0u ? 1u : 0u);
 }
 
-template <bool POLYS>
-SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
-                              f4 shape_b, f4 mat_b, float margin, const f4* table) {
+/* bounding-circle reject: most candidate pairs of a frame are not touching in a given substep,
+ * and this costs a dozen flops instead of a SAT */
+SFP_HD bool narrowphase_far(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float margin) {
+    float ba = sqrtf(shape_a.x * shape_a.x + shape_a.y * shape_a.y) + shape_a.z;
+    float bb = sqrtf(shape_b.x * shape_b.x + shape_b.y * shape_b.y) + shape_b.z;
+    float dx = pose_b.x - pose_a.x, dy = pose_b.y - pose_a.y;
+    float reach = (ba + bb) + margin;
+    return dx * dx + dy * dy >= reach * reach;
+}
+SFP_HD ContactRec empty_contact() {
     ContactRec c;
-    {
-        /* bounding-circle reject: most candidate pairs of a frame are not touching in a given
-         * substep, and this costs a dozen flops instead of a SAT */
-        float ba = sqrtf(shape_a.x * shape_a.x + shape_a.y * shape_a.y) + shape_a.z;
-        float bb = sqrtf(shape_b.x * shape_b.x + shape_b.y * shape_b.y) + shape_b.z;
-        float dx = pose_b.x - pose_a.x, dy = pose_b.y - pose_a.y;
-        float reach = (ba + bb) + margin;
-        if (dx * dx + dy * dy >= reach * reach) {
-            f4 z;
-            z.x = z.y = z.z = z.w = 0.0f;
-            c.a = c.b = c.p0 = c.p1 = c.s = z;
-            return c;
-        }
-    }
+    f4 z;
+    z.x = z.y = z.z = z.w = 0.0f;
+    c.a = c.b = c.p0 = c.p1 = c.s = z;
+    return c;
+}
+
+/* the contact record of a pair that passed narrowphase_far() */
+template <bool POLYS>
+SFP_HD ContactRec narrowphase_near(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
+                                   f4 shape_b, f4 mat_b, float margin, const f4* table) {
+    ContactRec c;
     Manifold m = collide<POLYS>(pose_a, shape_a, pose_b, shape_b, margin, table);
     v2 qa = mk(pose_a.z, pose_a.w), qb = mk(pose_b.z, pose_b.w);
     v2 dab = mk(pose_b.x - pose_a.x, pose_b.y - pose_a.y);
@@ -799,6 +803,14 @@ SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose
     c.s.z = 0.0f;
     c.s.w = 0.0f;
     return c;
+}
+
+template <bool POLYS>
+SFP_HD ContactRec narrowphase(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
+                              f4 shape_b, f4 mat_b, float margin, const f4* table) {
+    if (narrowphase_far(pose_a, shape_a, pose_b, shape_b, margin)) return empty_contact();
+    return narrowphase_near<POLYS>(pose_a, vel_a, shape_a, mat_a, pose_b, vel_b, shape_b, mat_b, margin,
+                                   table);
 }
 
 /* contact event of one pair from its records (layout of SfpContactEvent in sfp.h) */
