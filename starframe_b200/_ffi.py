@@ -110,7 +110,7 @@ PRODUCT_SYMBOLS = [
     "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host",
     "alloc_host_states", "free_host_states",
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
-    "batch_download", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
+    "batch_download", "batch_step_host", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
@@ -190,6 +190,7 @@ class Api:
             "batch_step": [vp, f32, u32],
             "batch_sync": [vp],
             "batch_download": [vp, vp],
+            "batch_step_host": [vp, vp, vp, f32, u32],
             "batch_stats": [vp, vp],
             "batch_last_step_ms": [vp, C.POINTER(f32)],
             "step_small_noalloc": [vp, vp, u32, f32, u32, u32, vp, C.c_char_p, u32],
@@ -452,6 +453,16 @@ class Batch:
         out = np.zeros(self.n_worlds * self.bpw, dtype=BODY_STATE_DTYPE)
         self._check(self.api.fn("batch_download")(self.h, _ptr(out)), "batch_download")
         return out.reshape(self.n_worlds, self.bpw)
+
+    def step_host(self, states: np.ndarray, dt: float = 1.0 / 60.0, substeps: int = 8,
+                  out: np.ndarray | None = None) -> np.ndarray:
+        """host states in -> one frame -> host states out (n_worlds * bpw, world-major)"""
+        s = np.ascontiguousarray(states, dtype=BODY_STATE_DTYPE).reshape(-1)
+        if out is None:
+            out = np.zeros(self.n_worlds * self.bpw, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("batch_step_host")(self.h, _ptr(s), _ptr(out), dt, substeps),
+                    "batch_step_host")
+        return out
 
     def stats(self) -> np.ndarray:
         out = np.zeros(self.n_worlds, dtype=STATS_DTYPE)

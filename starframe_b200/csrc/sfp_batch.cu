@@ -396,6 +396,40 @@ __global__ void __launch_bounds__(256) k_batch_pack(const float4* __restrict__ p
     }
 }
 
+// scene-graph states -> pose / vel (statics keep zero velocity).  A state whose rotor is zero
+// carries its rotation in `angle` only; the device's sincosf is used for it (the single-world
+// entry converts those on the host with libm — the last bits may differ).
+__global__ void __launch_bounds__(256) k_batch_unpack(const sfp::StateRec* __restrict__ in,
+                                                      const float2* __restrict__ minv,
+                                                      float4* __restrict__ pose,
+                                                      float4* __restrict__ vel, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const float4* q = reinterpret_cast<const float4*>(in + i);
+        float4 a = q[0], b = q[1];
+        sfp::StateRec r;
+        r.x = a.x, r.y = a.y, r.c = a.z, r.s = a.w, r.vx = b.x, r.vy = b.y, r.omega = b.z, r.angle = b.w;
+        if (!(r.c * r.c + r.s * r.s > 0.0f)) sincosf(r.angle, &r.s, &r.c);
+        float2 m = minv[i];
+        f2 mi;
+        mi.x = m.x, mi.y = m.y;
+        f4 p, v;
+        sfp::state_unpack(r, mi, &p, &v);
+        pose[i] = make_float4(p.x, p.y, p.z, p.w);
+        vel[i] = make_float4(v.x, v.y, v.z, v.w);
+    }
+}
+
+// true if p is page-locked host memory the device can DMA from / to directly
+bool batch_host_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
 }  // namespace
 
 // The dynamic shared-memory limit of k_batch_frame is a per-device property of the FUNCTION,
@@ -655,6 +689,12 @@ int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out) {
     k_batch_pack<<<(unsigned)std::min<size_t>((nb + 255) / 256, 148 * 8), 256, 0, b->stream>>>(
         b->ctx.base.pose, b->ctx.base.vel, b->d_state, nb);
     BCU(cudaGetLastError());
+    if (batch_host_pinned(out)) {  // page-locked destination (sfp_alloc_host_states): one DMA
+        BCU(cudaMemcpyAsync(out, b->d_state, sizeof(SfpBodyState) * nb, cudaMemcpyDeviceToHost,
+                            b->stream));
+        BCU(cudaStreamSynchronize(b->stream));
+        return SFP_OK;
+    }
     const size_t chunk = b->pin_states;
     for (size_t o = 0; o < nb; o += chunk) {
         size_t m = std::min(chunk, nb - o);
@@ -664,6 +704,34 @@ int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out) {
         std::memcpy(out + o, b->pin_state, sizeof(SfpBodyState) * m);
     }
     return SFP_OK;
+}
+
+int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBodyState* out, float dt,
+                            uint32_t substeps) {
+    if (!b || !in || !out || !b->uploaded) return SFP_E_INVALID;
+    if (!(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    BCU(cudaSetDevice(b->device));
+    const size_t nb = (size_t)b->n_worlds * b->bpw;
+    if (batch_host_pinned(in)) {
+        BCU(cudaMemcpyAsync(b->d_state, in, sizeof(SfpBodyState) * nb, cudaMemcpyHostToDevice,
+                            b->stream));
+    } else {
+        const size_t chunk = b->pin_states;
+        for (size_t o = 0; o < nb; o += chunk) {
+            size_t m = std::min(chunk, nb - o);
+            BCU(cudaStreamSynchronize(b->stream));  // the staging buffer is reused
+            std::memcpy(b->pin_state, in + o, sizeof(SfpBodyState) * m);
+            BCU(cudaMemcpyAsync(b->d_state + o, b->pin_state, sizeof(SfpBodyState) * m,
+                                cudaMemcpyHostToDevice, b->stream));
+        }
+    }
+    k_batch_unpack<<<(unsigned)std::min<size_t>((nb + 255) / 256, 148 * 8), 256, 0, b->stream>>>(
+        b->d_state, b->ctx.base.minv, b->ctx.base.pose, b->ctx.base.vel, nb);
+    BCU(cudaGetLastError());
+    int32_t rc = sfp_batch_step(b, dt, substeps);
+    if (rc != SFP_OK) return rc;
+    return sfp_batch_download(b, out);
 }
 
 int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out) {

@@ -117,3 +117,42 @@ def test_batch_rejects_bad_arguments(gpu_api):
     b = sf.Batch(gpu_api, 2, 16)
     with pytest.raises(sf.SfpError):
         b.step()  # nothing uploaded
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_batch_step_host_matches_oracle(gpu_api, ref_api, pinned):
+    """sfp_batch_step_host: states in from the host every frame (edited by the "game" in between),
+    one frame, states out — against the oracle's sfp_ref_step_host per world, bit for bit"""
+    nw, bpw, frames = 5, 128, 30
+    bodies = scenes.worlds(nw, bpw)
+    batch = sf.Batch(gpu_api, nw, bpw)
+    batch.upload(bodies)
+    refs = []
+    for w in range(nw):
+        r = sf.World(ref_api)
+        r.upload_bodies(bodies[w])
+        refs.append(r)
+    n = nw * bpw
+    if pinned:
+        bufs = [gpu_api.alloc_host_states(n), gpu_api.alloc_host_states(n)]
+    else:
+        bufs = [np.zeros(n, dtype=sf._ffi.BODY_STATE_DTYPE) for _ in range(2)]
+    bufs[0][:] = batch.download().reshape(-1)
+    ref_states = [r.download_bodies() for r in refs]
+    for f in range(frames):
+        src, dst = bufs[f & 1], bufs[(f + 1) & 1]
+        if f == 10:
+            # the game kicks one dynamic body of every world (body 5 is dynamic: 0..2 are the container)
+            for w in range(nw):
+                src[w * bpw + 5]["vx"] = 2.0
+                src[w * bpw + 5]["vy"] = 3.0
+                ref_states[w][5]["vx"] = 2.0
+                ref_states[w][5]["vy"] = 3.0
+        batch.step_host(src, out=dst)
+        for w in range(nw):
+            ref_states[w] = refs[w].step_host(ref_states[w])
+    out = bufs[frames & 1].reshape(nw, bpw)
+    for w in range(nw):
+        same(out[w], ref_states[w])
+        assert np.array_equal(out[w]["angle"].view(np.uint32), ref_states[w]["angle"].view(np.uint32))
+    assert batch.stats()["n_contacts"].sum() > 0
