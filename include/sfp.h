@@ -294,8 +294,7 @@ SFP_API int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out);
 /* Replaces: the same round trip as sfp_step_host for every world of the batch (reference
  * file:line unavailable): `in` / `out` hold n_worlds * bodies_per_world states, world-major;
  * upload + unpack on the device + one frame + pack + download.  Page-locked arrays from
- * sfp_alloc_host_states are copied by DMA without staging.  A state with a zero rotor takes its
- * rotation from `angle` through the DEVICE's sincosf. */
+ * sfp_alloc_host_states are copied by DMA without staging. */
 SFP_API int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBodyState* out,
                                     float dt, uint32_t substeps);
 /* per-world stats: out has room for n_worlds entries (n_pairs, n_contacts, n_colours ...) */

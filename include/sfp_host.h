@@ -207,20 +207,10 @@ inline SfpBodyState state_from_records(f4 pose, f4 vel) {
     return s;
 }
 
-/* a state whose rotor is (0, 0) carries its rotation in `angle` only: give it a rotor */
-inline SfpBodyState state_with_rotor(const SfpBodyState& in) {
-    SfpBodyState s = in;
-    if (!(s.c * s.c + s.s * s.s > 0.0f)) {
-        s.c = cosf(s.angle);
-        s.s = sinf(s.angle);
-    }
-    return s;
-}
-
+/* (a state whose rotor is (0, 0) takes its rotation from `angle`: state_unpack, sfp_math.h) */
 inline void records_from_state(const SfpBodyState& in, f2 minv, f4* pose, f4* vel) {
-    SfpBodyState s = state_with_rotor(in);
     StateRec r;
-    std::memcpy(&r, &s, sizeof(r));
+    std::memcpy(&r, &in, sizeof(r));
     state_unpack(r, minv, pose, vel);
 }
 

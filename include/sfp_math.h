@@ -177,10 +177,53 @@ SFP_HD StateRec state_pack(f4 pose, f4 vel) {
     r.angle = atan2_det(pose.w, pose.z);
     return r;
 }
-/* requires (c, s) != (0, 0); the host substitutes cos / sin of `angle` for a zero rotor */
+/* sin and cos from + - * only (Cephes' sinf / cosf: octant reduction with a three-part pi/4,
+ * two polynomials; |error| < 2e-7 for |x| < 8192, larger arguments are first brought into that
+ * range and lose accuracy accordingly).  Same reason as atan_det: the library's and the
+ * device's functions differ in the last bits. */
+SFP_HD void sincos_det(float x, float* sn, float* cs) {
+    float ax = fabsf(x);
+    if (!(ax < 8192.0f)) {
+        if (!(ax - ax == 0.0f)) { /* not finite */
+            *sn = 0.0f;
+            *cs = 1.0f;
+            return;
+        }
+        ax = ax - 6.283185307179586f * floorf(ax * 0.15915494309189535f);
+    }
+    int j = (int)(ax * 1.27323954473516f); /* 4 / pi */
+    float y = (float)j;
+    if (j & 1) {
+        j += 1;
+        y += 1.0f;
+    }
+    j &= 7;
+    float r = ((ax - y * 0.78515625f) - y * 2.4187564849853515625e-4f) - y * 3.77489497744594108e-8f;
+    float z = r * r;
+    float ps = ((-1.9515295891e-4f * z + 8.3321608736e-3f) * z - 1.6666654611e-1f) * z * r + r;
+    float pc = ((2.443315711809948e-5f * z - 1.388731625493765e-3f) * z + 4.166664568298827e-2f) * z * z -
+               0.5f * z + 1.0f;
+    /* octant pairs 0: (s, c)  2: (c, -s)  4: (-s, -c)  6: (-c, s) */
+    float s0 = ps, c0 = pc;
+    if (j == 2) {
+        s0 = pc;
+        c0 = -ps;
+    } else if (j == 4) {
+        s0 = -ps;
+        c0 = -pc;
+    } else if (j == 6) {
+        s0 = -pc;
+        c0 = ps;
+    }
+    *sn = (x < 0.0f) ? -s0 : s0;
+    *cs = c0;
+}
+
+/* a state whose rotor is (0, 0) carries its rotation in `angle` only */
 SFP_HD void state_unpack(StateRec r, f2 minv, f4* pose, f4* vel) {
     pose->x = r.x;
     pose->y = r.y;
+    if (!(r.c * r.c + r.s * r.s > 0.0f)) sincos_det(r.angle, &r.s, &r.c);
     float inv = 1.0f / sqrtf(r.c * r.c + r.s * r.s);
     pose->z = r.c * inv;
     pose->w = r.s * inv;

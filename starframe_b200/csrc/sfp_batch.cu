@@ -396,9 +396,8 @@ __global__ void __launch_bounds__(256) k_batch_pack(const float4* __restrict__ p
     }
 }
 
-// scene-graph states -> pose / vel (statics keep zero velocity).  A state whose rotor is zero
-// carries its rotation in `angle` only; the device's sincosf is used for it (the single-world
-// entry converts those on the host with libm — the last bits may differ).
+// scene-graph states -> pose / vel (statics keep zero velocity; a zero rotor is replaced by
+// sincos_det(angle) inside state_unpack)
 __global__ void __launch_bounds__(256) k_batch_unpack(const sfp::StateRec* __restrict__ in,
                                                       const float2* __restrict__ minv,
                                                       float4* __restrict__ pose,
@@ -409,7 +408,6 @@ __global__ void __launch_bounds__(256) k_batch_unpack(const sfp::StateRec* __res
         float4 a = q[0], b = q[1];
         sfp::StateRec r;
         r.x = a.x, r.y = a.y, r.c = a.z, r.s = a.w, r.vx = b.x, r.vy = b.y, r.omega = b.z, r.angle = b.w;
-        if (!(r.c * r.c + r.s * r.s > 0.0f)) sincosf(r.angle, &r.s, &r.c);
         float2 m = minv[i];
         f2 mi;
         mi.x = m.x, mi.y = m.y;

@@ -1219,11 +1219,11 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
     CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
-    bool zero_rotor = false;  // rare: a state that carries its rotation in `angle` only
-    for (uint32_t i = 0; i < n; ++i) zero_rotor |= !(in[i].c * in[i].c + in[i].s * in[i].s > 0.0f);
+    // (a state that carries its rotation in `angle` only is given its rotor by the unpack
+    // kernel: no pass over the states on the host)
     const SfpBodyState* src = in;
-    if (zero_rotor || !host_pinned(in)) {
-        for (uint32_t i = 0; i < n; ++i) w->pin_state[i] = sfp::state_with_rotor(in[i]);
+    if (!host_pinned(in)) {
+        std::memcpy(w->pin_state, in, sizeof(SfpBodyState) * n);
         src = w->pin_state;
     }
     CU(cudaMemcpyAsync(w->d_state, src, sizeof(SfpBodyState) * n, cudaMemcpyHostToDevice,
@@ -1441,7 +1441,7 @@ int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* 
     if (m == 0) return SFP_OK;
     CU(cudaSetDevice(w->device));
     CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
-    for (uint32_t k = 0; k < m; ++k) w->pin_state[k] = sfp::state_with_rotor(states[k]);
+    std::memcpy(w->pin_state, states, sizeof(SfpBodyState) * m);
     CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * m, cudaMemcpyHostToDevice,
                        w->stream));
     CU(cudaMemcpyAsync(w->d_idx, idx, sizeof(uint32_t) * m, cudaMemcpyHostToDevice, w->stream));

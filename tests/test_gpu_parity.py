@@ -185,6 +185,40 @@ def test_step_host_with_pinned_arrays(gpu_api, ref_api):
         assert np.array_equal(buf[0][f].view(np.uint32), sr[f].view(np.uint32)), f
 
 
+@pytest.mark.parametrize("pinned", [False, True])
+def test_states_with_zero_rotor_take_their_angle(gpu_api, ref_api, pinned):
+    """a scene graph that keeps angles only hands over states with c = s = 0: both sides build
+    the rotor from `angle` with the shared sincos_det (no libm / CUDA sincosf involved)"""
+    b, j = scenes.mixed_pile(800)
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    n = len(b)
+    sg = gpu_api.alloc_host_states(n) if pinned else np.zeros(n, dtype=sf._ffi.BODY_STATE_DTYPE)
+    out = gpu_api.alloc_host_states(n) if pinned else np.zeros(n, dtype=sf._ffi.BODY_STATE_DTYPE)
+    sg[:] = g.download_bodies()
+    sr = r.download_bodies()
+    for k in range(4):
+        for s_ in (sg, sr):
+            s_["angle"][::3] += np.float32(0.25 * (k + 1))  # the game turns every third body ...
+            s_["c"][::3] = 0.0                               # ... and only knows angles
+            s_["s"][::3] = 0.0
+        g.step_host(sg, out=out)
+        sr = r.step_host(sr)
+        sg[:] = out
+    for f in FIELDS + ("angle",):
+        assert np.array_equal(sg[f].view(np.uint32), sr[f].view(np.uint32)), f
+    # and update_bodies takes the same route
+    idx = np.arange(0, n, 7, dtype=np.uint32)
+    st = sr[idx].copy()
+    st["c"], st["s"] = 0.0, 0.0
+    st["angle"] = np.linspace(-9.0, 9.0, len(idx)).astype(np.float32)
+    g.update_bodies(idx, st)
+    r.update_bodies(idx, st)
+    assert_same_state(g, r)
+    got = r.download_bodies()[idx]
+    assert np.max(np.abs(got["c"] - np.cos(st["angle"].astype(np.float64)))) < 3e-7
+    assert np.max(np.abs(got["s"] - np.sin(st["angle"].astype(np.float64)))) < 3e-7
+
+
 def test_empty_and_tiny_worlds(gpu_api, ref_api):
     for n in (0, 1, 2):
         b, j = scenes.random_soup(max(n, 1), 5)
