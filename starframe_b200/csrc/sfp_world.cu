@@ -351,6 +351,22 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         }
     };
 
+    // after the last big colour, block 0 fetches its first SMALL colour's record instead, so
+    // that the small-colour loop starts from registers as well
+    const int first_small = next_bit(small, -1);
+    auto prefetch_pos_after = [&](int col) {
+        const int nb = next_bit(big, col);
+        if (nb < 64) prefetch_pos(nb, stid);
+        else if (blockIdx.x == 0) prefetch_pos(first_small, threadIdx.x);
+        else have = false;
+    };
+    auto prefetch_vel_after = [&](int col) {
+        const int nb = next_bit(big, col);
+        if (nb < 64) prefetch_vel(nb, stid);
+        else if (blockIdx.x == 0) prefetch_vel(first_small, threadIdx.x);
+        else have = false;
+    };
+
     // per-stage wall time (ns, %globaltimer) seen by thread 0 — the phases are grid-wide, so
     // one observer is representative
     unsigned long long t_prev = 0, acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -407,7 +423,7 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
                 t3 = clock64();
             }
             stage_solve_pos(c, (uint32_t)col, inv_h2, stid, nth, have, s_joff, s_poff);
-            prefetch_pos(next_bit(big, col), stid);
+            prefetch_pos_after(col);
             long long t4 = clock64();
             if (__any_sync(0xffffffffu, busy) && (threadIdx.x & 31u) == 0u) {
                 // lane 0's clock reads bracket the whole warp's (divergent) execution
@@ -438,15 +454,16 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_pos_pair(c, rec_k, rec);
             stage_solve_pos(c, (uint32_t)col, inv_h2, stid, nth, have, s_joff, s_poff);
-            prefetch_pos(next_bit(big, col), stid);
+            prefetch_pos_after(col);
             grid.sync();
         }
 #endif
         lap(6);
         if (small || serial) {
             if (blockIdx.x == 0) {
-                // same record prefetch as above, one block wide
-                have = false;
+                // same record prefetch as above, one block wide (the first record came with
+                // the last big colour, if there was one)
+                if (!big) have = false;
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     if (have) solve_pos_pair(c, rec_k, rec);
                     stage_solve_pos(c, (uint32_t)col, inv_h2, threadIdx.x, blockDim.x, have, s_joff,
@@ -466,13 +483,13 @@ __global__ void __launch_bounds__(TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, fl
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
             stage_solve_vel(c, (uint32_t)col, h, rest_threshold, stid, nth, have, s_poff);
-            prefetch_vel(next_bit(big, col), stid);
+            prefetch_vel_after(col);
             grid.sync();
         }
         lap(8);
         if (small || serial) {
             if (blockIdx.x == 0) {
-                have = false;
+                if (!big) have = false;
                 for (int col = next_bit(small, -1); col < 64; col = next_bit(small, col)) {
                     if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
                     stage_solve_vel(c, (uint32_t)col, h, rest_threshold, threadIdx.x, blockDim.x,
