@@ -288,6 +288,12 @@ SFP_API int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds,
 SFP_API int32_t sfp_batch_destroy(SfpBatch* b);
 /* bodies: n_worlds * bodies_per_world descs, world-major */
 SFP_API int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies);
+/* Replaces: registration of distance / rope constraints, per world (reference file:line
+ * unavailable).  joints: n_worlds * joints_per_world descs, world-major, body indices local to
+ * the world; counts (or NULL = every slot used) says how many of a world's slots are in use.
+ * Replaces all joints of the batch; joints_per_world = 0 removes them. */
+SFP_API int32_t sfp_batch_set_joints(SfpBatch* b, const SfpJointDesc* joints,
+                                     uint32_t joints_per_world, const uint32_t* counts);
 SFP_API int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps);
 SFP_API int32_t sfp_batch_sync(SfpBatch* b);
 SFP_API int32_t sfp_batch_download(SfpBatch* b, SfpBodyState* out);

@@ -48,6 +48,8 @@ struct BatchCtx {
     Counters* counters;    // [n_worlds]
     uint32_t* scratch;     // [n_worlds][bpw] per-body pair counts / offsets
     uint32_t tab_slots;    // colour-table slots per world (power of two)
+    uint32_t joint_cap;    // joint slots per world (0: the batch has no joints)
+    const uint32_t* n_joints;  // [n_worlds] joints in use per world, or null
 };
 
 __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
@@ -78,6 +80,17 @@ __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
     c.cnt = b.counters + w;
     c.n = b.bpw;
     c.nj = 0;
+    if (b.joint_cap) {
+        const size_t jo = (size_t)w * b.joint_cap;
+        c.jbod_in += jo;
+        c.janc_in += jo;
+        c.jpar_in += jo;
+        c.jbod += jo;
+        c.janc += jo;
+        c.jpar += jo;
+        c.jcol += jo;
+        c.nj = b.n_joints[w];
+    }
     c.cap_pairs = b.pair_cap;
     return c;
 }
@@ -172,9 +185,26 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
         ex += v[j];
     }
     __syncthreads();
+    // joints: a world holds at most a few hundred, so each one counts its predecessors — the
+    // joints of a lower colour, and those of its own colour that come earlier in upload order
+    // (stable: the serial group, whose members may share bodies, keeps upload order)
+    const uint32_t nj = c.nj;
+    for (uint32_t k = tid; k < nj; k += nth) {
+        const uint32_t col = c.jcol[k];
+        uint32_t pos = 0;
+        for (uint32_t i = 0; i < nj; ++i) {
+            const uint32_t ci = c.jcol[i];
+            pos += (ci < col || (ci == col && i < k)) ? 1u : 0u;
+        }
+        c.jbod[pos] = c.jbod_in[k];
+        c.janc[pos] = c.janc_in[k];
+        c.jpar[pos] = c.jpar_in[k];
+    }
     for (uint32_t col = tid; col <= SFP_MAX_COLOURS; col += nth) {
         c.cnt->pair_col_off[col] = (col < SFP_MAX_COLOURS) ? bins[col << SFP_TYPE_BITS] : P;
-        c.cnt->joint_col_off[col] = 0;
+        uint32_t below = 0;
+        for (uint32_t i = 0; i < nj; ++i) below += (c.jcol[i] < col) ? 1u : 0u;
+        c.cnt->joint_col_off[col] = below;
     }
     __syncthreads();
     for (uint32_t k = tid; k < P; k += nth) {
@@ -297,6 +327,8 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
     auto issue = [&](uint32_t oi, bool with_lam) {
         if (oi >= nord) return false;
         const uint32_t col = s_order[oi];
+        // a colour's joints come before its pairs: item `tid` is then not pair `tid`
+        if (!with_lam && c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return false;
         const uint32_t k = c.cnt->pair_col_off[col] + tid;
         if (k >= c.cnt->pair_col_off[col + 1]) return false;
         __pipeline_memcpy_async(&s_rec[0][tid], &c.ca[k], 16);
@@ -472,6 +504,9 @@ struct SfpBatch {
     size_t pin_states = 0;
     uint32_t n_dynamic_total = 0;
     std::vector<uint32_t> n_dynamic;
+    uint32_t joint_cap = 0;              // joint slots per world
+    std::vector<uint32_t> n_joints;      // per world
+    std::vector<void*> joint_allocs;
     std::string err;
     int32_t sticky = SFP_OK;
 };
@@ -600,6 +635,7 @@ int32_t sfp_batch_destroy(SfpBatch* b) {
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
     for (void* p : b->allocs) cudaFree(p);
+    for (void* p : b->joint_allocs) cudaFree(p);
     if (b->pin_state) cudaFreeHost(b->pin_state);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
@@ -639,6 +675,79 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
     b->colour_age = 0;
     b->uploaded = true;
     b->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_set_joints(SfpBatch* b, const SfpJointDesc* joints, uint32_t joints_per_world,
+                             const uint32_t* counts) {
+    if (!b || (joints_per_world && !joints) || joints_per_world > 65536u) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    const uint32_t J = joints_per_world;
+    std::vector<uint32_t> nj(b->n_worlds, J);
+    for (uint32_t w = 0; w < b->n_worlds && J; ++w) {
+        if (counts) nj[w] = counts[w];
+        if (nj[w] > J) return SFP_E_INVALID;
+        for (uint32_t k = 0; k < nj[w]; ++k)
+            if (!sfp::joint_valid(joints[(size_t)w * J + k], b->bpw)) {
+                b->err = "invalid joint desc, world " + std::to_string(w) + " joint " + std::to_string(k);
+                return SFP_E_INVALID;
+            }
+    }
+    BCU(cudaSetDevice(b->device));
+    BCU(cudaStreamSynchronize(b->stream));
+    for (void* p : b->joint_allocs) cudaFree(p);
+    b->joint_allocs.clear();
+    Ctx& c = b->ctx.base;
+    b->joint_cap = J;
+    b->ctx.joint_cap = J;
+    b->ctx.n_joints = nullptr;
+    b->n_joints = nj;
+    b->colour_age = 0;
+    if (J == 0) {
+        // as after creation: unused pointers keep a valid target
+        c.jbod_in = reinterpret_cast<const uint2*>(c.pairs_raw);
+        c.jcol = c.pcol;
+        std::fill(b->n_joints.begin(), b->n_joints.end(), 0u);
+        return SFP_OK;
+    }
+    const size_t tot = (size_t)b->n_worlds * J;
+    std::vector<uint2> jb(tot, make_uint2(0u, 0u));
+    std::vector<float4> ja(tot, make_float4(0, 0, 0, 0)), jp(tot, make_float4(0, 0, 0, 0));
+    for (uint32_t w = 0; w < b->n_worlds; ++w)
+        for (uint32_t k = 0; k < nj[w]; ++k) {
+            const SfpJointDesc& j = joints[(size_t)w * J + k];
+            const size_t i = (size_t)w * J + k;
+            jb[i] = make_uint2(j.body_a, j.body_b);
+            ja[i] = make_float4(j.ax, j.ay, j.bx, j.by);
+            jp[i] = make_float4(j.rest, j.compliance, sfp::u2f(j.kind), 0.0f);
+        }
+    auto jalloc = [&](void** out, size_t bytes) {
+        if (cudaMalloc(out, bytes) != cudaSuccess) return false;
+        b->joint_allocs.push_back(*out);
+        return cudaMemset(*out, 0, bytes) == cudaSuccess;
+    };
+    void *d_jb_in = nullptr, *d_ja_in = nullptr, *d_jp_in = nullptr, *d_jb = nullptr, *d_ja = nullptr,
+         *d_jp = nullptr, *d_jcol = nullptr, *d_nj = nullptr;
+    if (!jalloc(&d_jb_in, sizeof(uint2) * tot) || !jalloc(&d_ja_in, sizeof(float4) * tot) ||
+        !jalloc(&d_jp_in, sizeof(float4) * tot) || !jalloc(&d_jb, sizeof(uint2) * tot) ||
+        !jalloc(&d_ja, sizeof(float4) * tot) || !jalloc(&d_jp, sizeof(float4) * tot) ||
+        !jalloc(&d_jcol, sizeof(uint32_t) * tot) || !jalloc(&d_nj, sizeof(uint32_t) * b->n_worlds)) {
+        b->err = "cudaMalloc (joints)";
+        b->sticky = SFP_E_CUDA;
+        return SFP_E_CUDA;
+    }
+    BCU(cudaMemcpy(d_jb_in, jb.data(), sizeof(uint2) * tot, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(d_ja_in, ja.data(), sizeof(float4) * tot, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(d_jp_in, jp.data(), sizeof(float4) * tot, cudaMemcpyHostToDevice));
+    BCU(cudaMemcpy(d_nj, nj.data(), sizeof(uint32_t) * b->n_worlds, cudaMemcpyHostToDevice));
+    c.jbod_in = static_cast<const uint2*>(d_jb_in);
+    c.janc_in = static_cast<const float4*>(d_ja_in);
+    c.jpar_in = static_cast<const float4*>(d_jp_in);
+    c.jbod = static_cast<uint2*>(d_jb);
+    c.janc = static_cast<float4*>(d_ja);
+    c.jpar = static_cast<float4*>(d_jp);
+    c.jcol = static_cast<uint32_t*>(d_jcol);
+    b->ctx.n_joints = static_cast<const uint32_t*>(d_nj);
     return SFP_OK;
 }
 
@@ -748,6 +857,7 @@ int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out) {
         s.body_substeps = b->body_substeps / b->n_worlds;
         s.n_bodies = b->bpw;
         s.n_dynamic = b->n_dynamic.empty() ? 0u : b->n_dynamic[w];
+        s.n_joints = b->n_joints.empty() ? 0u : b->n_joints[w];
         s.n_pairs = b->stepped ? k[w].n_pairs : 0u;
         s.n_contacts = k[w].n_contacts;
         s.n_manifolds = k[w].n_manifolds;

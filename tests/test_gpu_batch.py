@@ -156,3 +156,71 @@ def test_batch_step_host_matches_oracle(gpu_api, ref_api, pinned):
         same(out[w], ref_states[w])
         assert np.array_equal(out[w]["angle"].view(np.uint32), ref_states[w]["angle"].view(np.uint32))
     assert batch.stats()["n_contacts"].sum() > 0
+
+
+def rope_worlds(nw):
+    """nw small rope worlds of identical size but different content; world w keeps only its first
+    (jmax - w) joints, so the per-world counts differ"""
+    worlds, joints = [], []
+    for w in range(nw):
+        b, j = scenes.ropes(n_ropes=4, links=12, n_free=40 + 0 * w, seed=scenes.BASE_SEED + 40 + w, rope_rows=2)
+        worlds.append(b)
+        joints.append(j)
+    n = len(worlds[0])
+    assert all(len(b) == n for b in worlds)
+    jmax = max(len(j) for j in joints)
+    counts = np.array([len(j) - w for w, j in enumerate(joints)], dtype=np.uint32)
+    packed = np.zeros((nw, jmax), dtype=sf._ffi.JOINT_DESC_DTYPE)
+    for w, j in enumerate(joints):
+        packed[w, :counts[w]] = j[:counts[w]]
+    return np.stack(worlds), packed, counts
+
+
+def test_batch_joints_match_oracle(gpu_api, ref_api):
+    """distance / rope joints inside batched worlds (sfp_batch_set_joints), per-world counts"""
+    nw, frames = 4, 60
+    bodies, joints, counts = rope_worlds(nw)
+    batch = sf.Batch(gpu_api, nw, bodies.shape[1])
+    batch.upload(bodies)
+    batch.set_joints(joints, counts)
+    refs = []
+    for w in range(nw):
+        r = sf.World(ref_api)
+        r.upload_bodies(bodies[w])
+        r.set_joints(joints[w, :counts[w]])
+        refs.append(r)
+    for f in range(frames):
+        batch.step()
+        for r in refs:
+            r.step()
+    out, st = batch.download(), batch.stats()
+    for w in range(nw):
+        same(out[w], refs[w].download_bodies())
+        rs = refs[w].stats()
+        for k in ("n_pairs", "n_contacts", "n_colours", "colour_rounds", "n_joints"):
+            assert st[k][w] == rs[k], (w, k, st[k][w], rs[k])
+    # ropes hold: no link has fallen to the floor region... (stretch is bounded)
+    assert st["n_joints"].sum() == counts.sum()
+    # removing the joints again is the joint-free batch
+    batch.set_joints(joints[:, :0])
+    for r in refs:
+        r.set_joints(joints[0, :0])
+    for f in range(10):
+        batch.step()
+        for r in refs:
+            r.step()
+    out = batch.download()
+    for w in range(nw):
+        same(out[w], refs[w].download_bodies())
+
+
+def test_batch_set_joints_rejects_bad_arguments(gpu_api):
+    bodies, joints, counts = rope_worlds(2)
+    batch = sf.Batch(gpu_api, 2, bodies.shape[1])
+    batch.upload(bodies)
+    bad = joints.copy()
+    bad[1, 0]["body_b"] = bodies.shape[1]  # out of the world
+    with pytest.raises(sf.SfpError):
+        batch.set_joints(bad, counts)
+    with pytest.raises(sf.SfpError):
+        batch.set_joints(joints, counts + joints.shape[1])  # more than the slots
