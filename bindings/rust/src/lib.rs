@@ -228,6 +228,7 @@ extern "C" {
                             out: *mut *mut SfpBatch) -> i32;
     pub fn sfp_batch_destroy(b: *mut SfpBatch) -> i32;
     pub fn sfp_batch_upload(b: *mut SfpBatch, bodies: *const SfpBodyDesc) -> i32;
+    pub fn sfp_batch_set_polygons(b: *mut SfpBatch, polys: *const SfpPolygon, n: u32) -> i32;
     pub fn sfp_batch_set_joints(b: *mut SfpBatch, joints: *const SfpJointDesc, joints_per_world: u32,
                                 counts: *const u32) -> i32;
     pub fn sfp_batch_step(b: *mut SfpBatch, dt: f32, substeps: u32) -> i32;

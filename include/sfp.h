@@ -288,6 +288,9 @@ SFP_API int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds,
 SFP_API int32_t sfp_batch_destroy(SfpBatch* b);
 /* bodies: n_worlds * bodies_per_world descs, world-major */
 SFP_API int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies);
+/* The polygon table shared by all worlds of the batch (see sfp_set_polygons); call it BEFORE
+ * sfp_batch_upload of bodies that use SFP_SHAPE_POLYGON. */
+SFP_API int32_t sfp_batch_set_polygons(SfpBatch* b, const SfpPolygon* polys, uint32_t n);
 /* Replaces: registration of distance / rope constraints, per world (reference file:line
  * unavailable).  joints: n_worlds * joints_per_world descs, world-major, body indices local to
  * the world; counts (or NULL = every slot used) says how many of a world's slots are in use.

@@ -110,7 +110,7 @@ PRODUCT_SYMBOLS = [
     "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host",
     "alloc_host_states", "free_host_states",
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
-    "batch_download", "batch_step_host", "batch_set_joints", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
+    "batch_download", "batch_step_host", "batch_set_joints", "batch_set_polygons", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
@@ -192,6 +192,7 @@ class Api:
             "batch_download": [vp, vp],
             "batch_step_host": [vp, vp, vp, f32, u32],
             "batch_set_joints": [vp, vp, u32, vp],
+            "batch_set_polygons": [vp, vp, u32],
             "batch_stats": [vp, vp],
             "batch_last_step_ms": [vp, C.POINTER(f32)],
             "step_small_noalloc": [vp, vp, u32, f32, u32, u32, vp, C.c_char_p, u32],
@@ -443,6 +444,11 @@ class Batch:
         b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE).reshape(-1)
         assert b.shape[0] == self.n_worlds * self.bpw
         self._check(self.api.fn("batch_upload")(self.h, _ptr(b)), "batch_upload")
+
+    def set_polygons(self, polys: np.ndarray):
+        p = np.ascontiguousarray(polys, dtype=POLYGON_DTYPE)
+        self._check(self.api.fn("batch_set_polygons")(self.h, _ptr(p) if p.size else None, p.shape[0]),
+                    "batch_set_polygons")
 
     def set_joints(self, joints: np.ndarray, counts: np.ndarray | None = None):
         """joints: (n_worlds, joints_per_world) descs with world-local body indices"""

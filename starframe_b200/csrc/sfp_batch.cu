@@ -222,14 +222,18 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
 #ifndef SFP_BCTAS
 #define SFP_BCTAS 3
 #endif
-template <bool SMEM>
-__global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, float dt, uint32_t substeps,
-                                                         float rest_threshold) {
+// FULL: the variant that can collide general polygons and solve joints (more registers and
+// code: two CTAs per SM); the host launches it only for batches that hold a polygon body or
+// a joint, so that plain worlds keep the lean kernel
+template <bool SMEM, bool FULL = false>
+__global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
+    k_batch_frame(BatchCtx b, float dt, uint32_t substeps, float rest_threshold) {
     extern __shared__ float4 dyn[];
     __shared__ uint32_t smem9[9];
     const uint32_t w = blockIdx.x;
     if (w >= b.n_worlds) return;
     Ctx c = world_view(b, w);
+    if (!FULL) c.nj = 0;  // compile-time: the lean variant carries no joint code
     const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
     uint32_t* cnt_off = b.scratch + (size_t)w * b.bpw;
     float4 *g_pose = c.pose, *g_vel = c.vel;
@@ -328,7 +332,9 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         if (oi >= nord) return false;
         const uint32_t col = s_order[oi];
         // a colour's joints come before its pairs: item `tid` is then not pair `tid`
-        if (!with_lam && c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col]) return false;
+        if (!with_lam && c.nj != 0u &&
+            c.cnt->joint_col_off[col + 1] != c.cnt->joint_col_off[col])
+            return false;
         const uint32_t k = c.cnt->pair_col_off[col] + tid;
         if (k >= c.cnt->pair_col_off[col + 1]) return false;
         __pipeline_memcpy_async(&s_rec[0][tid], &c.ca[k], 16);
@@ -354,7 +360,7 @@ __global__ void __launch_bounds__(BTPB, SFP_BCTAS) k_batch_frame(BatchCtx b, flo
         stage_integrate(c, h, tid, nth);
         __syncthreads();
         LAP(4);
-        stage_narrowphase<false>(c, tid, nth);  // batched worlds hold no general polygons
+        stage_narrowphase<FULL>(c, tid, nth);
         __syncthreads();
         LAP(5);
         {
@@ -469,8 +475,11 @@ static cudaError_t raise_batch_smem_limit(int device, size_t bytes) {
     static size_t current[64] = {0};
     if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
     if (bytes <= current[device]) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(k_batch_frame<true>,
+    cudaError_t e = cudaFuncSetAttribute(k_batch_frame<true, false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_batch_frame<true, true>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
     if (e == cudaSuccess) current[device] = bytes;
     return e;
 }
@@ -504,6 +513,9 @@ struct SfpBatch {
     size_t pin_states = 0;
     uint32_t n_dynamic_total = 0;
     std::vector<uint32_t> n_dynamic;
+    sfp::PolyTable polys;                // general-polygon table shared by all worlds
+    float4* d_polytab = nullptr;
+    bool has_polygons = false;
     uint32_t joint_cap = 0;              // joint slots per world
     std::vector<uint32_t> n_joints;      // per world
     std::vector<void*> joint_allocs;
@@ -636,6 +648,7 @@ int32_t sfp_batch_destroy(SfpBatch* b) {
     if (b->stream) cudaStreamSynchronize(b->stream);
     for (void* p : b->allocs) cudaFree(p);
     for (void* p : b->joint_allocs) cudaFree(p);
+    if (b->d_polytab) cudaFree(b->d_polytab);
     if (b->pin_state) cudaFreeHost(b->pin_state);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
@@ -648,7 +661,7 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
     if (!b || !bodies) return SFP_E_INVALID;
     const size_t nb = (size_t)b->n_worlds * b->bpw;
     for (size_t i = 0; i < nb; ++i)
-        if (!sfp::desc_valid(bodies[i])) {
+        if (!sfp::desc_valid(bodies[i], &b->polys)) {
             b->err = "invalid body desc at index " + std::to_string(i);
             return SFP_E_INVALID;
         }
@@ -656,8 +669,10 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
     std::vector<sfp::f4> pose(nb), vel(nb), shape(nb), mat(nb);
     b->h_minv.resize(nb);
     b->n_dynamic.assign(b->n_worlds, 0);
+    b->has_polygons = false;
     for (size_t i = 0; i < nb; ++i) {
-        sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &b->h_minv[i], &shape[i], &mat[i]);
+        sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &b->h_minv[i], &shape[i], &mat[i], &b->polys);
+        b->has_polygons |= (bodies[i].shape & 0xffu) == SFP_SHAPE_POLYGON;
         if (b->h_minv[i].x > 0.0f || b->h_minv[i].y > 0.0f) b->n_dynamic[i / b->bpw] += 1;
     }
     Ctx& c = b->ctx.base;
@@ -675,6 +690,30 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
     b->colour_age = 0;
     b->uploaded = true;
     b->stepped = false;
+    return SFP_OK;
+}
+
+int32_t sfp_batch_set_polygons(SfpBatch* b, const SfpPolygon* polys, uint32_t n) {
+    if (!b || (n && !polys)) return SFP_E_INVALID;
+    if (b->sticky != SFP_OK) return b->sticky;
+    sfp::PolyTable t;
+    long bad = sfp::build_poly_table(polys, n, &t);
+    if (bad >= 0) {
+        b->err = "invalid polygon at index " + std::to_string(bad) +
+                 " (3..8 vertices, counter-clockwise, strictly convex, centroid at the origin)";
+        return SFP_E_INVALID;
+    }
+    BCU(cudaSetDevice(b->device));
+    BCU(cudaStreamSynchronize(b->stream));
+    if (b->d_polytab) cudaFree(b->d_polytab);
+    b->d_polytab = nullptr;
+    if (n) {
+        BCU(cudaMalloc(&b->d_polytab, sizeof(float4) * 8u * (size_t)n));
+        BCU(cudaMemcpy(b->d_polytab, t.recs.data(), sizeof(float4) * 8u * (size_t)n,
+                       cudaMemcpyHostToDevice));
+    }
+    b->ctx.base.polytab = b->d_polytab;
+    b->polys = std::move(t);
     return SFP_OK;
 }
 
@@ -763,12 +802,19 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     b->ctx.base.tab_new = b->d_tab[b->colour_age & 1u];
     b->colour_age += 1;
     BCU(cudaEventRecord(b->ev0, b->stream));
-    if (b->smem_bytes)
-        k_batch_frame<true><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps,
-                                                                           2.0f * g * h);
-    else
-        k_batch_frame<false><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps,
-                                                                 2.0f * g * h);
+    const float rt = 2.0f * g * h;
+    const bool full = b->has_polygons || b->joint_cap != 0u;
+    if (b->smem_bytes) {
+        if (full)
+            k_batch_frame<true, true><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps, rt);
+        else
+            k_batch_frame<true, false><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps, rt);
+    } else {
+        if (full)
+            k_batch_frame<false, true><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, rt);
+        else
+            k_batch_frame<false, false><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, rt);
+    }
     BCU(cudaGetLastError());
     BCU(cudaEventRecord(b->ev1, b->stream));
     b->timed = true;

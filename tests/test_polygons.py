@@ -181,8 +181,41 @@ def test_polygon_world_multi_kernel_mode(gpu_api, ref_api):
 
 
 @pytest.mark.gpu
-def test_batch_rejects_polygons(gpu_api):
+def test_batch_rejects_polygons_without_a_table(gpu_api):
     b = sf.Batch(gpu_api, 1, 4)
     bodies = np.concatenate([poly_body(0, float(i), 1.0) for i in range(4)])
     with pytest.raises(sf.SfpError):
         b.upload(bodies)
+
+
+@pytest.mark.gpu
+def test_batched_polygon_worlds_match_oracle(gpu_api, ref_api):
+    """general polygons inside batched worlds (sfp_batch_set_polygons + the polygon kernel variant)"""
+    nw, n, frames = 4, 300, 90
+    worlds, table = [], None
+    for w in range(nw):
+        b, j, table = scenes.polygon_pile(n, seed=scenes.BASE_SEED + 60 + w, cols=20)
+        worlds.append(b)
+    bodies = np.stack(worlds)
+    batch = sf.Batch(gpu_api, nw, bodies.shape[1])
+    batch.set_polygons(table)
+    batch.upload(bodies)
+    refs = []
+    for w in range(nw):
+        r = sf.World(ref_api)
+        r.set_polygons(table)
+        r.upload_bodies(bodies[w])
+        refs.append(r)
+    for f in range(frames):
+        batch.step()
+        for r in refs:
+            r.step()
+    out, st = batch.download(), batch.stats()
+    for w in range(nw):
+        ro = refs[w].download_bodies()
+        for f in ("x", "y", "c", "s", "vx", "vy", "omega"):
+            assert np.array_equal(out[w][f].view(np.uint32), ro[f].view(np.uint32)), (w, f)
+        rs = refs[w].stats()
+        for k in ("n_pairs", "n_contacts", "n_manifolds", "n_colours"):
+            assert st[k][w] == rs[k], (w, k, st[k][w], rs[k])
+    assert st["n_contacts"].sum() > nw * n // 2
