@@ -38,6 +38,10 @@ struct Collider {
     static Collider new_rounded_rect(float w, float h, float r) {
         return {SFP_SHAPE_RECT, 0.5f * w - r, 0.5f * h - r, r};
     }
+    /* general convex polygon: `index` into the table given to Physics::set_polygons */
+    static Collider new_polygon(uint32_t index, float rounding = 0.0f) {
+        return {SFP_SHAPE_POLYGON | (index << 8), 0.0f, 0.0f, rounding};
+    }
     Collider with_material(Material m) const {
         Collider c = *this;
         c.material = m;
@@ -91,10 +95,42 @@ class Physics {
     uint32_t add_rope_constraint(uint32_t a, uint32_t b, float max_len, float compliance = 0.0f) {
         return add_joint(a, b, max_len, compliance, SFP_JOINT_ROPE);
     }
+    /* vertex table of the polygon colliders (CCW, strictly convex, centroid at the origin) */
+    void set_polygons(const std::vector<SfpPolygon>& polys) {
+        check(SFP_FN(set_polygons)(w_, polys.data(), (uint32_t)polys.size()), "set_polygons");
+        dirty_ = true;
+    }
     // the reference's per-frame step: frame dt, substep count
     void tick(float dt = 1.0f / 60.0f) {
         flush();
         check(SFP_FN(step)(w_, dt, substeps_), "step");
+    }
+    /* one call per frame for engines that keep body state on the host: states in, states out */
+    void tick_host(const std::vector<SfpBodyState>& in, std::vector<SfpBodyState>& out,
+                   float dt = 1.0f / 60.0f) {
+        flush();
+        out.resize(in.size());
+        check(SFP_FN(step_host)(w_, in.data(), out.data(), (uint32_t)in.size(), dt, substeps_), "step_host");
+    }
+    /* collisions of the last substep, for game code */
+    std::vector<SfpContactEvent> contact_events() {
+        uint32_t n = 0;
+        check(SFP_FN(get_contact_events)(w_, nullptr, 0, &n), "get_contact_events");
+        std::vector<SfpContactEvent> out(n);
+        if (n) check(SFP_FN(get_contact_events)(w_, out.data(), n, &n), "get_contact_events");
+        return out;
+    }
+    std::vector<SfpRayHit> ray_cast(const std::vector<SfpRay>& rays) {
+        flush();
+        std::vector<SfpRayHit> hits(rays.size());
+        if (!rays.empty())
+            check(SFP_FN(ray_cast)(w_, rays.data(), (uint32_t)rays.size(), hits.data()), "ray_cast");
+        return hits;
+    }
+    /* teleport / kinematic control of individual bodies between ticks */
+    void set_body_states(const std::vector<uint32_t>& idx, const std::vector<SfpBodyState>& states) {
+        flush();
+        check(SFP_FN(update_bodies)(w_, idx.data(), states.data(), (uint32_t)idx.size()), "update_bodies");
     }
     std::vector<SfpBodyState> body_states() {
         flush();

@@ -18,7 +18,27 @@ int main() {
     uint32_t hook = ph.add_body(Body::new_static(-3.f, 3.f), Collider::new_circle(0.05f));
     uint32_t bob = ph.add_body(Body::new_dynamic(-2.f, 3.f), Collider::new_circle(0.1f));
     ph.add_distance_constraint(hook, bob, 1.0f);
+    // a hexagon from the polygon table, resting on the ground
+    SfpPolygon hex{};
+    hex.count = 6;
+    for (int k = 0; k < 6; ++k) {
+        hex.x[k] = 0.3f * std::cos(6.283185307f * k / 6.f - 1.570796327f + 0.523598776f);
+        hex.y[k] = 0.3f * std::sin(6.283185307f * k / 6.f - 1.570796327f + 0.523598776f);
+    }
+    ph.set_polygons({hex});
+    uint32_t nut = ph.add_body(Body::new_dynamic(4.f, 0.5f), Collider::new_polygon(0));
     for (int f = 0; f < 180; ++f) ph.tick();
+    auto ev = ph.contact_events();
+    bool ball_on_ground = false;
+    for (auto& e : ev) ball_on_ground |= (e.a == 0u && e.b == ball && e.impulse > 0.f);
+    SfpRay ray{};
+    ray.ox = 4.f, ray.oy = 5.f, ray.dx = 0.f, ray.dy = -1.f, ray.max_t = 10.f, ray.mask = 0xffffffffu;
+    auto hit = ph.ray_cast({ray});
+    if (!ball_on_ground || hit[0].body != nut) return 2;
+    auto s0 = ph.body_states();
+    std::vector<SfpBodyState> s1;
+    ph.tick_host(s0, s1);
+    if (s1.size() != s0.size()) return 3;
     auto s = ph.body_states();
     float len = std::hypot(s[bob].x - s[hook].x, s[bob].y - s[hook].y);
     std::printf("%f %f %f\n", s[ball].y, s[box].y, len);
