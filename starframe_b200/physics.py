@@ -221,6 +221,36 @@ class Physics:
     def contacts(self) -> np.ndarray:
         return self._world.get_contacts()
 
+    def contact_events(self) -> np.ndarray:
+        """collisions of the last substep (body pair, normal, point, impulse) for game code"""
+        return self._world.get_contact_events()
+
+    def ray_cast(self, origins, directions, max_t: float = 1.0e9, mask: int = 0xFFFF) -> np.ndarray:
+        """closest hit per ray (body index 0xffffffff = none) against the current poses"""
+        self._flush()
+        from ._ffi import RAY_DTYPE
+        o = np.atleast_2d(np.asarray(origins, dtype=np.float32))
+        d = np.atleast_2d(np.asarray(directions, dtype=np.float32))
+        rays = np.zeros(len(o), dtype=RAY_DTYPE)
+        rays["ox"], rays["oy"], rays["dx"], rays["dy"] = o[:, 0], o[:, 1], d[:, 0], d[:, 1]
+        rays["max_t"], rays["mask"] = max_t, mask
+        return self._world.ray_cast(rays)
+
+    def query_aabb(self, lo, hi, mask: int = 0xFFFF) -> np.ndarray:
+        """indices of the bodies whose tight box overlaps [lo, hi]"""
+        self._flush()
+        return self._world.query_aabb(lo, hi, mask)
+
+    def set_body_states(self, idx, states: np.ndarray):
+        """teleport / kinematic control of individual bodies between ticks"""
+        self._flush()
+        self._world.update_bodies(np.asarray(idx, dtype=np.uint32), states)
+
+    def tick_host(self, states: np.ndarray, dt: float = 1.0 / 60.0, out: np.ndarray | None = None):
+        """states in from the host, one frame, states out (the engine's per-frame round trip)"""
+        self._flush()
+        return self._world.step_host(states, dt, self.substeps, out=out)
+
     def stats(self) -> dict:
         return self._world.stats()
 

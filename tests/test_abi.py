@@ -102,3 +102,27 @@ def test_host_mirror_builds_a_scene():
     b = Body.new_dynamic(1.0, 2.0, 0.3).with_velocity(1.0, 0.0, 0.5)
     assert (b.vx, b.omega, b.is_static) == (1.0, 0.5, False)
     assert Body.new_static().is_static
+
+
+def test_host_mirror_drives_the_oracle_end_to_end(ref_api):
+    """the same mirror bound to the oracle library: tick, events, queries, per-body updates and the
+    host-state round trip go through the calls the product library exports under the same names"""
+    import starframe_b200 as sf
+
+    ph = sf.Physics(api=ref_api)
+    ph.add_body(sf.Body.new_static(0.0, -0.5), sf.Collider.new_rect(10.0, 1.0))
+    ball = ph.add_body(sf.Body.new_dynamic(0.0, 0.5), sf.Collider.new_circle(0.5))
+    for _ in range(30):
+        ph.tick()
+    ev = ph.contact_events()
+    assert len(ev) == 1 and (ev[0]["a"], ev[0]["b"]) == (0, ball) and ev[0]["impulse"] > 0.0
+    hit = ph.ray_cast([(0.0, 5.0)], [(0.0, -1.0)], 10.0)
+    assert hit[0]["body"] == ball and hit[0]["t"] == pytest.approx(4.0, abs=1e-3)
+    assert list(ph.query_aabb((-1.0, 0.0), (1.0, 1.0))) == [0, ball]
+    st = ph.body_states()
+    moved = st[[ball]].copy()
+    moved["x"] = 3.0
+    ph.set_body_states([ball], moved)
+    assert ph.body_states()[ball]["x"] == np.float32(3.0)
+    out = ph.tick_host(ph.body_states())
+    assert out[ball]["x"] == pytest.approx(3.0, abs=1e-4) and out[ball]["y"] == pytest.approx(0.5, abs=1e-2)
