@@ -252,3 +252,39 @@ def test_determinism(gpu_api):
             g.step()
         outs.append(g.download_bodies().tobytes())
     assert outs[0] == outs[1]
+
+
+def test_worlds_driven_from_different_threads(gpu_api, ref_api):
+    """one world per thread at a time, different worlds from different threads.
+    Four threads step four worlds (cooperative launches, graphs and all) at the same time; every
+    world must still equal its oracle twin bit for bit."""
+    import threading
+
+    seeds = [21, 22, 23, 24]
+    worlds, results, errors = [], [None] * len(seeds), []
+    for sd in seeds:
+        b, j = scenes.random_soup(700, sd)
+        g, r = make_worlds(gpu_api, ref_api, b, j)
+        worlds.append((g, r))
+
+    def run(k):
+        try:
+            g = worlds[k][0]
+            for _ in range(25):
+                g.step()
+            results[k] = g.download_bodies()
+        except Exception as e:  # surfaced below: an assertion in a thread is otherwise silent
+            errors.append((k, e))
+
+    threads = [threading.Thread(target=run, args=(k,)) for k in range(len(seeds))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for k, (g, r) in enumerate(worlds):
+        for _ in range(25):
+            r.step()
+        ro = r.download_bodies()
+        for f in FIELDS:
+            assert np.array_equal(results[k][f].view(np.uint32), ro[f].view(np.uint32)), (k, f)
