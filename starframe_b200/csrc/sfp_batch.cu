@@ -48,6 +48,7 @@ struct BatchCtx {
     Counters* counters;    // [n_worlds]
     uint32_t* scratch;     // [n_worlds][bpw] per-body pair counts / offsets
     uint32_t tab_slots;    // colour-table slots per world (power of two)
+    uint32_t world_base;   // first world of this launch (blockIdx.x counts from it)
     uint32_t joint_cap;    // joint slots per world (0: the batch has no joints)
     const uint32_t* n_joints;  // [n_worlds] joints in use per world, or null
 };
@@ -230,7 +231,7 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
     k_batch_frame(BatchCtx b, float dt, uint32_t substeps, float rest_threshold) {
     extern __shared__ float4 dyn[];
     __shared__ uint32_t smem9[9];
-    const uint32_t w = blockIdx.x;
+    const uint32_t w = blockIdx.x + b.world_base;
     if (w >= b.n_worlds) return;
     Ctx c = world_view(b, w);
     if (!FULL) c.nj = 0;  // compile-time: the lean variant carries no joint code
@@ -513,6 +514,8 @@ struct SfpBatch {
     size_t pin_states = 0;
     uint32_t n_dynamic_total = 0;
     std::vector<uint32_t> n_dynamic;
+    cudaStream_t aux[3] = {nullptr, nullptr, nullptr};  // sfp_batch_step_host's pipeline
+    cudaEvent_t aux_done[3] = {nullptr, nullptr, nullptr};
     sfp::PolyTable polys;                // general-polygon table shared by all worlds
     float4* d_polytab = nullptr;
     bool has_polygons = false;
@@ -649,6 +652,10 @@ int32_t sfp_batch_destroy(SfpBatch* b) {
     for (void* p : b->allocs) cudaFree(p);
     for (void* p : b->joint_allocs) cudaFree(p);
     if (b->d_polytab) cudaFree(b->d_polytab);
+    for (int k = 0; k < 3; ++k) {
+        if (b->aux_done[k]) cudaEventDestroy(b->aux_done[k]);
+        if (b->aux[k]) cudaStreamDestroy(b->aux[k]);
+    }
     if (b->pin_state) cudaFreeHost(b->pin_state);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
@@ -790,6 +797,23 @@ int32_t sfp_batch_set_joints(SfpBatch* b, const SfpJointDesc* joints, uint32_t j
     return SFP_OK;
 }
 
+namespace {
+// worlds [w0, w0 + nw) of the batch, one CTA each, on `st`
+void launch_batch_frame(SfpBatch* b, cudaStream_t st, uint32_t w0, uint32_t nw, float dt,
+                        uint32_t substeps, float rt) {
+    BatchCtx ctx = b->ctx;
+    ctx.world_base = w0;
+    const bool full = b->has_polygons || b->joint_cap != 0u;
+    if (b->smem_bytes) {
+        if (full) k_batch_frame<true, true><<<nw, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
+        else k_batch_frame<true, false><<<nw, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
+    } else {
+        if (full) k_batch_frame<false, true><<<nw, BTPB, 0, st>>>(ctx, dt, substeps, rt);
+        else k_batch_frame<false, false><<<nw, BTPB, 0, st>>>(ctx, dt, substeps, rt);
+    }
+}
+}  // namespace
+
 int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     if (!b || !(dt > 0.0f) || substeps == 0 || substeps > 1024 || !b->uploaded)
         return SFP_E_INVALID;
@@ -802,19 +826,7 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     b->ctx.base.tab_new = b->d_tab[b->colour_age & 1u];
     b->colour_age += 1;
     BCU(cudaEventRecord(b->ev0, b->stream));
-    const float rt = 2.0f * g * h;
-    const bool full = b->has_polygons || b->joint_cap != 0u;
-    if (b->smem_bytes) {
-        if (full)
-            k_batch_frame<true, true><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps, rt);
-        else
-            k_batch_frame<true, false><<<b->n_worlds, BTPB, b->smem_bytes, b->stream>>>(b->ctx, dt, substeps, rt);
-    } else {
-        if (full)
-            k_batch_frame<false, true><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, rt);
-        else
-            k_batch_frame<false, false><<<b->n_worlds, BTPB, 0, b->stream>>>(b->ctx, dt, substeps, rt);
-    }
+    launch_batch_frame(b, b->stream, 0u, b->n_worlds, dt, substeps, 2.0f * g * h);
     BCU(cudaGetLastError());
     BCU(cudaEventRecord(b->ev1, b->stream));
     b->timed = true;
@@ -866,6 +878,51 @@ int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBodyState* o
     if (b->sticky != SFP_OK) return b->sticky;
     BCU(cudaSetDevice(b->device));
     const size_t nb = (size_t)b->n_worlds * b->bpw;
+    if (batch_host_pinned(in) && batch_host_pinned(out) && b->n_worlds >= 64u) {
+        // Both arrays page-locked: the worlds go through in four slices on three extra streams,
+        // so that a slice's upload and download overlap the other slices' frames (the worlds
+        // are independent; each slice is the same kernel over its own world range).
+        for (int k = 0; k < 3; ++k) {
+            if (!b->aux[k]) BCU(cudaStreamCreateWithFlags(&b->aux[k], cudaStreamNonBlocking));
+            if (!b->aux_done[k]) BCU(cudaEventCreateWithFlags(&b->aux_done[k], cudaEventDisableTiming));
+        }
+        const float h = dt / (float)substeps;
+        const float g = sqrtf(b->p.gravity_x * b->p.gravity_x + b->p.gravity_y * b->p.gravity_y);
+        b->ctx.base.warm = (b->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+        b->ctx.base.tab_old = b->d_tab[(b->colour_age + 1u) & 1u];
+        b->ctx.base.tab_new = b->d_tab[b->colour_age & 1u];
+        b->colour_age += 1;
+        BCU(cudaEventRecord(b->ev0, b->stream));
+        for (int k = 0; k < 3; ++k) BCU(cudaStreamWaitEvent(b->aux[k], b->ev0, 0));
+        const uint32_t slices = 4, per = (b->n_worlds + slices - 1u) / slices;
+        for (uint32_t k = 0; k < slices; ++k) {
+            const uint32_t w0 = k * per;
+            if (w0 >= b->n_worlds) break;
+            const uint32_t nw = std::min(per, b->n_worlds - w0);
+            const size_t o = (size_t)w0 * b->bpw, m = (size_t)nw * b->bpw;
+            cudaStream_t st = (k == 0) ? b->stream : b->aux[(k - 1u) % 3u];
+            const unsigned blocks = (unsigned)std::min<size_t>((m + 255) / 256, 148 * 4);
+            BCU(cudaMemcpyAsync(b->d_state + o, in + o, sizeof(SfpBodyState) * m,
+                                cudaMemcpyHostToDevice, st));
+            k_batch_unpack<<<blocks, 256, 0, st>>>(b->d_state + o, b->ctx.base.minv + o,
+                                                   b->ctx.base.pose + o, b->ctx.base.vel + o, m);
+            launch_batch_frame(b, st, w0, nw, dt, substeps, 2.0f * g * h);
+            k_batch_pack<<<blocks, 256, 0, st>>>(b->ctx.base.pose + o, b->ctx.base.vel + o,
+                                                 b->d_state + o, m);
+            BCU(cudaGetLastError());
+            BCU(cudaMemcpyAsync(out + o, b->d_state + o, sizeof(SfpBodyState) * m,
+                                cudaMemcpyDeviceToHost, st));
+            if (k > 0) BCU(cudaEventRecord(b->aux_done[(k - 1u) % 3u], st));
+        }
+        for (int k = 0; k < 3; ++k) BCU(cudaStreamWaitEvent(b->stream, b->aux_done[k], 0));
+        BCU(cudaEventRecord(b->ev1, b->stream));
+        b->timed = true;
+        b->stepped = true;
+        b->frames += 1;
+        b->body_substeps += (uint64_t)b->n_worlds * b->bpw * substeps;
+        BCU(cudaStreamSynchronize(b->stream));
+        return SFP_OK;
+    }
     if (batch_host_pinned(in)) {
         BCU(cudaMemcpyAsync(b->d_state, in, sizeof(SfpBodyState) * nb, cudaMemcpyHostToDevice,
                             b->stream));

@@ -119,11 +119,12 @@ def test_batch_rejects_bad_arguments(gpu_api):
         b.step()  # nothing uploaded
 
 
-@pytest.mark.parametrize("pinned", [False, True])
-def test_batch_step_host_matches_oracle(gpu_api, ref_api, pinned):
+@pytest.mark.parametrize("pinned,nw,bpw", [(False, 5, 128), (True, 5, 128), (True, 70, 64)])
+def test_batch_step_host_matches_oracle(gpu_api, ref_api, pinned, nw, bpw):
     """sfp_batch_step_host: states in from the host every frame (edited by the "game" in between),
-    one frame, states out — against the oracle's sfp_ref_step_host per world, bit for bit"""
-    nw, bpw, frames = 5, 128, 30
+    one frame, states out — against the oracle's sfp_ref_step_host per world, bit for bit
+    (64 worlds and more with page-locked arrays take the sliced, overlapped path)"""
+    frames = 30
     bodies = scenes.worlds(nw, bpw)
     batch = sf.Batch(gpu_api, nw, bpw)
     batch.upload(bodies)
