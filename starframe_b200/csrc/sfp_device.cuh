@@ -494,7 +494,7 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
     // the idle lanes (100 k bodies: 205 -> 227 us), so there each thread keeps its own pair.
     // (The order of the list is whatever the shared-memory atomic gives: each pair is still
     // handled exactly once and writes only its own record.)
-    __shared__ uint32_t s_list[256];
+    __shared__ uint32_t s_list[512];  // one slot per thread of the block (blocks are <= 512 wide)
     __shared__ uint32_t s_n;
     const uint32_t P = c.cnt->n_pairs;
     const bool compact = P >= 6u * nth;
