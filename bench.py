@@ -464,18 +464,21 @@ def run_reference(args, rank, world_size):
     api = loader.api()
     cores = os.cpu_count() or 1
     if args.workload != "worlds512":
-        # a single scene's Gauss-Seidel sweep is serial: 1 thread.  Sample: a narrower pile from the
-        # same generator with the same depth (100 rows), so per-body work matches the full scene.
-        full_n = {"pile100k": 100_000, "circles10k": 10_000}.get(args.workload)
+        # All host threads: the oracle's colour-order step runs each colour's constraints (and the
+        # per-body / per-pair loops) on SFP_REF_THREADS threads, with the same bits as one thread
+        # (scripts/oracle_threads.py); its broadphase and colouring stay sequential.  Sample: a
+        # narrower pile from the same generator with the same depth (100 rows), so per-body work
+        # matches the full scene.
+        os.environ["SFP_REF_THREADS"] = str(cores)
         if args.workload == "pile100k":
-            n_sample = 6000
-            bodies, joints = scenes.mixed_pile(n_sample, cols=60)
-            what = f"{n_sample}-body slice of pile100k (same generator, 60 columns x 100 rows)"
+            n_sample = 30000
+            bodies, joints = scenes.mixed_pile(n_sample, cols=300)
+            what = f"{n_sample}-body slice of pile100k (same generator, 300 columns x 100 rows)"
         else:
             bodies, joints = make_scene(args.workload)
             what = f"the full {args.workload} scene"
         n = len(bodies)
-        ref = sf.World(api, solver_order=_ffi.ORDER_REFERENCE)
+        ref = sf.World(api, solver_order=_ffi.ORDER_COLOUR)
         ref.upload_bodies(bodies)
         ref.set_joints(joints)
         for _ in range(args.settle + args.warmup):
@@ -490,10 +493,10 @@ def run_reference(args, rank, world_size):
         s = time.perf_counter() - t1
         st = ref.stats()
         value = n * SUBSTEPS * done / s
-        used = 1
+        used = cores
         sample = (f"{what}, settled {args.settle} frames on the CPU, then {done} timed frames; "
-                  f"1 thread (pairs/body {st['n_pairs'] / n:.2f}, contacts/body "
-                  f"{st['n_contacts'] / n:.2f}); host has {cores} logical cores")
+                  f"{cores} threads in the solver loops (pairs/body {st['n_pairs'] / n:.2f}, "
+                  f"contacts/body {st['n_contacts'] / n:.2f}); host has {cores} logical cores")
         workload, steps = args.workload, done
     else:
         nw = min(args.worlds_per_gpu * world_size, 4 * cores)
@@ -533,7 +536,8 @@ def run_reference(args, rank, world_size):
         "e2e": {"value": value, "unit": "body-substeps/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "note": "reference CPU step unavailable (tree not mounted, BASELINE.md §0): this is the "
-                "CPU oracle port, sequential Gauss-Seidel in reference order",
+                "CPU oracle port (single scene: colour-order Gauss-Seidel, colours in parallel; "
+                "worlds: one sequential world per task)",
     }
 
 

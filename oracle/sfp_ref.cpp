@@ -11,18 +11,27 @@
  *     capsule / rounded-polygon colliders, XPBD projection of contacts and distance/rope
  *     joints, velocity update with friction and restitution), and
  *   - the public XPBD rigid-body algorithm (Müller et al. 2020), Algorithm 2 + §3.5/3.6,
- * in plain sequential C++ (single thread, Gauss-Seidel).  It is pinned to PHYSICS instead, by
- * the analytic known-answer tests in tests/test_oracle_kat.py.
+ * in plain sequential C++ (Gauss-Seidel; one thread unless SFP_REF_THREADS asks for more, in
+ * which case the loops over bodies, pairs and the constraints of ONE colour are split over a
+ * small pool — same bits, see tests/test_oracle_props.py — for bench.py's CPU arm).  It is
+ * pinned to PHYSICS instead, by the analytic known-answer tests in tests/test_oracle_kat.py.
  *
  * The per-item arithmetic lives in include/sfp_math.h, compiled here with -ffp-contract=off.
  * The data-parallel structure (hashing, sorting, colouring rounds, solve order) is restated
  * here independently of the CUDA code: sequential loops over std::vector.
  */
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -31,6 +40,81 @@
 #include "sfp_math.h"
 
 using namespace sfp;
+
+/* A small persistent fork-join pool for the colour-order step (SFP_REF_THREADS > 1): the
+ * caller is worker 0, the others sleep on a condition variable between loops.  Static
+ * partition of [0, n) into one contiguous range per worker; no work stealing, no atomics on the
+ * data — the loops it runs touch disjoint items by construction. */
+class Pool {
+   public:
+    explicit Pool(int workers) : n_workers_(workers) {
+        for (int t = 1; t < workers; ++t) threads_.emplace_back([this, t] { run(t); });
+    }
+    ~Pool() {
+        stop_.store(true, std::memory_order_release);
+        epoch_.fetch_add(1, std::memory_order_acq_rel);
+        {
+            std::unique_lock<std::mutex> lk(m_);
+        }
+        cv_.notify_all();
+        for (auto& th : threads_) th.join();
+    }
+    int workers() const { return n_workers_; }
+    template <typename F>
+    void run_loop(size_t n, const F& f) {
+        fn_ = [&](int t) {
+            size_t lo = n * (size_t)t / (size_t)n_workers_, hi = n * (size_t)(t + 1) / (size_t)n_workers_;
+            for (size_t i = lo; i < hi; ++i) f(i, t);
+        };
+        pending_.store(n_workers_ - 1, std::memory_order_release);
+        epoch_.fetch_add(1, std::memory_order_acq_rel);
+        if (sleepers_.load(std::memory_order_acquire) > 0) {
+            {
+                std::unique_lock<std::mutex> lk(m_);
+            }
+            cv_.notify_all();
+        }
+        fn_(0);
+        while (pending_.load(std::memory_order_acquire) != 0) cpu_relax();
+    }
+
+   private:
+    static void cpu_relax() {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+    }
+    /* the loops of a substep follow each other within microseconds: spin first, sleep only when
+     * the owner has gone quiet (between frames, or when the world is idle) */
+    void run(int t) {
+        unsigned long seen = 0;
+        for (;;) {
+            int spins = 0;
+            while (epoch_.load(std::memory_order_acquire) == seen) {
+                if (++spins < 200000) {
+                    cpu_relax();
+                } else {
+                    std::unique_lock<std::mutex> lk(m_);
+                    sleepers_.fetch_add(1, std::memory_order_acq_rel);
+                    cv_.wait(lk, [&] { return epoch_.load(std::memory_order_acquire) != seen; });
+                    sleepers_.fetch_sub(1, std::memory_order_acq_rel);
+                }
+            }
+            seen = epoch_.load(std::memory_order_acquire);
+            if (stop_.load(std::memory_order_acquire)) return;
+            fn_(t);
+            pending_.fetch_sub(1, std::memory_order_acq_rel);
+        }
+    }
+    int n_workers_;
+    std::vector<std::thread> threads_;
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::function<void(int)> fn_;
+    std::atomic<unsigned long> epoch_{0};
+    std::atomic<int> pending_{0}, sleepers_{0};
+    std::atomic<bool> stop_{false};
+};
 
 struct SfpWorld {
     SfpParams p;
@@ -50,6 +134,13 @@ struct SfpWorld {
     std::unordered_map<uint64_t, uint32_t> prev_pair_colour;
     std::vector<uint32_t> prev_joint_colour;
     uint32_t colour_age = 0; /* colourings since the last upload */
+    /* constraints of each colour, in index order (rebuilt with every colouring) */
+    std::vector<std::vector<uint32_t>> pairs_of, joints_of;
+    /* CPU threads for the colour-order step (env SFP_REF_THREADS, default 1).  Constraints of one
+     * colour touch disjoint dynamic bodies and every other loop is per body or per pair, so the
+     * result does not depend on the thread count (tests/test_oracle_props.py checks). */
+    int threads = 1;
+    std::unique_ptr<Pool> pool;
     SfpStats stats;
     std::string err;
     float last_ms = 0.0f;
@@ -68,6 +159,17 @@ bool is_dynamic(const SfpWorld& w, uint32_t i) { return w.minv[i].x > 0.0f || w.
 bool pair_allowed(const SfpWorld& w, uint32_t a, uint32_t b) {
     if (!is_dynamic(w, a) && !is_dynamic(w, b)) return false;
     return layers_collide(f2u(w.mat[a].w), f2u(w.mat[b].w));
+}
+
+/* f(i, worker) for i in [0, n); with T == 1 (or a short loop) a plain loop in the caller */
+template <typename F>
+void parallel_for(SfpWorld& w, int T, size_t n, const F& f) {
+    if (T <= 1 || n < 256) {
+        for (size_t i = 0; i < n; ++i) f(i, 0);
+        return;
+    }
+    if (!w.pool || w.pool->workers() != T) w.pool.reset(new Pool(T));
+    w.pool->run_loop(n, f);
 }
 
 void compute_aabbs(const SfpWorld& w, float dt, std::vector<f4>& aabb) {
@@ -232,6 +334,12 @@ int colour_constraints(SfpWorld& w) {
     for (uint32_t k = 0; k < P; ++k)
         w.prev_pair_colour[ctab_key(w.pairs[k].a, w.pairs[k].b)] = w.pair_colour[k];
     w.prev_joint_colour = w.joint_colour;
+    w.pairs_of.assign(SFP_MAX_COLOURS, {});
+    w.joints_of.assign(SFP_MAX_COLOURS, {});
+    for (uint32_t k = 0; k < P; ++k)
+        if (w.pair_colour[k] < SFP_MAX_COLOURS) w.pairs_of[w.pair_colour[k]].push_back(k);
+    for (uint32_t k = 0; k < (uint32_t)w.joints.size(); ++k)
+        if (w.joint_colour[k] < SFP_MAX_COLOURS) w.joints_of[w.joint_colour[k]].push_back(k);
     if (overflow) {
         w.stats.overflow |= 4u;
         w.err = "more than SFP_SERIAL_MAX constraints left without a colour";
@@ -321,24 +429,32 @@ void substep(SfpWorld& w, float h) {
     const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
     const float g = sqrtf(w.p.gravity_x * w.p.gravity_x + w.p.gravity_y * w.p.gravity_y);
     const float rest_threshold = 2.0f * g * h;
+    const int T = w.threads; /* 1: plain sequential loops in the caller */
     /* A3 */
-    for (uint32_t i = 0; i < w.n; ++i) {
+    parallel_for(w, T, w.n, [&](size_t i, int) {
         integrate_body(&w.pose[i], &w.prev[i], &w.vel[i], w.minv[i], w.p.gravity_x, w.p.gravity_y, h);
-    }
+    });
     /* A4 */
     w.contacts.resize(P);
     w.lambdas.assign(P, f4{0.0f, 0.0f, 0.0f, 0.0f});
-    uint32_t npts = 0, nman = 0;
-    float maxpen = 0.0f;
-    for (uint32_t k = 0; k < P; ++k) {
+    std::vector<uint32_t> t_npts((size_t)T, 0u), t_nman((size_t)T, 0u);
+    std::vector<float> t_maxpen((size_t)T, 0.0f);
+    parallel_for(w, T, P, [&](size_t k, int t) {
         uint32_t a = w.pairs[k].a, b = w.pairs[k].b;
         w.contacts[k] = narrowphase<true>(w.pose[a], w.vel[a], w.shape[a], w.mat[a], w.pose[b], w.vel[b],
                                     w.shape[b], w.mat[b], w.p.contact_margin, w.polys.recs.data());
         uint32_t cnt = f2u(w.contacts[k].b.y);
-        npts += cnt;
-        nman += cnt > 0 ? 1u : 0u;
-        if (cnt > 0) maxpen = std::max(maxpen, -w.contacts[k].s.x);
-        if (cnt > 1) maxpen = std::max(maxpen, -w.contacts[k].s.y);
+        t_npts[t] += cnt;
+        t_nman[t] += cnt > 0 ? 1u : 0u;
+        if (cnt > 0) t_maxpen[t] = std::max(t_maxpen[t], -w.contacts[k].s.x);
+        if (cnt > 1) t_maxpen[t] = std::max(t_maxpen[t], -w.contacts[k].s.y);
+    });
+    uint32_t npts = 0, nman = 0;
+    float maxpen = 0.0f;
+    for (int t = 0; t < T; ++t) {
+        npts += t_npts[t];
+        nman += t_nman[t];
+        maxpen = std::max(maxpen, t_maxpen[t]);
     }
     w.stats.n_contacts = npts;
     w.stats.n_manifolds = nman;
@@ -361,22 +477,26 @@ void substep(SfpWorld& w, float h) {
         for (uint32_t k = 0; k < P; ++k) solve_pair_position(w, k);
     } else {
         for (uint32_t c : order) {
-            for (uint32_t k = 0; k < J; ++k)
-                if (w.joint_colour[k] == c) solve_joint_position(w, k, inv_h2);
-            for (uint32_t k = 0; k < P; ++k)
-                if (w.pair_colour[k] == c) solve_pair_position(w, k);
+            const std::vector<uint32_t>&jl = w.joints_of[c], &pl = w.pairs_of[c];
+            /* the serial group's members may share bodies: always in sequence */
+            const int Tc = (c == SFP_SERIAL_COLOUR) ? 1 : T;
+            parallel_for(w, Tc, jl.size(), [&](size_t i, int) { solve_joint_position(w, jl[i], inv_h2); });
+            parallel_for(w, Tc, pl.size(), [&](size_t i, int) { solve_pair_position(w, pl[i]); });
         }
     }
     /* A7 (i) */
-    for (uint32_t i = 0; i < w.n; ++i)
+    parallel_for(w, T, w.n, [&](size_t i, int) {
         w.vel[i] = derive_velocity(w.pose[i], w.prev[i], w.vel[i], w.minv[i], inv_h);
+    });
     /* A7 (ii) */
     if (w.p.solver_order == SFP_ORDER_REFERENCE) {
         for (uint32_t k = 0; k < P; ++k) solve_pair_velocity(w, k, h, rest_threshold);
     } else {
-        for (uint32_t c : order)
-            for (uint32_t k = 0; k < P; ++k)
-                if (w.pair_colour[k] == c) solve_pair_velocity(w, k, h, rest_threshold);
+        for (uint32_t c : order) {
+            const std::vector<uint32_t>& pl = w.pairs_of[c];
+            const int Tc = (c == SFP_SERIAL_COLOUR) ? 1 : T;
+            parallel_for(w, Tc, pl.size(), [&](size_t i, int) { solve_pair_velocity(w, pl[i], h, rest_threshold); });
+        }
     }
 }
 
@@ -423,6 +543,10 @@ int32_t sfp_ref_create(const SfpParams* params, SfpWorld** out) {
     if (!w) return SFP_E_NOMEM;
     w->p = p;
     std::memset(&w->stats, 0, sizeof(w->stats));
+    if (const char* e = std::getenv("SFP_REF_THREADS")) {
+        int t = std::atoi(e);
+        w->threads = t < 1 ? 1 : (t > 256 ? 256 : t);
+    }
     *out = w;
     return SFP_OK;
 }

@@ -280,3 +280,26 @@ def test_serial_group_when_a_body_has_more_partners_than_colours(ref_api):
     s = w.download_bodies()
     assert abs(s["y"][plank] - 0.06) < 5e-3 and abs(s["angle"][plank]) < 1e-3
     assert np.all(s["y"][2:] > 0.1) and np.abs(s["vy"]).max() < 0.05  # riders rest on the plank
+
+
+def test_threaded_colour_order_step_has_the_same_bits(ref_api, monkeypatch):
+    """SFP_REF_THREADS: constraints of one colour touch disjoint dynamic bodies and every other
+    loop is per body or per pair, so the thread count must not change a single bit"""
+    import starframe_b200 as sf
+    from starframe_b200 import scenes
+
+    b, j = scenes.ropes(n_ropes=12, links=16, n_free=900)
+    out = {}
+    for threads in (1, 3):
+        monkeypatch.setenv("SFP_REF_THREADS", str(threads))
+        w = sf.World(ref_api)
+        w.upload_bodies(b)
+        w.set_joints(j)
+        for _ in range(25):
+            w.step()
+        out[threads] = (w.download_bodies(), w.stats())
+    for f in ("x", "y", "c", "s", "vx", "vy", "omega", "angle"):
+        assert np.array_equal(out[1][0][f].view(np.uint32), out[3][0][f].view(np.uint32)), f
+    for k in ("n_pairs", "n_contacts", "n_manifolds", "n_colours"):
+        assert out[1][1][k] == out[3][1][k]
+    assert out[1][1]["n_contacts"] > 300
