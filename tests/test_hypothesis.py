@@ -143,3 +143,49 @@ def test_gpu_matches_oracle_on_generated_worlds(gpu_api, ref_api, spec):
     a, c = g.download_bodies(), r.download_bodies()
     for f in FIELDS + ("angle",):
         assert np.array_equal(a[f].view(np.uint32), c[f].view(np.uint32)), f
+
+
+batch_worlds = st.tuples(
+    st.lists(st.tuples(st.lists(body, min_size=12, max_size=12),
+                       st.lists(st.tuples(st.integers(0, 63), st.integers(0, 63), f32(0.2, 1.5),
+                                          st.integers(0, 1), st.sampled_from([0.0, 1.0e-4])),
+                                max_size=4)),
+             min_size=2, max_size=4),
+    st.sampled_from([0.25, 0.5]),
+)
+
+
+@pytest.mark.gpu
+@settings(max_examples=100, **SETTINGS)
+@given(batch_worlds)
+def test_gpu_batch_matches_oracle_on_generated_worlds(gpu_api, ref_api, spec):
+    """the same adversarial worlds, several of them in one batch (polygons and joints: the full
+    kernel variant), each against its own oracle world"""
+    specs, cell = spec
+    built = [build(bs, js) for bs, js in specs]
+    nw, n = len(built), len(built[0][0])
+    jmax = max(len(j) for _, j in built)
+    bodies = np.stack([b for b, _ in built])
+    batch = sf.Batch(gpu_api, nw, n, cell_size=cell)
+    batch.set_polygons(scenes.polygon_table())
+    batch.upload(bodies)
+    if jmax:
+        packed = np.zeros((nw, jmax), dtype=JOINT_DESC_DTYPE)
+        counts = np.zeros(nw, dtype=np.uint32)
+        for w, (_, j) in enumerate(built):
+            packed[w, :len(j)] = j
+            counts[w] = len(j)
+        batch.set_joints(packed, counts)
+    refs = [make(ref_api, b, j, cell) for b, j in built]
+    for _ in range(3):
+        batch.step()
+        for r in refs:
+            r.step()
+    out, st_ = batch.download(), batch.stats()
+    for w, r in enumerate(refs):
+        c = r.download_bodies()
+        for f in FIELDS:
+            assert np.array_equal(out[w][f].view(np.uint32), c[f].view(np.uint32)), (w, f)
+        rs = r.stats()
+        for k in ("n_pairs", "n_contacts", "n_colours"):
+            assert st_[k][w] == rs[k], (w, k)
