@@ -127,12 +127,21 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
 
 // (cell, body) entries, written to the SECOND buffer pair: the three radix passes that follow
 // (24-bit key) ping-pong 1 -> 0 -> 1 -> 0 and leave the sorted list in ekey0 / eval0.
-// A body covering few cells writes them itself; a body covering many
-// (the floor of a pile covers thousands) is handed to its whole warp, 32 cells per step.
+// A body covering few cells writes them itself; a body covering more than 32 is handed to its
+// whole warp, 32 cells per step; a body covering more than 512 (the floor and the walls of a
+// pile cover a thousand and more: one warp walking them alone was 10 us of this 20 us stage)
+// is handed to the whole block.  Every thread of the block must call this.
 __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, uint32_t nth) {
+    constexpr uint32_t HUGE_SLOTS = 8;
+    __shared__ int s_hx0[HUGE_SLOTS], s_hy0[HUGE_SLOTS];
+    __shared__ uint32_t s_hw[HUGE_SLOTS], s_ho[HUGE_SLOTS], s_hcnt[HUGE_SLOTS], s_hi[HUGE_SLOTS];
+    __shared__ uint32_t s_nh;
     const uint32_t lane = threadIdx.x & 31u;
-    for (uint32_t base = tid - lane; base < c.n; base += nth) {
-        const uint32_t i = base + lane;
+    for (uint32_t bbase = tid - threadIdx.x; bbase < c.n; bbase += nth) {
+        if (threadIdx.x == 0) s_nh = 0u;
+        __syncthreads();
+        const uint32_t i = bbase + threadIdx.x;
+        const uint32_t base = i - lane;
         int x0 = 0, y0 = 0, x1 = -1, y1 = -1;
         uint32_t o = 0, cnt = 0;
         if (i < c.n) {
@@ -141,8 +150,21 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
             o = c.cell_off[i];
             cnt = (uint32_t)(x1 - x0 + 1) * (uint32_t)(y1 - y0 + 1);
         }
-        const bool big = cnt > 32u;
-        if (!big) {
+        bool taken = false;
+        if (cnt > 512u) {
+            const uint32_t slot = atomicAdd(&s_nh, 1u);
+            if (slot < HUGE_SLOTS) {
+                s_hx0[slot] = x0;
+                s_hy0[slot] = y0;
+                s_hw[slot] = (uint32_t)(x1 - x0 + 1);
+                s_ho[slot] = o;
+                s_hcnt[slot] = cnt;
+                s_hi[slot] = i;
+                taken = true;
+            }
+        }
+        const bool big = cnt > 32u && !taken;
+        if (cnt <= 32u) {
             for (int cy = y0; cy <= y1; ++cy)
                 for (int cx = x0; cx <= x1; ++cx) {
                     if (o < c.cap_entries) {
@@ -170,6 +192,20 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
                 }
             }
         }
+        __syncthreads();
+        const uint32_t nh = s_nh < HUGE_SLOTS ? s_nh : HUGE_SLOTS;
+        for (uint32_t j = 0; j < nh; ++j) {
+            const uint32_t w = s_hw[j], bo = s_ho[j], bcnt = s_hcnt[j], bi = s_hi[j];
+            const int bx0 = s_hx0[j], by0 = s_hy0[j];
+            for (uint32_t k = threadIdx.x; k < bcnt; k += blockDim.x) {
+                uint32_t pos = bo + k;
+                if (pos < c.cap_entries) {
+                    c.ekey1[pos] = sfp::cell_key(bx0 + (int)(k % w), by0 + (int)(k / w));
+                    c.eval1[pos] = bi;
+                }
+            }
+        }
+        __syncthreads();
     }
     if (tid == 0 && c.cnt->n_entries > c.cap_entries) {
         c.cnt->n_entries = c.cap_entries;
@@ -178,36 +214,63 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
 }
 
 // pair test shared by the count and the write pass; entries are sorted by cell key
-__device__ __forceinline__ bool pair_test(const Ctx& c, int cx, int cy, uint32_t a, f4 bba, int4 ma,
-                                          uint32_t b) {
+__device__ __forceinline__ bool pair_test(int cx, int cy, uint32_t a, f4 bba, int4 ma, uint32_t b,
+                                          int4 mb, f4 bbb) {
     if (a == b) return false;
-    int4 mb = c.meta[b];
     if ((ma.w | mb.w) == 0) return false;
     if (!sfp::same_cell(max(ma.x, mb.x), max(ma.y, mb.y), cx, cy)) return false;
     if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
-    return sfp::aabb_overlap(bba, ld4(c.aabb, b));
+    return sfp::aabb_overlap(bba, bbb);
 }
 
+// One thread per entry: the rest of the entry's cell is scanned for partners.  The scan is a
+// chain of dependent loads (next key -> its body -> that body's box), so it goes four entries
+// at a time: the four keys and bodies are loaded together, then the boxes of those that are
+// still in the cell — two round trips per four candidates instead of three per candidate.
 template <bool WRITE>
 __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
                                             const uint32_t* eval, uint32_t tid, uint32_t nth) {
     const uint32_t E = c.cnt->n_entries;
     for (uint32_t e = tid; e < E; e += nth) {
-        uint32_t key = ekey[e], a = eval[e];
+        const uint32_t key = ekey[e], a = eval[e];
         int cx = sfp::key_cx(key), cy = sfp::key_cy(key);
         f4 bba = ld4(c.aabb, a);
         int4 ma = c.meta[a];
         uint32_t k = 0;
         uint32_t o = WRITE ? c.poff[e] : 0u;
-        for (uint32_t f = e + 1; f < E && ekey[f] == key; ++f) {
-            uint32_t b = eval[f];
-            if (pair_test(c, cx, cy, a, bba, ma, b)) {
-                if (WRITE) {
-                    if (o + k < c.cap_pairs)
-                        c.pairs_raw[o + k] = make_uint2(min(a, b), max(a, b));
-                }
-                ++k;
+        for (uint32_t f = e + 1; f < E; f += 4u) {
+            uint32_t kf[4], bf[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t idx = f + (uint32_t)j;
+                const bool in = idx < E;
+                kf[j] = in ? ekey[idx] : ~key;
+                bf[j] = in ? eval[idx] : 0u;
             }
+            bool same[4];
+            same[0] = kf[0] == key;
+#pragma unroll
+            for (int j = 1; j < 4; ++j) same[j] = same[j - 1] && kf[j] == key;
+            int4 mb[4];
+            f4 bbb[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (same[j]) {
+                    mb[j] = c.meta[bf[j]];
+                    bbb[j] = ld4(c.aabb, bf[j]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (same[j] && pair_test(cx, cy, a, bba, ma, bf[j], mb[j], bbb[j])) {
+                    if (WRITE) {
+                        if (o + k < c.cap_pairs)
+                            c.pairs_raw[o + k] = make_uint2(min(a, bf[j]), max(a, bf[j]));
+                    }
+                    ++k;
+                }
+            }
+            if (!same[3]) break;
         }
         if (!WRITE) c.pcnt[e] = k;
     }
