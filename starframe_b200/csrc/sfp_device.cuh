@@ -216,11 +216,12 @@ __device__ __forceinline__ void stage_emit_entries(const Ctx& c, uint32_t tid, u
 // pair test shared by the count and the write pass; entries are sorted by cell key
 __device__ __forceinline__ bool pair_test(int cx, int cy, uint32_t a, f4 bba, int4 ma, uint32_t b,
                                           int4 mb, f4 bbb) {
+    // (a conjunction: the box test goes first because it rejects most candidates of a cell)
+    if (!sfp::aabb_overlap(bba, bbb)) return false;
     if (a == b) return false;
     if ((ma.w | mb.w) == 0) return false;
     if (!sfp::same_cell(max(ma.x, mb.x), max(ma.y, mb.y), cx, cy)) return false;
-    if (!sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z)) return false;
-    return sfp::aabb_overlap(bba, bbb);
+    return sfp::layers_collide((uint32_t)ma.z, (uint32_t)mb.z);
 }
 
 // One thread per entry: the rest of the entry's cell is scanned for partners.  The scan is a
