@@ -59,6 +59,9 @@ struct Ctx {
     uint2* pairs_raw;
     // colouring
     unsigned long long *mask, *claim0, *claim1;
+    // dataflow solve (k_substeps_flow): per body, the colours whose constraint has been applied
+    // in the current substep's position pass [2 i] and velocity pass [2 i + 1]; null elsewhere
+    unsigned long long* done;
     uint32_t *pcol, *jcol;
     // pairs that the warm start left uncoloured, in any order (null: the rounds walk all pairs);
     // after a warm start that is a few per cent of the pairs
@@ -312,6 +315,18 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
     for (uint32_t k = tid; k < MAX_ROUNDS; k += nth) c.cnt->round_flags[k] = 0u;
 }
 
+// Sort key of a coloured pair: bits 0-1 narrowphase class, bits 2-7 colour (the radix pass sorts on
+// these eight), bit 8 / 9 set when body a / b is static (rides along into pcol_sorted, where the
+// dataflow solve reads colour and flags of a pair with one coalesced load).
+__device__ __forceinline__ uint32_t pair_sort_key(const Ctx& c, uint32_t col, uint2 p) {
+    return (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y)) |
+           (c.meta[p.x].w ? 0u : 0x100u) | (c.meta[p.y].w ? 0u : 0x200u);
+}
+constexpr uint32_t PAIR_KEY_COLOUR_MASK = (uint32_t)SFP_MAX_COLOURS - 1u;
+__device__ __forceinline__ uint32_t pair_key_colour(uint32_t key) {
+    return (key >> SFP_TYPE_BITS) & PAIR_KEY_COLOUR_MASK;
+}
+
 // warm start: a constraint that existed in the previous frame keeps its colour.  Runs after
 // stage_colour_init (masks are zero), before the first round.
 __device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b, uint32_t col) {
@@ -339,8 +354,7 @@ __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, ui
                 if ((slot & SFP_CTAB_KEYMASK) == key) {
                     uint32_t col = (uint32_t)(slot >> 44) - 1u;
                     colour_keep(c, p.x, p.y, col);
-                    c.pcol[k] = (col << SFP_TYPE_BITS) |
-                                sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+                    c.pcol[k] = pair_sort_key(c, col, p);
                     found = true;
                     break;
                 }
@@ -371,7 +385,7 @@ __device__ __forceinline__ void stage_colour_record(const Ctx& c, uint32_t tid, 
         uint32_t key16 = c.pcol[k];
         if (key16 == UNCOLOURED) continue;
         uint2 p = c.pairs_raw[k];
-        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, key16 >> SFP_TYPE_BITS);
+        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, pair_key_colour(key16));
         uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
         while (atomicCAS(&c.tab_new[h], 0ull, packed) != 0ull) h = (h + 1u) & c.tab_mask;
     }
@@ -478,8 +492,7 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
                                            sfp::pair_priority(p.x, p.y), round);
             // sort key: colour in the high bits, narrowphase class in the low ones (coherence
             // inside a colour bucket)
-            if (col != UNCOLOURED)
-                col = (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y));
+            if (col != UNCOLOURED) col = pair_sort_key(c, col, p);
             c.pcol[k] = col;
         }
     }
@@ -496,8 +509,8 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
 // (`shift` strips the sub-key below the colour)
 __device__ __forceinline__ void colour_bounds(const uint32_t* sorted_col, uint32_t n, uint32_t i,
                                               uint32_t* off, int shift) {
-    uint32_t col = sorted_col[i] >> shift;
-    int prev = (i == 0) ? -1 : (int)(sorted_col[i - 1] >> shift);
+    uint32_t col = (sorted_col[i] >> shift) & PAIR_KEY_COLOUR_MASK;
+    int prev = (i == 0) ? -1 : (int)((sorted_col[i - 1] >> shift) & PAIR_KEY_COLOUR_MASK);
     for (int cc = prev + 1; cc <= (int)col; ++cc) off[cc] = i;
     if (i == n - 1)
         for (int cc = (int)col + 1; cc <= SFP_MAX_COLOURS; ++cc) off[cc] = n;
@@ -534,6 +547,7 @@ __device__ __forceinline__ void stage_integrate(const Ctx& c, float h, uint32_t 
         st4(c.prev, i, prev);
         st4(c.pose, i, pose);
         st4(c.vel, i, vel);
+        if (c.done) reinterpret_cast<ulonglong2*>(c.done)[i] = make_ulonglong2(0ull, 0ull);
     }
     if (tid == 0) {
         c.cnt->n_contacts = 0;
@@ -545,7 +559,27 @@ __device__ __forceinline__ void stage_integrate(const Ctx& c, float h, uint32_t 
 // ---------------------------------------------------------------------------------------
 // A4 narrowphase: one thread per candidate pair (colour-sorted order)
 // ---------------------------------------------------------------------------------------
-template <bool POLYS>
+// MARK (dataflow solve only): a pair without a contact in this substep is a no-op in both solver
+// passes, so it reports itself done on its dynamic bodies here and nobody ever waits for it.
+__device__ __forceinline__ void red_or_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("red.relaxed.gpu.global.or.b64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void flow_mark_noop(const Ctx& c, uint32_t k, uint2 p, bool pos_too) {
+    const uint32_t key = c.pcol_sorted[k];
+    const uint32_t col = pair_key_colour(key);
+    if (col == SFP_SERIAL_COLOUR) return;
+    const unsigned long long bit = 1ull << col;
+    if (!(key & 0x100u)) {
+        if (pos_too) red_or_u64(&c.done[2u * p.x], bit);
+        red_or_u64(&c.done[2u * p.x + 1u], bit);
+    }
+    if (!(key & 0x200u)) {
+        if (pos_too) red_or_u64(&c.done[2u * p.y], bit);
+        red_or_u64(&c.done[2u * p.y + 1u], bit);
+    }
+}
+
+template <bool POLYS, bool MARK = false>
 __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, uint32_t nth) {
     // Per block-sized chunk of pairs: (1) every thread tests its pair's bounding circles; a pair
     // that is out of reach gets its empty record at once.  (2) The SAT for the pairs in reach.
@@ -577,7 +611,10 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
             uint2 p = c.pairs[k];
             near = !sfp::narrowphase_far(ld4(c.pose, p.x), ld4(c.shape, p.x), ld4(c.pose, p.y),
                                          ld4(c.shape, p.y), c.contact_margin);
-            if (!near) c.cb[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (!near) {
+                c.cb[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                if (MARK) flow_mark_noop(c, k, p, true);
+            }
         }
         uint32_t k2 = near ? k : NONE;
         if (compact) {
@@ -599,6 +636,7 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
                 reinterpret_cast<const sfp::f4*>(c.polytab));
             uint32_t cnt = sfp::f2u(r.b.y);
             st4(c.cb, k2, r.b);
+            if (MARK && cnt == 0u) flow_mark_noop(c, k2, p, true);
             if (cnt) {  // an empty manifold is fully described by count == 0
                 st4(c.ca, k2, r.a);
                 st4(c.cp0, k2, r.p0);
@@ -772,6 +810,284 @@ __device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, f
                                                 float rest_threshold, uint32_t tid, uint32_t nth,
                                                 bool skip_first = false) {
     stage_solve_vel(c, colour, h, rest_threshold, tid, nth, skip_first, c.cnt->pair_col_off);
+}
+
+// ---------------------------------------------------------------------------------------
+// Dataflow solve (k_substeps_flow).  Coloured Gauss-Seidel needs, for every body, that its
+// constraints are applied one after another in the solve order of their colours — nothing
+// more.  A grid-wide barrier after every colour enforces far more than that (264 barriers a
+// frame at ~3 us each on a 100 k-body pile: most of the frame).  Here every body carries a
+// bit mask of the colours already applied to it in the current pass (Ctx::done).  A constraint
+// of colour c waits until the masks of its two bodies hold every colour those bodies use that
+// comes before c in the solve order (Ctx::mask, left by the colouring, says which those are),
+// reads the bodies, solves, writes them back and sets its bit: release fence + RED on the
+// writer's side, relaxed polling + acquire fence on the reader's.  The whole pass is one
+// grid-wide phase; the per-body order — and therefore every bit of the result — is that of
+// the barrier version and of the oracle.
+//
+// Work distribution: a colour's items (joints, then pairs) are cut into runs of 32, runs are
+// numbered in solve order and dealt round-robin to the grid's warps, each warp takes its runs
+// in ascending order.  A run depends only on runs with lower numbers, every warp is resident
+// (cooperative launch) and the lanes of a run never depend on each other (one colour), so the
+// waiting cannot deadlock.  A wait that does not end (a bug, not a data condition) gives up
+// after ~1 s and raises overflow bit 32.
+// ---------------------------------------------------------------------------------------
+struct FlowOrder {
+    uint32_t n;                                   // proper colours in use, in solve order
+    uint32_t run_base[SFP_MAX_COLOURS + 1];       // first run of the i-th colour of the order
+    unsigned long long before[SFP_MAX_COLOURS];   // colours that precede it
+    uint8_t colour[SFP_MAX_COLOURS];
+};
+
+// by ONE thread; joff / poff are the colour offsets of joints and pairs
+__device__ __forceinline__ void flow_build_order(const Ctx& c, uint32_t ncol, const uint32_t* joff,
+                                                 const uint32_t* poff, FlowOrder* fo) {
+    const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
+    const unsigned long long big = big_colour_mask(c, ncol);
+    const unsigned long long small = all & ~big & ~(1ull << SFP_SERIAL_COLOUR);
+    uint32_t n = 0, runs = 0;
+    unsigned long long acc = 0ull;
+    for (int pass = 0; pass < 2; ++pass) {
+        const unsigned long long m = pass ? small : big;
+        for (uint32_t col = 0; col < (uint32_t)SFP_SERIAL_COLOUR; ++col) {
+            if (!((m >> col) & 1ull)) continue;
+            const uint32_t items = (joff[col + 1] - joff[col]) + (poff[col + 1] - poff[col]);
+            fo->colour[n] = (uint8_t)col;
+            fo->before[n] = acc;
+            fo->run_base[n] = runs;
+            runs += (items + 31u) / 32u;
+            acc |= 1ull << col;
+            ++n;
+        }
+    }
+    fo->run_base[n] = runs;
+    fo->n = n;
+}
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ f4 ldcg4(const float4* p, uint32_t i) {
+    float4 v = __ldcg(p + i);
+    f4 r;
+    r.x = v.x, r.y = v.y, r.z = v.z, r.w = v.w;
+    return r;
+}
+
+#ifndef SFP_FLOW_SLEEP
+#define SFP_FLOW_SLEEP 40
+#endif
+#ifndef SFP_FLOW_SPIN_LIMIT
+#define SFP_FLOW_SPIN_LIMIT (1u << 21)
+#endif
+// wait until slot_a holds need_a and slot_b holds need_b
+__device__ __forceinline__ void flow_wait(const Ctx& c, const unsigned long long* slot_a,
+                                          unsigned long long need_a,
+                                          const unsigned long long* slot_b,
+                                          unsigned long long need_b) {
+    if ((need_a | need_b) == 0ull) return;  // the bodies were last written before a grid barrier
+    uint32_t spins = 0;
+    for (;;) {
+        const unsigned long long da = need_a ? ld_relaxed_u64(slot_a) : 0ull;
+        const unsigned long long db = need_b ? ld_relaxed_u64(slot_b) : 0ull;
+        if ((da & need_a) == need_a && (db & need_b) == need_b) break;
+#if SFP_FLOW_SLEEP > 0
+        __nanosleep(SFP_FLOW_SLEEP);
+#endif
+        ++spins;
+        if ((spins & 1023u) == 0u &&
+            (spins >= SFP_FLOW_SPIN_LIMIT ||
+             (*reinterpret_cast<volatile uint32_t*>(&c.cnt->overflow) & 32u))) {
+            atomicOr(&c.cnt->overflow, 32u);
+            break;
+        }
+    }
+#ifndef SFP_FLOW_NOACQ
+    fence_acq_rel_gpu();
+#endif
+}
+
+__device__ __forceinline__ sfp::BodyPos load_pos_cg(const Ctx& c, uint32_t i) {
+    f4 pose = ldcg4(c.pose, i), prev = ldcg4(c.prev, i);
+    f2 mi = ld2(c.minv, i);
+    sfp::BodyPos b;
+    b.x = sfp::mk(pose.x, pose.y);
+    b.q = sfp::mk(pose.z, pose.w);
+    b.d = sfp::mk(prev.x, prev.y);
+    b.qp = sfp::mk(prev.z, prev.w);
+    b.im = mi.x;
+    b.ii = mi.y;
+    return b;
+}
+
+// one pass over all proper colours; gwarp / nwarps: this warp's index and the warp count of the grid
+__device__ __forceinline__ void flow_solve_pos(const Ctx& c, const FlowOrder& fo,
+                                               const uint32_t* joff, const uint32_t* poff,
+                                               float inv_h2, uint32_t gwarp, uint32_t nwarps,
+                                               uint32_t lane) {
+    uint32_t oi = 0;
+    const uint32_t total = fo.run_base[fo.n];
+    for (uint32_t r = gwarp; r < total; r += nwarps) {
+        while (r >= fo.run_base[oi + 1]) ++oi;
+        const uint32_t col = fo.colour[oi];
+        const unsigned long long before = fo.before[oi], bit = 1ull << col;
+        const uint32_t t = (r - fo.run_base[oi]) * 32u + lane;
+        const uint32_t j0 = joff[col], nj = joff[col + 1] - j0;
+        const uint32_t p0 = poff[col], np = poff[col + 1] - p0;
+#ifdef SFP_FLOW_PROBE
+        // development probe (scripts/flow_probe.py): per run, cycles before the wait (record
+        // loads), in the wait, in gather + solve + store, in the release; lane 0 reads the clock
+        // with the warp converged, so the readings bracket the slowest lane
+        long long pt[5];
+        __syncwarp();
+        pt[0] = pt[1] = pt[2] = pt[3] = pt[4] = clock64();
+#define FLOW_PROBE_AT(i) \
+    do {                 \
+        pt[i] = clock64(); \
+    } while (0)
+#else
+#define FLOW_PROBE_AT(i) \
+    do {                 \
+    } while (0)
+#endif
+        if (t < nj) {
+            const uint32_t k = j0 + t;
+            const uint2 jb = c.jbod[k];
+            const float4 an = c.janc[k], pr = c.jpar[k];
+            // (a body's mask holds this joint's colour iff the body is dynamic)
+            const unsigned long long ma = c.mask[jb.x], mb = c.mask[jb.y];
+            flow_wait(c, &c.done[2u * jb.x], ma & before, &c.done[2u * jb.y], mb & before);
+            sfp::BodyPos A = load_pos_cg(c, jb.x), B = load_pos_cg(c, jb.y);
+            sfp::solve_joint(&A, &B, sfp::mk(an.x, an.y), sfp::mk(an.z, an.w), pr.x, pr.y,
+                             sfp::f2u(pr.z), inv_h2);
+            store_pos(c, jb.x, A);
+            store_pos(c, jb.y, B);
+            fence_acq_rel_gpu();
+            // joints have no velocity pass: done there as well
+            if (ma & bit) {
+                red_or_u64(&c.done[2u * jb.x], bit);
+                red_or_u64(&c.done[2u * jb.x + 1u], bit);
+            }
+            if (mb & bit) {
+                red_or_u64(&c.done[2u * jb.y], bit);
+                red_or_u64(&c.done[2u * jb.y + 1u], bit);
+            }
+        } else if (t - nj < np) {
+            const uint32_t k = p0 + (t - nj);
+            const f4 cb = ld4(c.cb, k);
+            const uint32_t cnt = sfp::f2u(cb.y);
+            if (cnt == 0u) {
+                // (reported done by the narrowphase)
+                c.lam[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            } else {
+                const uint2 p = c.pairs[k];
+                const f4 ca = ld4(c.ca, k), q0 = ld4(c.cp0, k), q1 = ld4(c.cp1, k);
+                const unsigned long long ma = c.mask[p.x], mb = c.mask[p.y];
+                FLOW_PROBE_AT(1);
+                flow_wait(c, &c.done[2u * p.x], ma & before, &c.done[2u * p.y], mb & before);
+                FLOW_PROBE_AT(2);
+                sfp::BodyPos A = load_pos_cg(c, p.x), B = load_pos_cg(c, p.y);
+                const f4 lam = sfp::solve_contact_manifold(
+                    &A, &B, sfp::mk(ca.x, ca.y), cnt, sfp::mk(q0.x, q0.y), sfp::mk(q0.z, q0.w),
+                    sfp::mk(q1.x, q1.y), sfp::mk(q1.z, q1.w), ca.z);
+                store_pos(c, p.x, A);
+                store_pos(c, p.y, B);
+                st4(c.lam, k, lam);
+                FLOW_PROBE_AT(3);
+                fence_acq_rel_gpu();
+                // a manifold that carried no normal impulse is a no-op in the velocity pass
+                const bool vel_too = !(lam.x > 0.0f || lam.z > 0.0f);
+                if (ma & bit) {
+                    red_or_u64(&c.done[2u * p.x], bit);
+                    if (vel_too) red_or_u64(&c.done[2u * p.x + 1u], bit);
+                }
+                if (mb & bit) {
+                    red_or_u64(&c.done[2u * p.y], bit);
+                    if (vel_too) red_or_u64(&c.done[2u * p.y + 1u], bit);
+                }
+                FLOW_PROBE_AT(4);
+            }
+        }
+#ifdef SFP_FLOW_PROBE
+        {
+            // per lane: the four segments of its own path; reduced to the warp's maxima
+            uint32_t seg[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                long long d = pt[i + 1] - pt[i];
+                uint32_t v = d > 0 ? (uint32_t)d : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+                seg[i] = v;
+            }
+            __syncwarp();
+            const long long tend = clock64();
+            if (lane == 0 && (gwarp & 31u) == 0u) {  // a sample of the warps: the counters are shared
+                uint32_t* f = c.cnt->round_flags;
+                for (int i = 0; i < 4; ++i) {
+                    atomicAdd(&f[480 + i], seg[i] >> 4);
+                    atomicMax(&f[484 + i], seg[i]);
+                }
+                atomicAdd(&f[488], 1u);
+                atomicAdd(&f[489], (uint32_t)((tend - pt[0]) >> 4));
+                atomicAdd(&f[oi], seg[1] >> 4);        // wait per colour of the order
+                atomicAdd(&f[64 + oi], 1u);            // runs per colour
+                atomicAdd(&f[128 + oi], (uint32_t)((tend - pt[0]) >> 4));
+            }
+        }
+#endif
+    }
+#undef FLOW_PROBE_AT
+}
+
+__device__ __forceinline__ void flow_solve_vel(const Ctx& c, const FlowOrder& fo,
+                                               const uint32_t* joff, const uint32_t* poff, float h,
+                                               float rest_threshold, uint32_t gwarp,
+                                               uint32_t nwarps, uint32_t lane) {
+    uint32_t oi = 0;
+    const uint32_t total = fo.run_base[fo.n];
+    for (uint32_t r = gwarp; r < total; r += nwarps) {
+        while (r >= fo.run_base[oi + 1]) ++oi;
+        const uint32_t col = fo.colour[oi];
+        const unsigned long long before = fo.before[oi], bit = 1ull << col;
+        const uint32_t t = (r - fo.run_base[oi]) * 32u + lane;
+        const uint32_t nj = joff[col + 1] - joff[col];
+        const uint32_t p0 = poff[col], np = poff[col + 1] - p0;
+        if (t < nj || t - nj >= np) continue;
+        const uint32_t k = p0 + (t - nj);
+        const f4 lam = ld4(c.lam, k);
+        if (!(lam.x > 0.0f || lam.z > 0.0f)) continue;  // reported done by the position pass
+        const PairRec r_ = load_pair_rec(c, k);
+        const uint32_t a = r_.p.x, b = r_.p.y;
+        const unsigned long long ma = c.mask[a], mb = c.mask[b];
+        flow_wait(c, &c.done[2u * a + 1u], ma & before, &c.done[2u * b + 1u], mb & before);
+        const uint32_t cnt = sfp::f2u(r_.cb.y);
+        f4 va = ldcg4(c.vel, a), vb = ldcg4(c.vel, b);
+        f4 pa = ld4(c.pose, a), pb = ld4(c.pose, b);
+        f2 mia = ld2(c.minv, a), mib = ld2(c.minv, b);
+        sfp::BodyVel A, B;
+        A.v = sfp::mk(va.x, va.y);
+        A.w = va.z;
+        A.im = mia.x;
+        A.ii = mia.y;
+        B.v = sfp::mk(vb.x, vb.y);
+        B.w = vb.z;
+        B.im = mib.x;
+        B.ii = mib.y;
+        sfp::solve_manifold_velocity(&A, &B, sfp::mk(pa.z, pa.w), sfp::mk(pb.z, pb.w),
+                                     sfp::mk(r_.ca.x, r_.ca.y), cnt, sfp::mk(r_.q0.x, r_.q0.y),
+                                     sfp::mk(r_.q0.z, r_.q0.w), sfp::mk(r_.q1.x, r_.q1.y),
+                                     sfp::mk(r_.q1.z, r_.q1.w), lam, r_.cb.z, r_.cb.w, r_.ca.z,
+                                     r_.ca.w, r_.cb.x, h, rest_threshold);
+        if (mia.x > 0.0f || mia.y > 0.0f) c.vel[a] = make_float4(A.v.x, A.v.y, A.w, 0.0f);
+        if (mib.x > 0.0f || mib.y > 0.0f) c.vel[b] = make_float4(B.v.x, B.v.y, B.w, 0.0f);
+        fence_acq_rel_gpu();
+        if (ma & bit) red_or_u64(&c.done[2u * a + 1u], bit);
+        if (mb & bit) red_or_u64(&c.done[2u * b + 1u], bit);
+    }
 }
 
 __device__ __forceinline__ void serial_solve_pos(const Ctx& c, uint32_t ncol, float inv_h2) {

@@ -528,6 +528,79 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
     }
 }
 
+// Experiment kept behind SFP_FLAG_FLOW_SOLVE (same bits as k_substeps_coop, slower — see
+// profiles/r2_flow_experiment.md): each solver pass is ONE grid-wide phase in which constraints
+// wait for their own two bodies only (sfp_device.cuh, "Dataflow solve").  Grid barriers per
+// substep: 5 (integrate | narrowphase | position pass | derive | velocity pass) instead of
+// 3 + 2 x (big colours + 1).
+template <bool POLYS>
+__global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS)
+    k_substeps_flow(Ctx c, float h, uint32_t substeps, float rest_threshold) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t tid = gtid(), nth = gnth();
+    const uint32_t lane = threadIdx.x & 31u;
+    // consecutive runs go to different SMs
+    const uint32_t gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t ncol = vload(&c.cnt->n_colours);
+    const bool serial = ncol > SFP_SERIAL_COLOUR;
+    const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    if (serial && blockIdx.x == 0) serial_sort_pairs(c, ncol);
+    __shared__ uint32_t s_poff[SFP_MAX_COLOURS + 1], s_joff[SFP_MAX_COLOURS + 1];
+    __shared__ FlowOrder s_fo;
+    for (uint32_t i = threadIdx.x; i <= (uint32_t)SFP_MAX_COLOURS; i += blockDim.x) {
+        s_poff[i] = c.cnt->pair_col_off[i];
+        s_joff[i] = c.cnt->joint_col_off[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) flow_build_order(c, ncol, s_joff, s_poff, &s_fo);
+    __syncthreads();
+#ifdef SFP_FLOW_PROBE
+    for (uint32_t i = tid; i < 512u; i += nth) c.cnt->round_flags[i] = 0u;
+    grid.sync();
+#endif
+
+    unsigned long long t_prev = 0, acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    auto lap = [&](int slot) {
+        if (tid == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (slot >= 0) acc[slot] += t - t_prev;
+            t_prev = t;
+        }
+    };
+    lap(-1);
+    for (uint32_t s = 0; s < substeps; ++s) {
+        stage_integrate(c, h, tid, nth);
+        grid.sync();
+        lap(4);
+        stage_narrowphase<POLYS, true>(c, tid, nth);
+        grid.sync();
+        lap(5);
+        flow_solve_pos(c, s_fo, s_joff, s_poff, inv_h2, gwarp, nwarps, lane);
+        if (serial) {
+            grid.sync();
+            if (tid == 0) serial_solve_pos(c, ncol, inv_h2);
+        }
+        grid.sync();
+        lap(6);
+        stage_derive(c, inv_h, tid, nth);
+        grid.sync();
+        lap(7);
+        flow_solve_vel(c, s_fo, s_joff, s_poff, h, rest_threshold, gwarp, nwarps, lane);
+        if (serial) {
+            grid.sync();
+            if (tid == 0) serial_solve_vel(c, ncol, h, rest_threshold);
+        }
+        grid.sync();
+        lap(8);
+    }
+    if (tid == 0) {
+        for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
+        c.cnt->stage_cycles[0] = (unsigned long long)s_fo.n;
+    }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
@@ -584,6 +657,7 @@ struct SfpWorld {
     sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
     uint32_t pin_cap = 0;
     int coop_max_colour = 0, coop_max_substep = 0, coop_max_substep_poly = 0, n_sm = 0;
+    int coop_max_flow = 0, coop_max_flow_poly = 0;
     bool has_polygons = false;
     SfpStats stats;
     std::string err;
@@ -640,6 +714,7 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.mask, cb, bag));
     TRY(alloc_dev(w, &c.claim0, cb, bag));
     TRY(alloc_dev(w, &c.claim1, cb, bag));
+    TRY(alloc_dev(w, &c.done, 2 * (size_t)cb, bag));
     TRY(alloc_dev(w, &c.ekey0, ce, bag));
     TRY(alloc_dev(w, &c.eval0, ce, bag));
     TRY(alloc_dev(w, &c.ekey1, ce, bag));
@@ -816,6 +891,16 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
     const bool multi = (w->p.flags & SFP_FLAG_MULTI_KERNEL) != 0u;
     const float g = sqrtf(w->p.gravity_x * w->p.gravity_x + w->p.gravity_y * w->p.gravity_y);
     float rest_threshold = 2.0f * g * h;
+    if (!multi && (w->p.flags & SFP_FLAG_FLOW_SOLVE)) {
+        const uint32_t want = (uint32_t)((4ull * w->n + w->nj + SFP_SUB_TPB - 1) / SFP_SUB_TPB) + 1u;
+        void* args[] = {&c, &h, &substeps, &rest_threshold};
+        w->launches += 1;
+        if (w->has_polygons)
+            return launch_coop(w, (const void*)k_substeps_flow<true>,
+                               std::min<uint32_t>(want, (uint32_t)w->coop_max_flow_poly), args, SFP_SUB_TPB);
+        return launch_coop(w, (const void*)k_substeps_flow<false>,
+                           std::min<uint32_t>(want, (uint32_t)w->coop_max_flow), args, SFP_SUB_TPB);
+    }
     if (!multi) {
         uint32_t blocks = std::min<uint32_t>(
             (uint32_t)w->coop_max_substep,
@@ -1013,6 +1098,14 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
         cudaSuccess)
         return fail("occupancy(substeps, polygons)", e);
     w->coop_max_substep_poly = std::max(1, per_sm) * w->n_sm;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_flow<false>, SFP_SUB_TPB, 0)) !=
+        cudaSuccess)
+        return fail("occupancy(flow)", e);
+    w->coop_max_flow = std::max(1, per_sm) * w->n_sm;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_flow<true>, SFP_SUB_TPB, 0)) !=
+        cudaSuccess)
+        return fail("occupancy(flow, polygons)", e);
+    w->coop_max_flow_poly = std::max(1, per_sm) * w->n_sm;
     w->ctx.gx = p.gravity_x;
     w->ctx.gy = p.gravity_y;
     w->ctx.inv_cell = 1.0f / p.cell_size;
