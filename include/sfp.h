@@ -89,6 +89,8 @@ enum {
     SFP_FLAG_BROADPHASE_EVERY_SUBSTEP = 1u, /* default: once per frame     */
     SFP_FLAG_MULTI_KERNEL = 2u,             /* CUDA: one launch per stage instead of the
                                                persistent cooperative substep kernel (debug) */
+    SFP_FLAG_TILES = 8u,                    /* solve order: tile-interior constraints first,
+                                               then the boundary ones (sfp_math.h, "Tiles")  */
     SFP_FLAG_FLOW_SOLVE = 4u                /* CUDA: per-body dependency masks instead of a
                                                grid-wide barrier after every colour (same
                                                results, measured slower; an experiment)      */

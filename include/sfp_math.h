@@ -1389,6 +1389,61 @@ SFP_HD uint64_t ctab_pack(uint32_t a, uint32_t b, uint32_t colour) {
 }
 SFP_HD uint32_t ctab_hash(uint32_t a, uint32_t b) { return hash32(a * 0x9e3779b9u ^ hash32(b + 0x7f4a7c15u)); }
 
+/* ------------------------------------------------------------------------------------- */
+/* Tiles (solve order) — integer only                                                    */
+/* ------------------------------------------------------------------------------------- */
+/* The dynamic bodies of a world are cut into TILES: spatially compact groups of SFP_TILE_MIN ..
+ * SFP_TILE_MAX bodies (consecutive runs of the bodies sorted by the Morton code of their
+ * broadphase cell, ties by body index).  A constraint whose dynamic bodies all lie in one tile
+ * is INTERIOR to it, every other one is a BOUNDARY constraint (static bodies belong to no tile
+ * and never make a constraint a boundary one).  The two classes are coloured in separate
+ * colour namespaces (a body has one colour mask per class), and a solver pass runs
+ *     the interior constraints, colour 0, 1, 2, ... (tiles are independent of each other),
+ *     then the boundary constraints: colours with more than SFP_TAIL_ITEMS of them ascending,
+ *          then the smaller ones ascending,
+ *     then the serial group.
+ * Why: on the device one thread block keeps a tile's bodies in shared memory and runs all its
+ * interior colours between block-wide barriers; only the boundary constraints (a few per cent)
+ * need grid-wide phases.  The assignment is renewed whenever the colouring starts from scratch
+ * (every SFP_RECOLOUR_PERIOD-th colouring), from the poses at that moment, and is part of the
+ * algorithm's definition: the oracle computes the same tiles.  SFP_FLAG_NO_TILES turns every
+ * constraint into a boundary constraint (the plain global colour order). */
+#define SFP_TILE_TARGET 148u /* tiles aimed for: one per SM of a B200 */
+#define SFP_TILE_MIN 256u
+#define SFP_TILE_MAX 1024u
+#define SFP_NO_TILE 0xffffffffu
+#define SFP_CLASS_INTERIOR 64u /* get_colours reports an interior constraint's colour + 64 */
+
+SFP_HD uint32_t tile_size(uint32_t n_dynamic) {
+    uint32_t b = (n_dynamic + SFP_TILE_TARGET - 1u) / SFP_TILE_TARGET;
+    if (b < SFP_TILE_MIN) b = SFP_TILE_MIN;
+    if (b > SFP_TILE_MAX) b = SFP_TILE_MAX;
+    return b;
+}
+SFP_HD uint32_t morton_spread16(uint32_t v) {
+    v &= 0xffffu;
+    v = (v | (v << 8)) & 0x00ff00ffu;
+    v = (v | (v << 4)) & 0x0f0f0f0fu;
+    v = (v | (v << 2)) & 0x33333333u;
+    v = (v | (v << 1)) & 0x55555555u;
+    return v;
+}
+/* sort key of a body for the tile order: 31 bits of the Morton code of its cell (the lowest x
+ * bit dropped), statics behind every dynamic body */
+SFP_HD uint32_t tile_sort_key(float x, float y, float inv_cell, bool dynamic) {
+    if (!dynamic) return 0x80000000u;
+    uint32_t cx = (uint32_t)(cell_coord(x, inv_cell) - SFP_CELL_MIN);
+    uint32_t cy = (uint32_t)(cell_coord(y, inv_cell) - SFP_CELL_MIN);
+    return (morton_spread16(cx) | (morton_spread16(cy) << 1)) >> 1;
+}
+/* class of a constraint between bodies with tiles ta, tb (SFP_NO_TILE for a static body):
+ * the tile it is interior to, or SFP_NO_TILE for a boundary constraint */
+SFP_HD uint32_t constraint_tile(uint32_t ta, uint32_t tb) {
+    if (ta == SFP_NO_TILE) return tb;
+    if (tb == SFP_NO_TILE) return ta;
+    return ta == tb ? ta : SFP_NO_TILE;
+}
+
 /* index of the lowest zero bit of a 64-bit mask (64 if none) */
 SFP_HD int lowest_free(uint64_t mask);
 /* colour for a constraint whose dynamic bodies use the colours in `mask` */

@@ -125,8 +125,11 @@ struct SfpWorld {
     PolyTable polys; /* general convex polygons (sfp_ref_set_polygons) */
     /* per frame */
     std::vector<SfpPair> pairs;          /* sorted by (a,b) */
+    /* colour of a constraint as reported by get_colours: a boundary constraint's colour as it is
+     * (0..62), an interior one's + SFP_CLASS_INTERIOR, the serial group's 63 (sfp_math.h, "Tiles") */
     std::vector<uint32_t> pair_colour;   /* aligned with pairs */
     std::vector<uint32_t> joint_colour;  /* aligned with joints */
+    std::vector<uint32_t> tile;          /* per body: its tile, SFP_NO_TILE for statics / tiles off */
     std::vector<ContactRec> contacts;    /* aligned with pairs */
     std::vector<f4> lambdas;             /* aligned with pairs: ln0, lt0, ln1, lt1 */
     uint32_t n_colours = 0, colour_rounds = 0, n_entries = 0;
@@ -238,40 +241,67 @@ int broadphase(SfpWorld& w, float dt) {
     return SFP_OK;
 }
 
+/* tile of every dynamic body (sfp_math.h, "Tiles"): runs of tile_size() bodies in the order of
+ * their Morton cell key, ties by body index.  From the poses at the moment of the call. */
+void compute_tiles(SfpWorld& w) {
+    w.tile.assign(w.n, SFP_NO_TILE);
+    if (!(w.p.flags & SFP_FLAG_TILES)) return;
+    const float inv = 1.0f / w.p.cell_size;
+    std::vector<uint32_t> key(w.n), order(w.n);
+    uint32_t ndyn = 0;
+    for (uint32_t i = 0; i < w.n; ++i) {
+        const bool dyn = is_dynamic(w, i);
+        key[i] = tile_sort_key(w.pose[i].x, w.pose[i].y, inv, dyn);
+        order[i] = i;
+        ndyn += dyn ? 1u : 0u;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return key[a] < key[b]; });
+    const uint32_t B = tile_size(ndyn);
+    for (uint32_t r = 0; r < ndyn; ++r) w.tile[order[r]] = r / B;
+}
+
 /* A8: rounds of "every body grants its lowest-priority-key uncoloured constraint; a
- * constraint granted by all its dynamic bodies takes the lowest colour free on them". */
+ * constraint granted by all its dynamic bodies takes the lowest colour free on them" — free in
+ * the colour namespace of the constraint's class (interior to a tile / boundary). */
 int colour_constraints(SfpWorld& w) {
     const uint32_t P = (uint32_t)w.pairs.size(), J = (uint32_t)w.joints.size();
     const uint32_t UNC = 0xffffffffu;
+    /* warm start: a constraint that existed in the previous frame keeps its colour (those
+     * colours were proper among themselves and still are); the tiles stay as they are */
+    const bool warm = (w.colour_age % SFP_RECOLOUR_PERIOD) != 0u;
+    w.colour_age += 1;
+    if (!warm || w.tile.size() != w.n) compute_tiles(w);
     w.pair_colour.assign(P, UNC);
     w.joint_colour.assign(J, UNC);
-    std::vector<uint64_t> mask(w.n, 0ull), claim(w.n);
+    /* mask[0]: boundary colours in use per body, mask[1]: interior colours */
+    std::vector<uint64_t> mask[2] = {std::vector<uint64_t>(w.n, 0ull), std::vector<uint64_t>(w.n, 0ull)};
+    std::vector<uint64_t> claim(w.n);
     std::vector<uint64_t> pkey(P), jkey(J);
     for (uint32_t k = 0; k < P; ++k) pkey[k] = pair_priority(w.pairs[k].a, w.pairs[k].b);
     for (uint32_t k = 0; k < J; ++k) jkey[k] = joint_priority(k);
-    uint32_t remaining = P + J, rounds = 0, ncol = 0, serial = 0;
+    uint32_t remaining = P + J, rounds = 0, ncol[2] = {0, 0}, serial = 0;
     bool overflow = false;
+    auto interior = [&](uint32_t a, uint32_t b) {
+        return constraint_tile(w.tile[a], w.tile[b]) != SFP_NO_TILE;
+    };
     /* constraints without a dynamic end never conflict: colour 0 */
     for (uint32_t k = 0; k < J; ++k)
         if (!is_dynamic(w, w.joints[k].body_a) && !is_dynamic(w, w.joints[k].body_b)) {
             w.joint_colour[k] = 0;
             --remaining;
-            ncol = std::max(ncol, 1u);
+            ncol[0] = std::max(ncol[0], 1u);
         }
-    /* warm start: a constraint that existed in the previous frame keeps its colour (those
-     * colours were proper among themselves and still are) */
-    const bool warm = (w.colour_age % SFP_RECOLOUR_PERIOD) != 0u;
-    w.colour_age += 1;
     if (warm) {
-        auto keep = [&](uint32_t a, uint32_t b, uint32_t c, uint32_t* colour) {
+        auto keep = [&](uint32_t a, uint32_t b, uint32_t enc, uint32_t* colour) {
+            const uint32_t cls = enc >= SFP_CLASS_INTERIOR ? 1u : 0u, c = enc & 63u;
             if (c != SFP_SERIAL_COLOUR) {
-                if (is_dynamic(w, a)) mask[a] |= 1ull << c;
-                if (is_dynamic(w, b)) mask[b] |= 1ull << c;
+                if (is_dynamic(w, a)) mask[cls][a] |= 1ull << c;
+                if (is_dynamic(w, b)) mask[cls][b] |= 1ull << c;
             } else if (++serial > SFP_SERIAL_MAX) {
                 overflow = true;
             }
-            *colour = c;
-            ncol = std::max(ncol, c + 1u);
+            *colour = enc;
+            ncol[cls] = std::max(ncol[cls], c + 1u);
             --remaining;
         };
         for (uint32_t k = 0; k < P; ++k) {
@@ -308,16 +338,21 @@ int colour_constraints(SfpWorld& w) {
             bool da = is_dynamic(w, a), db = is_dynamic(w, b);
             if (da && claim[a] != key) return;
             if (db && claim[b] != key) return;
-            uint64_t m = (da ? mask[a] : 0ull) | (db ? mask[b] : 0ull);
+            const uint32_t cls = interior(a, b) ? 1u : 0u;
+            uint64_t m = (da ? mask[cls][a] : 0ull) | (db ? mask[cls][b] : 0ull);
             int c = pick_colour(m);
+            uint32_t enc = (uint32_t)c + (cls ? SFP_CLASS_INTERIOR : 0u);
             if (c != SFP_SERIAL_COLOUR) {
-                if (da) mask[a] |= 1ull << c;
-                if (db) mask[b] |= 1ull << c;
-            } else if (++serial > SFP_SERIAL_MAX) {
-                overflow = true;
+                if (da) mask[cls][a] |= 1ull << c;
+                if (db) mask[cls][b] |= 1ull << c;
+                ncol[cls] = std::max(ncol[cls], (uint32_t)c + 1u);
+            } else {
+                /* all 63 colours of the class taken: the serial group (one for both classes) */
+                enc = SFP_SERIAL_COLOUR;
+                ncol[0] = std::max(ncol[0], (uint32_t)SFP_SERIAL_COLOUR + 1u);
+                if (++serial > SFP_SERIAL_MAX) overflow = true;
             }
-            *colour = (uint32_t)c;
-            ncol = std::max(ncol, (uint32_t)c + 1u);
+            *colour = enc;
             --remaining;
         };
         for (uint32_t k = 0; k < P; ++k)
@@ -327,19 +362,19 @@ int colour_constraints(SfpWorld& w) {
             if (w.joint_colour[k] == UNC)
                 try_take(w.joints[k].body_a, w.joints[k].body_b, jkey[k], &w.joint_colour[k]);
     }
-    w.n_colours = ncol;
+    w.n_colours = ncol[0] + ncol[1];
     w.colour_rounds = rounds;
     w.prev_pair_colour.clear();
     w.prev_pair_colour.reserve(P * 2);
     for (uint32_t k = 0; k < P; ++k)
         w.prev_pair_colour[ctab_key(w.pairs[k].a, w.pairs[k].b)] = w.pair_colour[k];
     w.prev_joint_colour = w.joint_colour;
-    w.pairs_of.assign(SFP_MAX_COLOURS, {});
-    w.joints_of.assign(SFP_MAX_COLOURS, {});
+    w.pairs_of.assign(2 * SFP_MAX_COLOURS, {});
+    w.joints_of.assign(2 * SFP_MAX_COLOURS, {});
     for (uint32_t k = 0; k < P; ++k)
-        if (w.pair_colour[k] < SFP_MAX_COLOURS) w.pairs_of[w.pair_colour[k]].push_back(k);
+        if (w.pair_colour[k] < 2 * SFP_MAX_COLOURS) w.pairs_of[w.pair_colour[k]].push_back(k);
     for (uint32_t k = 0; k < (uint32_t)w.joints.size(); ++k)
-        if (w.joint_colour[k] < SFP_MAX_COLOURS) w.joints_of[w.joint_colour[k]].push_back(k);
+        if (w.joint_colour[k] < 2 * SFP_MAX_COLOURS) w.joints_of[w.joint_colour[k]].push_back(k);
     if (overflow) {
         w.stats.overflow |= 4u;
         w.err = "more than SFP_SERIAL_MAX constraints left without a colour";
@@ -459,17 +494,20 @@ void substep(SfpWorld& w, float h) {
     w.stats.n_contacts = npts;
     w.stats.n_manifolds = nman;
     w.stats.max_penetration = maxpen;
-    /* colour order: big colours first, then the small ones (see SFP_TAIL_ITEMS) */
+    /* solve order (sfp_math.h, "Tiles"): interior colours ascending; boundary colours with more
+     * than SFP_TAIL_ITEMS constraints ascending, then the smaller ones; the serial group last */
     std::vector<uint32_t> order;
     if (w.p.solver_order != SFP_ORDER_REFERENCE) {
-        std::vector<uint32_t> items(w.n_colours, 0);
-        for (uint32_t k = 0; k < P; ++k) items[w.pair_colour[k]] += 1;
-        for (uint32_t k = 0; k < J; ++k) items[w.joint_colour[k]] += 1;
-        for (uint32_t c = 0; c < w.n_colours; ++c)
-            if (c != SFP_SERIAL_COLOUR && items[c] > SFP_TAIL_ITEMS) order.push_back(c);
-        for (uint32_t c = 0; c < w.n_colours; ++c)
-            if (c != SFP_SERIAL_COLOUR && items[c] <= SFP_TAIL_ITEMS) order.push_back(c);
-        if (w.n_colours > SFP_SERIAL_COLOUR) order.push_back(SFP_SERIAL_COLOUR); /* serial, last */
+        for (uint32_t c = 0; c < SFP_SERIAL_COLOUR; ++c)
+            if (!w.pairs_of[SFP_CLASS_INTERIOR + c].empty() || !w.joints_of[SFP_CLASS_INTERIOR + c].empty())
+                order.push_back(SFP_CLASS_INTERIOR + c);
+        for (int pass = 0; pass < 2; ++pass)
+            for (uint32_t c = 0; c < SFP_SERIAL_COLOUR; ++c) {
+                const size_t items = w.pairs_of[c].size() + w.joints_of[c].size();
+                if (items > 0 && (items > SFP_TAIL_ITEMS) == (pass == 0)) order.push_back(c);
+            }
+        if (!w.pairs_of[SFP_SERIAL_COLOUR].empty() || !w.joints_of[SFP_SERIAL_COLOUR].empty())
+            order.push_back(SFP_SERIAL_COLOUR);
     }
     /* A5 + A6 */
     if (w.p.solver_order == SFP_ORDER_REFERENCE) {
@@ -594,6 +632,7 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
     w->pair_colour.clear();
     w->prev_pair_colour.clear();
     w->prev_joint_colour.clear();
+    w->tile.clear();
     w->colour_age = 0;
     w->stepped = false;
     return SFP_OK;

@@ -50,6 +50,12 @@ struct Ctx {
     const float4 *shape, *mat;
     const float2* minv;
     const float4* polytab;  // general-polygon table, 8 float4 per polygon (sfp_math.h), or null
+    // The single-world path keeps its bodies in a spatial order of its own (sfp_world.cu,
+    // "re-sort"): ext[i] is the caller's index (upload order) of the body stored at i, inv the
+    // inverse.  Everything whose RESULT depends on body numbering — which body of a pair is "a",
+    // constraint priorities, the order inside the serial group, ties — uses the caller's index,
+    // so the results do not depend on the internal order.  Null (batched worlds): identity.
+    const uint32_t *ext, *inv;
     // broadphase
     float4* aabb;
     int4* meta;  // cx0, cy0, layer bits, dynamic flag
@@ -104,6 +110,8 @@ __device__ __forceinline__ f2 ld2(const float2* p, uint32_t i) {
     r.y = v.y;
     return r;
 }
+
+__device__ __forceinline__ uint32_t ext_id(const Ctx& c, uint32_t i) { return c.ext ? c.ext[i] : i; }
 
 // ---------------------------------------------------------------------------------------
 // A2 broadphase
@@ -268,8 +276,11 @@ __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
             for (int j = 0; j < 4; ++j) {
                 if (same[j] && pair_test(cx, cy, a, bba, ma, bf[j], mb[j], bbb[j])) {
                     if (WRITE) {
-                        if (o + k < c.cap_pairs)
-                            c.pairs_raw[o + k] = make_uint2(min(a, bf[j]), max(a, bf[j]));
+                        if (o + k < c.cap_pairs) {
+                            // "a" is the body with the lower index in the caller's numbering
+                            const bool fwd = ext_id(c, a) < ext_id(c, bf[j]);
+                            c.pairs_raw[o + k] = fwd ? make_uint2(a, bf[j]) : make_uint2(bf[j], a);
+                        }
                     }
                     ++k;
                 }
@@ -423,7 +434,8 @@ __device__ __forceinline__ void serial_sort_pairs(const Ctx& c, uint32_t ncol) {
     for (uint32_t round = 0; round < m; ++round) {
         for (uint32_t i = 2u * threadIdx.x + (round & 1u); i + 1u < m; i += 2u * blockDim.x) {
             uint2 x = c.pairs[first + i], y = c.pairs[first + i + 1u];
-            if (x.x > y.x || (x.x == y.x && x.y > y.y)) {
+            const uint32_t xa = ext_id(c, x.x), xb = ext_id(c, x.y), ya = ext_id(c, y.x), yb = ext_id(c, y.y);
+            if (xa > ya || (xa == ya && xb > yb)) {
                 c.pairs[first + i] = y;
                 c.pairs[first + i + 1u] = x;
             }
@@ -446,7 +458,7 @@ __device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, u
         const uint32_t k = c.unc ? c.unc[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
-            colour_bid_one(c, claim, p.x, p.y, sfp::pair_priority(p.x, p.y));
+            colour_bid_one(c, claim, p.x, p.y, sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)));
         }
     }
     for (uint32_t k = tid; k < c.nj; k += nth)
@@ -489,7 +501,7 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
             uint32_t col = colour_take_one(c, claim, next_claim, p.x, p.y,
-                                           sfp::pair_priority(p.x, p.y), round);
+                                           sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)), round);
             // sort key: colour in the high bits, narrowphase class in the low ones (coherence
             // inside a colour bucket)
             if (col != UNCOLOURED) col = pair_sort_key(c, col, p);

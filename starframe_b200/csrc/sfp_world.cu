@@ -86,6 +86,61 @@ __global__ void k_serial_vel(Ctx c, float h, float rt) {
     if (threadIdx.x == 0 && blockIdx.x == 0) serial_solve_vel(c, vload(&c.cnt->n_colours), h, rt);
 }
 
+// ---- re-sort: bodies kept in the order of their Morton cell key (statics last) -----------------
+// Bodies that touch are then neighbours in memory — the solver's 16-byte gathers land in shared
+// sectors whatever order the scene graph uploaded them in — and a tile of the solve order
+// (sfp_math.h, "Tiles") is a contiguous index range.  Runs when the colouring starts from scratch
+// (every SFP_RECOLOUR_PERIOD-th frame): the colour table, keyed by internal indices, is not read
+// in such a frame.  Scratch: the broadphase entry buffers for the sort, the contact record arrays
+// (dead between frames) for the permuted copies.
+__global__ void __launch_bounds__(TPB) k_tile_keys(Ctx c, uint32_t* __restrict__ keys) {
+    for (uint32_t i = gtid(); i < c.n; i += gnth()) {
+        const float4 p = c.pose[i];
+        const float2 m = c.minv[i];
+        keys[i] = sfp::tile_sort_key(p.x, p.y, c.inv_cell, m.x > 0.0f || m.y > 0.0f);
+    }
+}
+__global__ void __launch_bounds__(TPB) k_permute_gather(Ctx c, const uint32_t* __restrict__ src) {
+    for (uint32_t j = gtid(); j < c.n; j += gnth()) {
+        const uint32_t i = src[j];
+        c.ca[j] = c.pose[i];
+        c.cb[j] = c.prev[i];
+        c.cp0[j] = c.vel[i];
+        c.cp1[j] = c.shape[i];
+        c.cs[j] = c.mat[i];
+        const float2 m = c.minv[i];
+        c.lam[j] = make_float4(m.x, m.y, __uint_as_float(c.ext[i]), 0.0f);
+    }
+}
+__global__ void __launch_bounds__(TPB) k_permute_store(Ctx c, uint32_t* __restrict__ ext,
+                                                       uint32_t* __restrict__ inv) {
+    for (uint32_t j = gtid(); j < c.n; j += gnth()) {
+        c.pose[j] = c.ca[j];
+        c.prev[j] = c.cb[j];
+        c.vel[j] = c.cp0[j];
+        const_cast<float4*>(c.shape)[j] = c.cp1[j];
+        const_cast<float4*>(c.mat)[j] = c.cs[j];
+        const float4 m = c.lam[j];
+        const_cast<float2*>(c.minv)[j] = make_float2(m.x, m.y);
+        const uint32_t e = __float_as_uint(m.z);
+        ext[j] = e;
+        inv[e] = j;
+    }
+}
+__global__ void __launch_bounds__(TPB) k_remap_joints(Ctx c, const uint2* __restrict__ jext) {
+    for (uint32_t k = gtid(); k < c.nj; k += gnth()) {
+        const uint2 j = jext[k];
+        const_cast<uint2*>(c.jbod_in)[k] = make_uint2(c.inv[j.x], c.inv[j.y]);
+    }
+}
+__global__ void __launch_bounds__(TPB) k_identity(uint32_t* __restrict__ a, uint32_t* __restrict__ b,
+                                                  uint32_t n) {
+    for (uint32_t i = gtid(); i < n; i += gnth()) {
+        a[i] = i;
+        b[i] = i;
+    }
+}
+
 // ---- spatial queries on the device hash --------------------------------------------------------
 __global__ void __launch_bounds__(TPB) k_query_aabbs(Ctx c) {
     stage_aabb_count(c, 0.0f, gtid(), gnth(), false);  // current poses, no sweep
@@ -129,8 +184,9 @@ __global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __re
                 if (!sfp::ray_collider(o, d, r.max_t, ld4(c.pose, b), ld4(c.shape, b),
                                        reinterpret_cast<const sfp::f4*>(c.polytab), &t, &n))
                     continue;
-                if (best_body == 0xffffffffu || t < best_t || (t == best_t && b < best_body)) {
-                    best_body = b;
+                const uint32_t be = ext_id(c, b);
+                if (best_body == 0xffffffffu || t < best_t || (t == best_t && be < best_body)) {
+                    best_body = be;
                     best_t = t;
                     best_n = n;
                 }
@@ -156,10 +212,11 @@ __global__ void __launch_bounds__(TPB) k_box_flags(Ctx c, float4 box, uint32_t m
                                                    uint32_t* __restrict__ flags) {
     f4 bx;
     bx.x = box.x, bx.y = box.y, bx.z = box.z, bx.w = box.w;
-    for (uint32_t i = gtid(); i < c.n; i += gnth()) {
+    for (uint32_t e = gtid(); e < c.n; e += gnth()) {  // e: the caller's index
+        const uint32_t i = c.inv[e];
         bool in = (((sfp::f2u(c.mat[i].w) & 0xffffu) & mask) != 0u) &&
                   sfp::aabb_overlap(sfp::tight_aabb(ld4(c.pose, i), ld4(c.shape, i)), bx);
-        flags[i] = in ? 1u : 0u;
+        flags[e] = in ? 1u : 0u;
     }
 }
 __global__ void __launch_bounds__(TPB) k_box_write(Ctx c, const uint32_t* __restrict__ off,
@@ -184,8 +241,9 @@ __global__ void __launch_bounds__(TPB) k_event_write(Ctx c, const uint32_t* __re
         if (off[k + 1] == off[k]) continue;
         uint2 p = c.pairs[k];
         sfp::EventRec e;
-        if (sfp::pair_event(p.x, p.y, ld4(c.ca, k), ld4(c.cb, k), ld4(c.cp0, k), ld4(c.cp1, k),
-                            ld4(c.lam, k), ld4(c.pose, p.x), ld4(c.pose, p.y), inv_h, &e)) {
+        if (sfp::pair_event(ext_id(c, p.x), ext_id(c, p.y), ld4(c.ca, k), ld4(c.cb, k), ld4(c.cp0, k),
+                            ld4(c.cp1, k), ld4(c.lam, k), ld4(c.pose, p.x), ld4(c.pose, p.y), inv_h,
+                            &e)) {
             uint4* o = reinterpret_cast<uint4*>(out + off[k]);
             o[0] = make_uint4(e.a, e.b, __float_as_uint(e.nx), __float_as_uint(e.ny));
             o[1] = make_uint4(__float_as_uint(e.px), __float_as_uint(e.py),
@@ -195,12 +253,13 @@ __global__ void __launch_bounds__(TPB) k_event_write(Ctx c, const uint32_t* __re
 }
 // scatter-update of individual bodies from scene-graph states
 __global__ void __launch_bounds__(TPB) k_update_bodies(const uint32_t* __restrict__ idx,
+                                                       const uint32_t* __restrict__ inv,
                                                        const sfp::StateRec* __restrict__ in,
                                                        const float2* __restrict__ minv,
                                                        float4* __restrict__ pose,
                                                        float4* __restrict__ vel, uint32_t m) {
     for (uint32_t k = gtid(); k < m; k += gnth()) {
-        const uint32_t i = idx[k];
+        const uint32_t i = inv[idx[k]];
         const float4* q = reinterpret_cast<const float4*>(in + k);
         float4 a = q[0], b = q[1];
         sfp::StateRec r;
@@ -213,22 +272,27 @@ __global__ void __launch_bounds__(TPB) k_update_bodies(const uint32_t* __restric
 }
 
 // ---- scene-graph state <-> solver records, on the device (AoS SfpBodyState, 32 B/body) -------
+// (states cross the ABI in the caller's order: e is the caller's index, inv[e] where the body is)
 __global__ void __launch_bounds__(TPB) k_pack_states(const float4* __restrict__ pose,
                                                      const float4* __restrict__ vel,
+                                                     const uint32_t* __restrict__ inv,
                                                      sfp::StateRec* __restrict__ out, uint32_t n) {
-    for (uint32_t i = gtid(); i < n; i += gnth()) {
+    for (uint32_t e = gtid(); e < n; e += gnth()) {
+        const uint32_t i = inv[e];
         sfp::StateRec r = sfp::state_pack(ld4(pose, i), ld4(vel, i));
-        float4* o = reinterpret_cast<float4*>(out + i);
+        float4* o = reinterpret_cast<float4*>(out + e);
         o[0] = make_float4(r.x, r.y, r.c, r.s);
         o[1] = make_float4(r.vx, r.vy, r.omega, r.angle);
     }
 }
 __global__ void __launch_bounds__(TPB) k_unpack_states(const sfp::StateRec* __restrict__ in,
                                                        const float2* __restrict__ minv,
+                                                       const uint32_t* __restrict__ inv,
                                                        float4* __restrict__ pose,
                                                        float4* __restrict__ vel, uint32_t n) {
-    for (uint32_t i = gtid(); i < n; i += gnth()) {
-        const float4* q = reinterpret_cast<const float4*>(in + i);
+    for (uint32_t e = gtid(); e < n; e += gnth()) {
+        const uint32_t i = inv[e];
+        const float4* q = reinterpret_cast<const float4*>(in + e);
         float4 a = q[0], b = q[1];
         sfp::StateRec r;
         r.x = a.x, r.y = a.y, r.c = a.z, r.s = a.w, r.vx = b.x, r.vy = b.y, r.omega = b.z, r.angle = b.w;
@@ -641,6 +705,9 @@ struct SfpWorld {
     uint32_t graph_next = 0;
     bool graphs_ok = true, capturing = false;
     Counters* d_cnt = nullptr;
+    // internal body order (re-sort): internal -> caller's index and back; joints as uploaded
+    uint32_t *d_ext = nullptr, *d_inv = nullptr;
+    uint2* d_jext = nullptr;
     // host mirrors
     sfp::PolyTable polys;
     float4* d_polytab = nullptr;
@@ -737,6 +804,10 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &w->d_evt_off, cp + 1, bag));
     TRY(alloc_dev(w, &w->d_events, cp, bag));
     TRY(alloc_dev(w, &w->d_idx, cb, bag));
+    TRY(alloc_dev(w, &w->d_ext, cb, bag));
+    TRY(alloc_dev(w, &w->d_inv, cb, bag));
+    c.ext = w->d_ext;
+    c.inv = w->d_inv;
     uint32_t slots = 1024;
     while (slots < 2u * cp) slots <<= 1;
     TRY(alloc_dev(w, &w->d_tab[0], slots, bag));
@@ -776,6 +847,7 @@ int ensure_joint_capacity(SfpWorld* w, uint32_t nj) {
     TRY(alloc_dev(w, &c.jcol, cj, bag));
     TRY(alloc_dev(w, &c.jcol_sorted, cj, bag));
     TRY(alloc_dev(w, &c.jperm, cj, bag));
+    TRY(alloc_dev(w, &w->d_jext, cj, bag));
     w->cap_joints = cj;
     // the radix histogram must cover the joint sort too
     if (radix_blocks(cj + 1) > w->hist_blocks) {
@@ -814,11 +886,36 @@ int launch_coop(SfpWorld* w, const void* fn, uint32_t blocks, void** args, uint3
     return SFP_OK;
 }
 
+// bodies into Morton order of their cells, statics last (see the kernels' comment)
+int resort_bodies(SfpWorld* w) {
+    Ctx& c = w->ctx;
+    cudaStream_t st = w->stream;
+    const uint32_t gb = blocks_for(w, w->n);
+    k_tile_keys<<<gb, TPB, 0, st>>>(c, c.ekey1);
+    // four 8-bit passes, 1 -> 0 -> 1 -> 0 -> 1: the sorted order ends in eval1
+    for (int pass = 0; pass < 4; ++pass) {
+        const bool back = (pass & 1) != 0;
+        const uint32_t* ki = back ? c.ekey0 : c.ekey1;
+        const uint32_t* vi = pass == 0 ? nullptr : (back ? c.eval0 : c.eval1);
+        uint32_t* ko = back ? c.ekey1 : c.ekey0;
+        uint32_t* vo = back ? c.eval1 : c.eval0;
+        CU(radix_pass(ki, vi, ko, vo, &w->d_cnt->n_bodies, w->cap_bodies, pass * 8, w->d_hist, st));
+    }
+    k_permute_gather<<<gb, TPB, 0, st>>>(c, c.eval1);
+    k_permute_store<<<gb, TPB, 0, st>>>(c, w->d_ext, w->d_inv);
+    if (w->nj) k_remap_joints<<<blocks_for(w, w->nj), TPB, 0, st>>>(c, w->d_jext);
+    CU(cudaGetLastError());
+    w->launches += 3 + (w->nj ? 1 : 0) + 4 * (radix_blocks(w->cap_bodies) > RADIX_INLINE_BLOCKS ? 3 : 2);
+    return SFP_OK;
+}
+
 int broadphase_and_colour(SfpWorld* w, float dt) {
     Ctx& c = w->ctx;
     cudaStream_t st = w->stream;
     const bool multi = (w->p.flags & SFP_FLAG_MULTI_KERNEL) != 0u;
     const uint32_t gb = blocks_for(w, w->n);
+    // the frames whose colouring starts from scratch also renew the body order
+    if ((w->colour_age % SFP_RECOLOUR_PERIOD) == 0u) TRY(resort_bodies(w));
     const bool mark = !(w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP);
     k_aabb_count<<<gb, TPB, 0, st>>>(c, dt);
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
@@ -1186,6 +1283,9 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     }
     w->n = n;
     c.n = n;
+    if (n) k_identity<<<blocks_for(w, n), TPB, 0, st>>>(w->d_ext, w->d_inv, n);
+    if (w->nj) k_remap_joints<<<blocks_for(w, w->nj), TPB, 0, st>>>(c, w->d_jext);
+    CU(cudaGetLastError());
     Counters zero;
     std::memset(&zero, 0, sizeof(zero));
     zero.n_bodies = n;
@@ -1245,8 +1345,7 @@ int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
     cudaStream_t st = w->stream;
     CU(cudaStreamSynchronize(st));
     if (nj) {
-        CU(cudaMemcpyAsync(const_cast<uint2*>(c.jbod_in), jb.data(), sizeof(uint2) * nj,
-                           cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(w->d_jext, jb.data(), sizeof(uint2) * nj, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(const_cast<float4*>(c.janc_in), ja.data(), sizeof(float4) * nj,
                            cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(const_cast<float4*>(c.jpar_in), jp.data(), sizeof(float4) * nj,
@@ -1254,6 +1353,10 @@ int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
     }
     w->nj = nj;
     c.nj = nj;
+    if (nj) {
+        k_remap_joints<<<blocks_for(w, nj), TPB, 0, st>>>(c, w->d_jext);
+        CU(cudaGetLastError());
+    }
     CU(cudaMemcpyAsync(&w->d_cnt->n_joints, &nj, sizeof(nj), cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));
     w->stats.n_joints = nj;
@@ -1318,7 +1421,7 @@ int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
     const bool direct = n && host_pinned(out);
     if (n) {
         // states are packed on the device (incl. the angle), one D2H copy, no per-body host work
-        k_pack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->ctx.pose, w->ctx.vel, w->d_state, n);
+        k_pack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->ctx.pose, w->ctx.vel, w->d_inv, w->d_state, n);
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(direct ? out : w->pin_state, w->d_state, sizeof(SfpBodyState) * n,
                            cudaMemcpyDeviceToHost, w->stream));
@@ -1345,8 +1448,8 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
     }
     CU(cudaMemcpyAsync(w->d_state, src, sizeof(SfpBodyState) * n, cudaMemcpyHostToDevice,
                        w->stream));
-    k_unpack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->d_state, w->ctx.minv, w->ctx.pose,
-                                                            w->ctx.vel, n);
+    k_unpack_states<<<blocks_for(w, n), TPB, 0, w->stream>>>(w->d_state, w->ctx.minv, w->d_inv,
+                                                            w->ctx.pose, w->ctx.vel, n);
     CU(cudaGetLastError());
     TRY(sfp_step(w, dt, substeps));
     return sfp_download_bodies(w, out, n);
@@ -1354,9 +1457,11 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
 
 namespace {
 struct HostPairs {
-    std::vector<uint2> pairs;       // colour-sorted device order
+    std::vector<uint2> pairs;       // colour-sorted device order, INTERNAL body indices
+    std::vector<uint2> ext;         // the same pairs in the caller's numbering (a < b)
     std::vector<uint32_t> colour;   // per pair
-    std::vector<uint32_t> order;    // permutation that sorts by (a,b)
+    std::vector<uint32_t> order;    // permutation that sorts by the caller's (a,b)
+    std::vector<uint32_t> ext_of;   // internal -> caller's index
     Counters k;
 };
 int fetch_pairs(SfpWorld* w, HostPairs* hp) {
@@ -1364,11 +1469,17 @@ int fetch_pairs(SfpWorld* w, HostPairs* hp) {
     TRY(check_overflow(w, hp->k));
     uint32_t P = w->stepped ? hp->k.n_pairs : 0u;
     hp->pairs.resize(P);
-    if (P) {
+    hp->ext_of.resize(w->n);
+    if (w->n)
+        CU(cudaMemcpyAsync(hp->ext_of.data(), w->d_ext, sizeof(uint32_t) * w->n, cudaMemcpyDeviceToHost,
+                           w->stream));
+    if (P)
         CU(cudaMemcpyAsync(hp->pairs.data(), w->ctx.pairs, sizeof(uint2) * P, cudaMemcpyDeviceToHost,
                            w->stream));
-        CU(cudaStreamSynchronize(w->stream));
-    }
+    CU(cudaStreamSynchronize(w->stream));
+    hp->ext.resize(P);
+    for (uint32_t i = 0; i < P; ++i)
+        hp->ext[i] = make_uint2(hp->ext_of[hp->pairs[i].x], hp->ext_of[hp->pairs[i].y]);
     hp->colour.resize(P);
     for (uint32_t col = 0; col < SFP_MAX_COLOURS; ++col)
         for (uint32_t i = hp->k.pair_col_off[col]; i < hp->k.pair_col_off[col + 1] && i < P; ++i)
@@ -1376,7 +1487,7 @@ int fetch_pairs(SfpWorld* w, HostPairs* hp) {
     hp->order.resize(P);
     for (uint32_t i = 0; i < P; ++i) hp->order[i] = i;
     std::sort(hp->order.begin(), hp->order.end(), [&](uint32_t x, uint32_t y) {
-        const uint2 &a = hp->pairs[x], &b = hp->pairs[y];
+        const uint2 &a = hp->ext[x], &b = hp->ext[y];
         return a.x != b.x ? a.x < b.x : a.y < b.y;
     });
     return SFP_OK;
@@ -1391,8 +1502,8 @@ int32_t sfp_get_pairs(SfpWorld* w, SfpPair* out, uint32_t cap, uint32_t* n_out) 
     TRY(fetch_pairs(w, &hp));
     *n_out = (uint32_t)hp.pairs.size();
     for (uint32_t i = 0; i < cap && i < hp.pairs.size(); ++i) {
-        out[i].a = hp.pairs[hp.order[i]].x;
-        out[i].b = hp.pairs[hp.order[i]].y;
+        out[i].a = hp.ext[hp.order[i]].x;
+        out[i].b = hp.ext[hp.order[i]].y;
     }
     return SFP_OK;
 }
@@ -1446,7 +1557,7 @@ int32_t sfp_get_contacts(SfpWorld* w, SfpContact* out, uint32_t cap, uint32_t* n
             r.p1 = cp1[k];
             r.s = cs[k];
             uint32_t a = hp.pairs[k].x, b = hp.pairs[k].y;
-            out[cnt] = sfp::contact_from_records(a, b, r, lam[k], pose[a], pose[b]);
+            out[cnt] = sfp::contact_from_records(hp.ext[k].x, hp.ext[k].y, r, lam[k], pose[a], pose[b]);
         }
         ++cnt;
     }
@@ -1562,8 +1673,8 @@ int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* 
     CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * m, cudaMemcpyHostToDevice,
                        w->stream));
     CU(cudaMemcpyAsync(w->d_idx, idx, sizeof(uint32_t) * m, cudaMemcpyHostToDevice, w->stream));
-    k_update_bodies<<<blocks_for(w, m), TPB, 0, w->stream>>>(w->d_idx, w->d_state, w->ctx.minv,
-                                                            w->ctx.pose, w->ctx.vel, m);
+    k_update_bodies<<<blocks_for(w, m), TPB, 0, w->stream>>>(w->d_idx, w->d_inv, w->d_state,
+                                                            w->ctx.minv, w->ctx.pose, w->ctx.vel, m);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(w->stream));  // idx is the caller's memory
     return SFP_OK;
@@ -1585,11 +1696,13 @@ int32_t sfp_get_stats(SfpWorld* w, SfpStats* out) {
     w->stats.max_penetration = sfp::u2f(k.maxpen_bits);
     w->stats.launches = w->launches;
     std::vector<sfp::f4> pose(w->n), vel(w->n);
+    std::vector<sfp::f2> minv(w->n);  // (the device arrays share one internal order)
     if (w->n) {
         CU(cudaMemcpy(pose.data(), w->ctx.pose, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost));
         CU(cudaMemcpy(vel.data(), w->ctx.vel, sizeof(sfp::f4) * w->n, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(minv.data(), w->ctx.minv, sizeof(sfp::f2) * w->n, cudaMemcpyDeviceToHost));
     }
-    sfp::energies(pose, vel, w->h_minv, w->p.gravity_x, w->p.gravity_y, &w->stats.kinetic_energy,
+    sfp::energies(pose, vel, minv, w->p.gravity_x, w->p.gravity_y, &w->stats.kinetic_energy,
                   &w->stats.potential_energy);
     *out = w->stats;
     return SFP_OK;
