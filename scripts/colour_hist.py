@@ -13,6 +13,6 @@ c = w.get_contacts(); print("manifolds", len(c), "points", int(c["count"].sum())
 print(w.last_step_breakdown_ms())
 import ctypes as C
 fn = w.api.lib.sfp_debug_stage_ns; fn.argtypes = [C.c_void_p, C.c_void_p]; fn.restype = C.c_int32
-out = np.zeros(10, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
+out = np.zeros(12, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
 names = {4: "integrate", 5: "narrowphase", 6: "pos head", 7: "derive", 8: "vel head", 9: "tails"}
 print("first tail colour", int(out[0]), {names[k]: round(float(out[k]) / 1e3, 1) for k in names}, "us per frame")

@@ -19,7 +19,7 @@ api = sf.product_api()
 fn = api.lib.sfp_debug_stage_ns
 fn.argtypes = [C.c_void_p, C.c_void_p]
 fn.restype = C.c_int32
-names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails"}
+names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails", 10: "tile_pos", 11: "tile_vel"}
 states = {}
 for label, flags in (("flow", 4), ("barrier", 0)):
     w = sf.World(api, flags=flags)
@@ -34,7 +34,7 @@ for label, flags in (("flow", 4), ("barrier", 0)):
         w.sync()
         for k, v in w.last_step_breakdown_ms().items():
             acc[k] = acc.get(k, 0) + v / frames
-    out = np.zeros(10, dtype=np.uint64)
+    out = np.zeros(12, dtype=np.uint64)
     fn(w.h, out.ctypes.data_as(C.c_void_p))
     st = w.stats()
     states[label] = w.download_bodies()

@@ -14,7 +14,7 @@ w.sync()
 fn = api.lib.sfp_debug_round_flags; fn.argtypes = [C.c_void_p, C.c_void_p]; fn.restype = C.c_int32
 f = np.zeros(512, dtype=np.uint32); fn(w.h, f.ctypes.data_as(C.c_void_p))
 fs = api.lib.sfp_debug_stage_ns; fs.argtypes = [C.c_void_p, C.c_void_p]; fs.restype = C.c_int32
-out = np.zeros(10, dtype=np.uint64); fs(w.h, out.ctypes.data_as(C.c_void_p))
+out = np.zeros(12, dtype=np.uint64); fs(w.h, out.ctypes.data_as(C.c_void_p))
 runs = int(f[488])
 print("runs with work (8 position passes)", runs, "pos pass us/frame", float(out[6]) / 1e3)
 seg = ["record loads", "wait", "gather+solve+store", "release"]

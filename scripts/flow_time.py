@@ -17,8 +17,8 @@ for _ in range(20):
     w.step(); w.sync()
     for k, v in w.last_step_breakdown_ms().items(): acc[k] = acc.get(k, 0) + v / 20
 fn = api.lib.sfp_debug_stage_ns; fn.argtypes = [C.c_void_p, C.c_void_p]; fn.restype = C.c_int32
-out = np.zeros(10, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
-names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails"}
+out = np.zeros(12, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
+names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails", 10: "tile_pos", 11: "tile_vel"}
 st = w.stats()
 print(os.path.basename(os.environ.get("SFP_B200_LIB", "default")), name, "flags", flags, {k: round(v, 4) for k, v in acc.items()},
       "overflow", st["overflow"], {names[k]: round(float(out[k]) / 1e3) for k in names}, flush=True)

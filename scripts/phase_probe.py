@@ -10,7 +10,7 @@ w = sf.World(sf.product_api()); w.upload_bodies(b); w.set_joints(j)
 for _ in range(240): w.step()
 w.sync(); w.step(); w.sync()
 fn = w.api.lib.sfp_debug_stage_ns; fn.argtypes = [C.c_void_p, C.c_void_p]; fn.restype = C.c_int32
-out = np.zeros(10, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
+out = np.zeros(12, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
 n = float(out[3])
 print(f"big position phases probed: {int(n)}; per phase (cycles): slowest block's work {out[1]/n:.0f}, "
       f"fastest block's work {out[2]/n:.0f}, phase duration (block 0) {out[4]/n:.0f}, block 0 waits at the barrier {out[5]/n:.0f}")

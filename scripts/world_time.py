@@ -13,6 +13,6 @@ for _ in range(30):
     w.step(); w.sync()
     for k, v in w.last_step_breakdown_ms().items(): acc[k] = acc.get(k, 0) + v / 30
 fn = w.api.lib.sfp_debug_stage_ns; fn.argtypes = [C.c_void_p, C.c_void_p]; fn.restype = C.c_int32
-out = np.zeros(10, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
-names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails"}
+out = np.zeros(12, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
+names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails", 10: "tile_pos", 11: "tile_vel"}
 print(os.environ.get("SFP_B200_LIB", "default"), name, {k: round(v, 3) for k, v in acc.items()}, "colour kernel us (init+warm, rounds, record)", [round(float(out[k]) / 1e3, 1) for k in (1, 2, 3)], "big", int(out[0]), {names[k]: round(float(out[k]) / 1e3) for k in names})

@@ -34,14 +34,14 @@ struct Counters {
     uint32_t overflow;
     uint32_t n_contacts, n_manifolds, maxpen_bits;
     uint32_t n_unc;  // length of Ctx::unc (pairs still uncoloured after the warm start)
-    uint32_t pad[1];
+    uint32_t n_colours_int;  // interior colours in use (tiles; n_colours counts the boundary ones)
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
     uint32_t round_flags[MAX_ROUNDS];
     // SM-clock cycles spent per stage in the last frame, written by thread 0 (batched path:
     // of each world's CTA): 0 load/store, 1 broadphase, 2 colouring, 3 bucketing, 4 integrate,
     // 5 narrowphase, 6 position solve, 7 derive, 8 velocity solve
-    unsigned long long stage_cycles[10];
+    unsigned long long stage_cycles[12];  // [10] / [11]: tile-interior position / velocity solve
 };
 
 struct Ctx {
@@ -63,6 +63,16 @@ struct Ctx {
     uint32_t *ekey0, *eval0, *ekey1, *eval1;
     uint32_t *pcnt, *poff;
     uint2* pairs_raw;
+    unsigned long long* pprio;  // per raw pair: its colouring priority (from the caller's indices); null: computed on the fly
+    // tiles (sfp_math.h, "Tiles"): after the re-sort the dynamic bodies are the indices [0, n_dyn)
+    // and tile t is the range [t * tile_b, (t + 1) * tile_b).  tile_b == 0: tiles off, every
+    // constraint is a boundary constraint.  Sorted constraint arrays: tile 0's interior
+    // constraints by colour, tile 1's, ..., then the boundary constraints by colour.  goff / jgoff:
+    // first sorted pair / joint of (group g, colour col) at [g * 64 + col], group n_tiles being the
+    // boundary (whose offsets Counters::pair_col_off / joint_col_off repeat).
+    uint32_t tile_b, n_dyn, n_tiles;
+    uint32_t *goff, *jgoff;
+    unsigned long long* mask_i;  // per body: interior colours in use (mask: boundary colours)
     // colouring
     unsigned long long *mask, *claim0, *claim1;
     // dataflow solve (k_substeps_flow): per body, the colours whose constraint has been applied
@@ -112,6 +122,14 @@ __device__ __forceinline__ f2 ld2(const float2* p, uint32_t i) {
 }
 
 __device__ __forceinline__ uint32_t ext_id(const Ctx& c, uint32_t i) { return c.ext ? c.ext[i] : i; }
+__device__ __forceinline__ uint32_t tile_of(const Ctx& c, uint32_t i) {
+    return (c.tile_b != 0u && i < c.n_dyn) ? i / c.tile_b : SFP_NO_TILE;
+}
+// sort group of a constraint: its tile if interior, n_tiles for the boundary
+__device__ __forceinline__ uint32_t group_of(const Ctx& c, uint32_t a, uint32_t b) {
+    const uint32_t t = sfp::constraint_tile(tile_of(c, a), tile_of(c, b));
+    return t == SFP_NO_TILE ? c.n_tiles : t;
+}
 
 // ---------------------------------------------------------------------------------------
 // A2 broadphase
@@ -132,6 +150,7 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
     if (tid == 0 && new_frame) {
         // per-frame counters
         c.cnt->n_colours = 0;
+        c.cnt->n_colours_int = 0;
         c.cnt->colour_rounds = 0;
     }
 }
@@ -278,8 +297,10 @@ __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
                     if (WRITE) {
                         if (o + k < c.cap_pairs) {
                             // "a" is the body with the lower index in the caller's numbering
-                            const bool fwd = ext_id(c, a) < ext_id(c, bf[j]);
+                            const uint32_t ea = ext_id(c, a), eb = ext_id(c, bf[j]);
+                            const bool fwd = ea < eb;
                             c.pairs_raw[o + k] = fwd ? make_uint2(a, bf[j]) : make_uint2(bf[j], a);
+                            if (c.pprio) c.pprio[o + k] = sfp::pair_priority(min(ea, eb), max(ea, eb));
                         }
                     }
                     ++k;
@@ -295,6 +316,36 @@ __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
     }
 }
 
+// Colours travel as `enc`: 0..62 a boundary colour, 63 the serial group, 64 + c an interior colour
+// (what sfp_get_colours reports).
+// Sort key of a coloured pair: bits 0-1 narrowphase class, 2-7 colour, 8-19 group (tile, or
+// n_tiles for the boundary and the serial group) — the radix passes sort on these —, bit 30 / 31
+// set when body a / b is static (rides along into pcol_sorted for the dataflow experiment).
+constexpr uint32_t PAIR_KEY_COLOUR_MASK = (uint32_t)SFP_MAX_COLOURS - 1u;
+constexpr uint32_t PAIR_KEY_GROUP_SHIFT = 8u, PAIR_KEY_GROUP_MASK = 0xfffu;
+constexpr uint32_t PAIR_KEY_STATIC_A = 1u << 30, PAIR_KEY_STATIC_B = 1u << 31;
+__device__ __forceinline__ uint32_t pair_sort_key(const Ctx& c, uint32_t enc, uint2 p) {
+    const uint32_t col = enc & PAIR_KEY_COLOUR_MASK;
+    const uint32_t group = (enc >= SFP_CLASS_INTERIOR) ? group_of(c, p.x, p.y) : c.n_tiles;
+    return (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y)) |
+           (group << PAIR_KEY_GROUP_SHIFT) | (c.meta[p.x].w ? 0u : PAIR_KEY_STATIC_A) |
+           (c.meta[p.y].w ? 0u : PAIR_KEY_STATIC_B);
+}
+__device__ __forceinline__ uint32_t pair_key_colour(uint32_t key) {
+    return (key >> SFP_TYPE_BITS) & PAIR_KEY_COLOUR_MASK;
+}
+__device__ __forceinline__ uint32_t pair_key_group(uint32_t key) {
+    return (key >> PAIR_KEY_GROUP_SHIFT) & PAIR_KEY_GROUP_MASK;
+}
+__device__ __forceinline__ uint32_t pair_key_enc(const Ctx& c, uint32_t key) {
+    return pair_key_colour(key) + (pair_key_group(key) != c.n_tiles ? SFP_CLASS_INTERIOR : 0u);
+}
+// joints: enc in bits 0-7, group above
+__device__ __forceinline__ uint32_t joint_sort_key(const Ctx& c, uint32_t enc, uint2 jb) {
+    const uint32_t group = (enc >= SFP_CLASS_INTERIOR) ? group_of(c, jb.x, jb.y) : c.n_tiles;
+    return enc | (group << PAIR_KEY_GROUP_SHIFT);
+}
+
 // ---------------------------------------------------------------------------------------
 // A8 colouring: rounds of bid (atomicMin of a unique 64-bit priority on each dynamic body) and
 // take (a constraint holding the claim on all its dynamic bodies takes the lowest free colour)
@@ -303,6 +354,7 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
     const uint32_t P = c.cnt->n_pairs;
     for (uint32_t i = tid; i < c.n; i += nth) {
         c.mask[i] = 0ull;
+        if (c.tile_b) c.mask_i[i] = 0ull;
         c.claim0[i] = SFP_NO_CLAIM;
         c.claim1[i] = SFP_NO_CLAIM;
     }
@@ -317,7 +369,7 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
         uint2 jb = c.jbod_in[k];
         bool dyn = (c.meta[jb.x].w | c.meta[jb.y].w) != 0;
         if (!dyn) {
-            c.jcol[k] = 0u;
+            c.jcol[k] = joint_sort_key(c, 0u, jb);
             atomicMax(&c.cnt->n_colours, 1u);
         } else if (!c.warm) {
             c.jcol[k] = UNCOLOURED;
@@ -326,32 +378,42 @@ __device__ __forceinline__ void stage_colour_init(const Ctx& c, uint32_t tid, ui
     for (uint32_t k = tid; k < MAX_ROUNDS; k += nth) c.cnt->round_flags[k] = 0u;
 }
 
-// Sort key of a coloured pair: bits 0-1 narrowphase class, bits 2-7 colour (the radix pass sorts on
-// these eight), bit 8 / 9 set when body a / b is static (rides along into pcol_sorted, where the
-// dataflow solve reads colour and flags of a pair with one coalesced load).
-__device__ __forceinline__ uint32_t pair_sort_key(const Ctx& c, uint32_t col, uint2 p) {
-    return (col << SFP_TYPE_BITS) | sfp::pair_type_key(ld4(c.shape, p.x), ld4(c.shape, p.y)) |
-           (c.meta[p.x].w ? 0u : 0x100u) | (c.meta[p.y].w ? 0u : 0x200u);
-}
-constexpr uint32_t PAIR_KEY_COLOUR_MASK = (uint32_t)SFP_MAX_COLOURS - 1u;
-__device__ __forceinline__ uint32_t pair_key_colour(uint32_t key) {
-    return (key >> SFP_TYPE_BITS) & PAIR_KEY_COLOUR_MASK;
-}
-
 // warm start: a constraint that existed in the previous frame keeps its colour.  Runs after
 // stage_colour_init (masks are zero), before the first round.
-__device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b, uint32_t col) {
-    if (col != SFP_SERIAL_COLOUR) {
-        if (c.meta[a].w) atomicOr(&c.mask[a], 1ull << col);
-        if (c.meta[b].w) atomicOr(&c.mask[b], 1ull << col);
+// (the colour counts are accumulated per thread and published once per warp: an atomicMax per
+// constraint on one of two addresses chosen per lane is 340 k serialised atomics on a 100 k pile)
+struct ColourCount {
+    uint32_t bnd = 0, inter = 0;
+};
+__device__ __forceinline__ void colour_count_publish(const Ctx& c, ColourCount n) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        n.bnd = max(n.bnd, __shfl_xor_sync(0xffffffffu, n.bnd, d));
+        n.inter = max(n.inter, __shfl_xor_sync(0xffffffffu, n.inter, d));
     }
-    atomicMax(&c.cnt->n_colours, col + 1u);
+    if ((threadIdx.x & 31u) == 0u) {
+        if (n.bnd) atomicMax(&c.cnt->n_colours, n.bnd);
+        if (n.inter) atomicMax(&c.cnt->n_colours_int, n.inter);
+    }
+}
+__device__ __forceinline__ void colour_keep(const Ctx& c, uint32_t a, uint32_t b, uint32_t enc,
+                                            ColourCount* n) {
+    const uint32_t col = enc & PAIR_KEY_COLOUR_MASK;
+    const bool inter = enc >= SFP_CLASS_INTERIOR;
+    if (col != SFP_SERIAL_COLOUR) {
+        unsigned long long* mk = inter ? c.mask_i : c.mask;
+        if (c.meta[a].w) atomicOr(&mk[a], 1ull << col);
+        if (c.meta[b].w) atomicOr(&mk[b], 1ull << col);
+    }
+    if (inter) n->inter = max(n->inter, col + 1u);
+    else n->bnd = max(n->bnd, col + 1u);
 }
 __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, uint32_t nth) {
     if (!c.warm) return;
     const uint32_t P = c.cnt->n_pairs;
     // (whole warps walk the loop together: the append below is warp-aggregated)
     const uint32_t lane = threadIdx.x & 31u;
+    ColourCount ncol;
     for (uint32_t base = tid - lane; base < P; base += nth) {
         const uint32_t k = base + lane;
         bool found = k >= P;  // lanes past the end have nothing to append
@@ -364,7 +426,7 @@ __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, ui
                 if (slot == 0ull) break;
                 if ((slot & SFP_CTAB_KEYMASK) == key) {
                     uint32_t col = (uint32_t)(slot >> 44) - 1u;
-                    colour_keep(c, p.x, p.y, col);
+                    colour_keep(c, p.x, p.y, col, &ncol);
                     c.pcol[k] = pair_sort_key(c, col, p);
                     found = true;
                     break;
@@ -385,8 +447,10 @@ __device__ __forceinline__ void stage_colour_warm(const Ctx& c, uint32_t tid, ui
     for (uint32_t k = tid; k < c.nj; k += nth) {
         uint32_t col = c.jcol[k];
         uint2 jb = c.jbod_in[k];
-        if (col != UNCOLOURED && (c.meta[jb.x].w | c.meta[jb.y].w) != 0) colour_keep(c, jb.x, jb.y, col);
+        if (col != UNCOLOURED && (c.meta[jb.x].w | c.meta[jb.y].w) != 0)
+            colour_keep(c, jb.x, jb.y, col & 0xffu, &ncol);
     }
+    colour_count_publish(c, ncol);
 }
 
 // record this frame's colours for the next one (tab_new was zeroed by the host / the caller)
@@ -396,7 +460,7 @@ __device__ __forceinline__ void stage_colour_record(const Ctx& c, uint32_t tid, 
         uint32_t key16 = c.pcol[k];
         if (key16 == UNCOLOURED) continue;
         uint2 p = c.pairs_raw[k];
-        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, pair_key_colour(key16));
+        const unsigned long long packed = sfp::ctab_pack(p.x, p.y, pair_key_enc(c, key16));
         uint32_t h = sfp::ctab_hash(p.x, p.y) & c.tab_mask;
         while (atomicCAS(&c.tab_new[h], 0ull, packed) != 0ull) h = (h + 1u) & c.tab_mask;
     }
@@ -458,7 +522,8 @@ __device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, u
         const uint32_t k = c.unc ? c.unc[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
-            colour_bid_one(c, claim, p.x, p.y, sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)));
+            colour_bid_one(c, claim, p.x, p.y,
+                           c.pprio ? c.pprio[k] : sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)));
         }
     }
     for (uint32_t k = tid; k < c.nj; k += nth)
@@ -472,7 +537,7 @@ __device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, u
 __device__ __forceinline__ uint32_t colour_take_one(const Ctx& c, const unsigned long long* claim,
                                                     unsigned long long* next_claim, uint32_t a,
                                                     uint32_t b, unsigned long long key,
-                                                    uint32_t round) {
+                                                    uint32_t round, ColourCount* n) {
     bool da = c.meta[a].w != 0, db = c.meta[b].w != 0;
     bool win = (!da || claim[a] == key) && (!db || claim[b] == key);
     if (!win) {
@@ -481,14 +546,20 @@ __device__ __forceinline__ uint32_t colour_take_one(const Ctx& c, const unsigned
         c.cnt->round_flags[round] = 1u;
         return UNCOLOURED;
     }
-    unsigned long long m = (da ? c.mask[a] : 0ull) | (db ? c.mask[b] : 0ull);
+    const bool inter = c.tile_b != 0u && group_of(c, a, b) != c.n_tiles;
+    unsigned long long* mk = inter ? c.mask_i : c.mask;
+    unsigned long long m = (da ? mk[a] : 0ull) | (db ? mk[b] : 0ull);
     int col = sfp::pick_colour(m);
     if (col != SFP_SERIAL_COLOUR) {
-        if (da) c.mask[a] |= 1ull << col;
-        if (db) c.mask[b] |= 1ull << col;
+        if (da) mk[a] |= 1ull << col;
+        if (db) mk[b] |= 1ull << col;
+        if (inter) n->inter = max(n->inter, (uint32_t)col + 1u);
+        else n->bnd = max(n->bnd, (uint32_t)col + 1u);
+        return (uint32_t)col + (inter ? SFP_CLASS_INTERIOR : 0u);
     }
-    atomicMax(&c.cnt->n_colours, (uint32_t)col + 1u);
-    return (uint32_t)col;
+    // every colour of the class is taken on these bodies: the serial group (one for both classes)
+    n->bnd = max(n->bnd, (uint32_t)SFP_SERIAL_COLOUR + 1u);
+    return (uint32_t)SFP_SERIAL_COLOUR;
 }
 
 __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, uint32_t tid,
@@ -496,12 +567,14 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
     unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
     unsigned long long* next_claim = (round & 1u) ? c.claim0 : c.claim1;
     const uint32_t P = c.unc ? c.cnt->n_unc : c.cnt->n_pairs;
+    ColourCount ncol;
     for (uint32_t i = tid; i < P; i += nth) {
         const uint32_t k = c.unc ? c.unc[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
-            uint32_t col = colour_take_one(c, claim, next_claim, p.x, p.y,
-                                           sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)), round);
+            uint32_t col = colour_take_one(
+                c, claim, next_claim, p.x, p.y,
+                c.pprio ? c.pprio[k] : sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)), round, &ncol);
             // sort key: colour in the high bits, narrowphase class in the low ones (coherence
             // inside a colour bucket)
             if (col != UNCOLOURED) col = pair_sort_key(c, col, p);
@@ -511,40 +584,58 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
     for (uint32_t k = tid; k < c.nj; k += nth)
         if (c.jcol[k] == UNCOLOURED) {
             uint2 p = c.jbod_in[k];
-            c.jcol[k] =
-                colour_take_one(c, claim, next_claim, p.x, p.y, sfp::joint_priority(k), round);
+            const uint32_t enc =
+                colour_take_one(c, claim, next_claim, p.x, p.y, sfp::joint_priority(k), round, &ncol);
+            c.jcol[k] = enc == UNCOLOURED ? UNCOLOURED : joint_sort_key(c, enc, p);
         }
+    colour_count_publish(c, ncol);
     if (tid == 0) c.cnt->colour_rounds = round + 1u;
 }
 
-// after the stable sort by colour: gather constraints into colour order, find colour bounds
-// (`shift` strips the sub-key below the colour)
-__device__ __forceinline__ void colour_bounds(const uint32_t* sorted_col, uint32_t n, uint32_t i,
-                                              uint32_t* off, int shift) {
-    uint32_t col = (sorted_col[i] >> shift) & PAIR_KEY_COLOUR_MASK;
-    int prev = (i == 0) ? -1 : (int)((sorted_col[i - 1] >> shift) & PAIR_KEY_COLOUR_MASK);
-    for (int cc = prev + 1; cc <= (int)col; ++cc) off[cc] = i;
-    if (i == n - 1)
-        for (int cc = (int)col + 1; cc <= SFP_MAX_COLOURS; ++cc) off[cc] = n;
+// after the stable sort by (group, colour): gather the constraints into that order and find where
+// every (group, colour) starts: one binary search per table entry over the sorted keys
+__device__ __forceinline__ uint32_t pair_key_dense(uint32_t key) {
+    return pair_key_group(key) * (uint32_t)SFP_MAX_COLOURS + pair_key_colour(key);
+}
+__device__ __forceinline__ uint32_t joint_key_dense(uint32_t key) {
+    return (key >> PAIR_KEY_GROUP_SHIFT) * (uint32_t)SFP_MAX_COLOURS + (key & PAIR_KEY_COLOUR_MASK);
+}
+template <bool JOINTS>
+__device__ __forceinline__ void group_offsets(const uint32_t* sorted, uint32_t n, uint32_t n_tiles,
+                                              uint32_t* goff, uint32_t* boff, uint32_t tid,
+                                              uint32_t nth) {
+    const uint32_t kmax = (n_tiles + 1u) * (uint32_t)SFP_MAX_COLOURS, bbase = n_tiles * (uint32_t)SFP_MAX_COLOURS;
+    for (uint32_t K = goff ? tid : bbase + tid; K <= kmax; K += nth) {
+        uint32_t lo = 0, hi = n;  // first i with dense(sorted[i]) >= K
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t d = JOINTS ? joint_key_dense(sorted[mid]) : pair_key_dense(sorted[mid]);
+            if (d < K) lo = mid + 1u;
+            else hi = mid;
+        }
+        if (goff) goff[K] = lo;
+        if (K >= bbase) boff[K - bbase] = lo;
+    }
 }
 
 __device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_t nth) {
     const uint32_t P = c.cnt->n_pairs;
-    for (uint32_t i = tid; i < P; i += nth) {
-        c.pairs[i] = c.pairs_raw[c.pperm[i]];
-        colour_bounds(c.pcol_sorted, P, i, c.cnt->pair_col_off, SFP_TYPE_BITS);
-    }
-    if (P == 0 && tid == 0)
-        for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->pair_col_off[cc] = 0;
+    for (uint32_t i = tid; i < P; i += nth) c.pairs[i] = c.pairs_raw[c.pperm[i]];
+    group_offsets<false>(c.pcol_sorted, P, c.n_tiles, c.goff, c.cnt->pair_col_off, tid, nth);
     for (uint32_t i = tid; i < c.nj; i += nth) {
         uint32_t s = c.jperm[i];
         c.jbod[i] = c.jbod_in[s];
         c.janc[i] = c.janc_in[s];
         c.jpar[i] = c.jpar_in[s];
-        colour_bounds(c.jcol_sorted, c.nj, i, c.cnt->joint_col_off, 0);
     }
-    if (c.nj == 0 && tid == 0)
-        for (int cc = 0; cc <= SFP_MAX_COLOURS; ++cc) c.cnt->joint_col_off[cc] = 0;
+    if (c.nj) {
+        group_offsets<true>(c.jcol_sorted, c.nj, c.n_tiles, c.jgoff, c.cnt->joint_col_off, tid, nth);
+    } else {
+        const uint32_t kmax = (c.n_tiles + 1u) * (uint32_t)SFP_MAX_COLOURS;
+        if (c.jgoff)
+            for (uint32_t K = tid; K <= kmax; K += nth) c.jgoff[K] = 0u;
+        for (uint32_t K = tid; K <= (uint32_t)SFP_MAX_COLOURS; K += nth) c.cnt->joint_col_off[K] = 0u;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -581,11 +672,11 @@ __device__ __forceinline__ void flow_mark_noop(const Ctx& c, uint32_t k, uint2 p
     const uint32_t col = pair_key_colour(key);
     if (col == SFP_SERIAL_COLOUR) return;
     const unsigned long long bit = 1ull << col;
-    if (!(key & 0x100u)) {
+    if (!(key & PAIR_KEY_STATIC_A)) {
         if (pos_too) red_or_u64(&c.done[2u * p.x], bit);
         red_or_u64(&c.done[2u * p.x + 1u], bit);
     }
-    if (!(key & 0x200u)) {
+    if (!(key & PAIR_KEY_STATIC_B)) {
         if (pos_too) red_or_u64(&c.done[2u * p.y], bit);
         red_or_u64(&c.done[2u * p.y + 1u], bit);
     }
@@ -822,6 +913,283 @@ __device__ __forceinline__ void stage_solve_vel(const Ctx& c, uint32_t colour, f
                                                 float rest_threshold, uint32_t tid, uint32_t nth,
                                                 bool skip_first = false) {
     stage_solve_vel(c, colour, h, rest_threshold, tid, nth, skip_first, c.cnt->pair_col_off);
+}
+
+// ---------------------------------------------------------------------------------------
+// Tile-resident solve (sfp_math.h, "Tiles"): ONE thread block holds a tile's bodies in shared
+// memory and runs all interior colours of a solver pass between __syncthreads — a colour costs a
+// shared-memory gather, the solve and a block barrier instead of an L2 gather / scatter and a
+// grid-wide barrier.  Interior constraints only touch the tile's own bodies and static ones
+// (read from global memory, never written), so tiles need nothing from each other.
+// ---------------------------------------------------------------------------------------
+struct TileView {
+    float4 *pose, *aux;  // aux: `prev` in the position pass, `vel` in the velocity pass
+    float2* minv;
+    unsigned long long *mask, *done;  // interior colours a body uses / has had applied this pass
+    uint32_t base, count;  // the tile is the bodies [base, base + count)
+};
+constexpr uint32_t TILE_SMEM_PER_BODY = 16u + 16u + 8u + 8u + 8u;
+
+__device__ __forceinline__ sfp::BodyPos tile_load_pos(const Ctx& c, const TileView& tv, uint32_t i) {
+    const uint32_t l = i - tv.base;
+    float4 pose, prev;
+    float2 mi;
+    if (l < tv.count) {
+        pose = tv.pose[l];
+        prev = tv.aux[l];
+        mi = tv.minv[l];
+    } else {  // a static body
+        pose = c.pose[i];
+        prev = c.prev[i];
+        mi = c.minv[i];
+    }
+    sfp::BodyPos b;
+    b.x = sfp::mk(pose.x, pose.y);
+    b.q = sfp::mk(pose.z, pose.w);
+    b.d = sfp::mk(prev.x, prev.y);
+    b.qp = sfp::mk(prev.z, prev.w);
+    b.im = mi.x;
+    b.ii = mi.y;
+    return b;
+}
+__device__ __forceinline__ void tile_store_pos(const TileView& tv, uint32_t i, const sfp::BodyPos& b) {
+    const uint32_t l = i - tv.base;
+    if (l < tv.count && (b.im > 0.0f || b.ii > 0.0f)) {
+        tv.pose[l] = make_float4(b.x.x, b.x.y, b.q.x, b.q.y);
+        tv.aux[l] = make_float4(b.d.x, b.d.y, b.qp.x, b.qp.y);
+    }
+}
+
+// Inside a tile the colours are NOT separated by barriers: every body of the tile has a bit mask
+// in shared memory of the interior colours already applied to it in this pass (TileView::done),
+// and a constraint of colour c waits until the masks of its two bodies hold every interior colour
+// those bodies use below c (TileView::mask, the colouring's per-body masks).  The per-body order
+// is the colour order, so the result is that of a barrier after every colour; but a hop of a
+// dependency chain now costs a shared-memory round trip plus the solve, and the warps of the
+// block work on many colours at once.  Items of a colour are cut into runs of 32 (padded, so a
+// run never straddles two colours and its lanes never depend on each other); runs are numbered
+// in colour order and dealt round-robin to the block's warps, each warp takes its runs in
+// ascending order: a run depends only on lower-numbered runs and every warp of the block is
+// resident, so the waiting cannot deadlock.  A pair without a contact (or without a normal
+// impulse, in the velocity pass) reports itself done without waiting.
+#ifndef SFP_TILE_SPIN_LIMIT
+#define SFP_TILE_SPIN_LIMIT (1u << 22)
+#endif
+__device__ __forceinline__ void tile_wait(const Ctx& c, const TileView& tv, uint32_t la,
+                                          unsigned long long need_a, uint32_t lb,
+                                          unsigned long long need_b) {
+    if ((need_a | need_b) == 0ull) return;
+    volatile unsigned long long* done = tv.done;
+    uint32_t spins = 0;
+    for (;;) {
+        const unsigned long long da = need_a ? done[la] : 0ull, db = need_b ? done[lb] : 0ull;
+        if ((da & need_a) == need_a && (db & need_b) == need_b) break;
+        __nanosleep(20);
+        if (++spins >= SFP_TILE_SPIN_LIMIT) {  // a bug, not a data condition: give up loudly
+            atomicOr(&c.cnt->overflow, 32u);
+            break;
+        }
+    }
+    __threadfence_block();
+}
+__device__ __forceinline__ void tile_mark(const TileView& tv, uint32_t l, unsigned long long bit) {
+    if (l < tv.count) atomicOr(&tv.done[l], bit);
+}
+// colour of run r (cursor `col` only moves forward); s_rb[col] = first run of colour col
+__device__ __forceinline__ uint32_t tile_run_colour(const uint32_t* s_rb, uint32_t r, uint32_t col) {
+    while (r >= s_rb[col + 1]) ++col;
+    return col;
+}
+
+__device__ __forceinline__ void tile_solve_pos(const Ctx& c, const TileView& tv, const uint32_t* s_jo,
+                                               const uint32_t* s_po, const uint32_t* s_rb,
+                                               float inv_h2) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t total = s_rb[SFP_SERIAL_COLOUR];
+    uint32_t col = 0;
+    for (uint32_t r = warp; r < total; r += nwarps) {
+        col = tile_run_colour(s_rb, r, col);
+        const unsigned long long bit = 1ull << col, below = bit - 1ull;
+        const uint32_t t = (r - s_rb[col]) * 32u + lane;
+        const uint32_t j0 = s_jo[col], nj = s_jo[col + 1] - j0;
+        const uint32_t p0 = s_po[col], np = s_po[col + 1] - p0;
+        if (t < nj) {
+            const uint32_t k = j0 + t;
+            const uint2 jb = c.jbod[k];
+            const float4 an = c.janc[k], pr = c.jpar[k];
+            const uint32_t la = jb.x - tv.base, lb = jb.y - tv.base;
+            tile_wait(c, tv, la, la < tv.count ? tv.mask[la] & below : 0ull, lb,
+                      lb < tv.count ? tv.mask[lb] & below : 0ull);
+            sfp::BodyPos A = tile_load_pos(c, tv, jb.x), B = tile_load_pos(c, tv, jb.y);
+            sfp::solve_joint(&A, &B, sfp::mk(an.x, an.y), sfp::mk(an.z, an.w), pr.x, pr.y,
+                             sfp::f2u(pr.z), inv_h2);
+            tile_store_pos(tv, jb.x, A);
+            tile_store_pos(tv, jb.y, B);
+            __threadfence_block();
+            tile_mark(tv, la, bit);
+            tile_mark(tv, lb, bit);
+        } else if (t - nj < np) {
+            const uint32_t k = p0 + (t - nj);
+#ifdef SFP_TILE_PROBE
+            const long long q0_ = clock64();
+#endif
+            const PairRec r_ = load_pair_rec(c, k);
+            const uint32_t cnt = sfp::f2u(r_.cb.y);
+            const uint32_t la = r_.p.x - tv.base, lb = r_.p.y - tv.base;
+            f4 lam;
+            lam.x = lam.y = lam.z = lam.w = 0.0f;
+            if (cnt != 0u) {
+#ifdef SFP_TILE_PROBE
+                const long long q1_ = clock64();
+#endif
+                tile_wait(c, tv, la, la < tv.count ? tv.mask[la] & below : 0ull, lb,
+                          lb < tv.count ? tv.mask[lb] & below : 0ull);
+#ifdef SFP_TILE_PROBE
+                const long long q2_ = clock64();
+#endif
+                sfp::BodyPos A = tile_load_pos(c, tv, r_.p.x), B = tile_load_pos(c, tv, r_.p.y);
+                lam = sfp::solve_contact_manifold(&A, &B, sfp::mk(r_.ca.x, r_.ca.y), cnt,
+                                                  sfp::mk(r_.q0.x, r_.q0.y), sfp::mk(r_.q0.z, r_.q0.w),
+                                                  sfp::mk(r_.q1.x, r_.q1.y), sfp::mk(r_.q1.z, r_.q1.w),
+                                                  r_.ca.z);
+                tile_store_pos(tv, r_.p.x, A);
+                tile_store_pos(tv, r_.p.y, B);
+                __threadfence_block();
+#ifdef SFP_TILE_PROBE
+                // development probe: per LANE cycles for record load / wait / solve, sampled
+                if (blockIdx.x == 3 && (k & 7u) == 0u) {
+                    const long long q3_ = clock64();
+                    uint32_t* f = c.cnt->round_flags;
+                    atomicAdd(&f[480], (uint32_t)(q1_ - q0_) >> 4);
+                    atomicAdd(&f[481], (uint32_t)(q2_ - q1_) >> 4);
+                    atomicAdd(&f[482], (uint32_t)(q3_ - q2_) >> 4);
+                    atomicMax(&f[484], (uint32_t)(q1_ - q0_));
+                    atomicMax(&f[485], (uint32_t)(q2_ - q1_));
+                    atomicMax(&f[486], (uint32_t)(q3_ - q2_));
+                    atomicAdd(&f[488], 1u);
+                    atomicAdd(&f[col], (uint32_t)(q2_ - q1_) >> 4);
+                    atomicAdd(&f[64 + col], 1u);
+                    atomicAdd(&f[128 + col], (uint32_t)(q3_ - q2_) >> 4);
+                }
+#endif
+            }
+            st4(c.lam, k, lam);
+            tile_mark(tv, la, bit);
+            tile_mark(tv, lb, bit);
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void tile_solve_vel(const Ctx& c, const TileView& tv, const uint32_t* s_jo,
+                                               const uint32_t* s_po, const uint32_t* s_rb, float h,
+                                               float rest_threshold) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t total = s_rb[SFP_SERIAL_COLOUR];
+    uint32_t col = 0;
+    for (uint32_t r = warp; r < total; r += nwarps) {
+        col = tile_run_colour(s_rb, r, col);
+        const unsigned long long bit = 1ull << col, below = bit - 1ull;
+        const uint32_t t = (r - s_rb[col]) * 32u + lane;
+        const uint32_t j0 = s_jo[col], nj = s_jo[col + 1] - j0;
+        const uint32_t p0 = s_po[col], np = s_po[col + 1] - p0;
+        if (t < nj) {
+            // joints have no velocity pass
+            const uint2 jb = c.jbod[j0 + t];
+            tile_mark(tv, jb.x - tv.base, bit);
+            tile_mark(tv, jb.y - tv.base, bit);
+        } else if (t - nj < np) {
+            const uint32_t k = p0 + (t - nj);
+            const f4 lam = ld4(c.lam, k);
+            const uint2 p = c.pairs[k];
+            const uint32_t la = p.x - tv.base, lb = p.y - tv.base;
+            if (lam.x > 0.0f || lam.z > 0.0f) {
+                const PairRec r_ = load_pair_rec(c, k);
+                tile_wait(c, tv, la, la < tv.count ? tv.mask[la] & below : 0ull, lb,
+                          lb < tv.count ? tv.mask[lb] & below : 0ull);
+                const bool ina = la < tv.count, inb = lb < tv.count;
+                const float4 va = ina ? tv.aux[la] : c.vel[p.x], vb = inb ? tv.aux[lb] : c.vel[p.y];
+                const float4 pa = ina ? tv.pose[la] : c.pose[p.x], pb = inb ? tv.pose[lb] : c.pose[p.y];
+                const float2 ma = ina ? tv.minv[la] : c.minv[p.x], mb = inb ? tv.minv[lb] : c.minv[p.y];
+                sfp::BodyVel A, B;
+                A.v = sfp::mk(va.x, va.y);
+                A.w = va.z;
+                A.im = ma.x;
+                A.ii = ma.y;
+                B.v = sfp::mk(vb.x, vb.y);
+                B.w = vb.z;
+                B.im = mb.x;
+                B.ii = mb.y;
+                sfp::solve_manifold_velocity(
+                    &A, &B, sfp::mk(pa.z, pa.w), sfp::mk(pb.z, pb.w), sfp::mk(r_.ca.x, r_.ca.y),
+                    sfp::f2u(r_.cb.y), sfp::mk(r_.q0.x, r_.q0.y), sfp::mk(r_.q0.z, r_.q0.w),
+                    sfp::mk(r_.q1.x, r_.q1.y), sfp::mk(r_.q1.z, r_.q1.w), lam, r_.cb.z, r_.cb.w, r_.ca.z,
+                    r_.ca.w, r_.cb.x, h, rest_threshold);
+                if (ina && (ma.x > 0.0f || ma.y > 0.0f)) tv.aux[la] = make_float4(A.v.x, A.v.y, A.w, 0.0f);
+                if (inb && (mb.x > 0.0f || mb.y > 0.0f)) tv.aux[lb] = make_float4(B.v.x, B.v.y, B.w, 0.0f);
+                __threadfence_block();
+            }
+            tile_mark(tv, la, bit);
+            tile_mark(tv, lb, bit);
+        }
+    }
+    __syncthreads();
+}
+
+// one pass over the tiles of this block: load the tile, solve its interior colours, store it.
+// smem: tile_b x TILE_SMEM_PER_BODY bytes; s_off: 3 x 65 words.  Every thread of the block must
+// call it.
+template <bool VEL>
+__device__ __forceinline__ void stage_tiles(const Ctx& c, float4* smem, uint32_t* s_off, float h,
+                                            float rest_threshold) {
+    TileView tv;
+    tv.pose = smem;
+    tv.aux = smem + c.tile_b;
+    tv.minv = reinterpret_cast<float2*>(smem + 2u * (size_t)c.tile_b);
+    tv.mask = reinterpret_cast<unsigned long long*>(tv.minv + c.tile_b);
+    tv.done = tv.mask + c.tile_b;
+    float4* g_aux = VEL ? c.vel : c.prev;
+    const float inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    uint32_t* s_jo = s_off;
+    uint32_t* s_po = s_off + (SFP_MAX_COLOURS + 1);
+    uint32_t* s_rb = s_off + 2 * (SFP_MAX_COLOURS + 1);
+    for (uint32_t t = blockIdx.x; t < c.n_tiles; t += gridDim.x) {
+        tv.base = t * c.tile_b;
+        tv.count = min(c.tile_b, c.n_dyn - tv.base);
+        for (uint32_t i = threadIdx.x; i <= (uint32_t)SFP_MAX_COLOURS; i += blockDim.x) {
+            s_po[i] = c.goff[(size_t)t * SFP_MAX_COLOURS + i];
+            s_jo[i] = c.jgoff[(size_t)t * SFP_MAX_COLOURS + i];
+        }
+        __syncthreads();
+        // (a tile without interior constraints has nothing to do)
+        if (s_po[0] == s_po[SFP_MAX_COLOURS] && s_jo[0] == s_jo[SFP_MAX_COLOURS]) {
+            __syncthreads();
+            continue;
+        }
+        if (threadIdx.x == 0) {
+            uint32_t runs = 0;
+            for (uint32_t col = 0; col < (uint32_t)SFP_SERIAL_COLOUR; ++col) {
+                s_rb[col] = runs;
+                runs += ((s_jo[col + 1] - s_jo[col]) + (s_po[col + 1] - s_po[col]) + 31u) / 32u;
+            }
+            s_rb[SFP_SERIAL_COLOUR] = runs;
+        }
+        for (uint32_t i = threadIdx.x; i < tv.count; i += blockDim.x) {
+            tv.pose[i] = c.pose[tv.base + i];
+            tv.aux[i] = g_aux[tv.base + i];
+            tv.minv[i] = c.minv[tv.base + i];
+            tv.mask[i] = c.mask_i[tv.base + i];
+            tv.done[i] = 0ull;
+        }
+        __syncthreads();
+        if (VEL) tile_solve_vel(c, tv, s_jo, s_po, s_rb, h, rest_threshold);
+        else tile_solve_pos(c, tv, s_jo, s_po, s_rb, inv_h2);
+        for (uint32_t i = threadIdx.x; i < tv.count; i += blockDim.x) {
+            if (!VEL) c.pose[tv.base + i] = tv.pose[i];
+            g_aux[tv.base + i] = tv.aux[i];
+        }
+        __syncthreads();
+    }
 }
 
 // ---------------------------------------------------------------------------------------

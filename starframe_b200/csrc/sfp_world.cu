@@ -93,11 +93,16 @@ __global__ void k_serial_vel(Ctx c, float h, float rt) {
 // (every SFP_RECOLOUR_PERIOD-th frame): the colour table, keyed by internal indices, is not read
 // in such a frame.  Scratch: the broadphase entry buffers for the sort, the contact record arrays
 // (dead between frames) for the permuted copies.
-__global__ void __launch_bounds__(TPB) k_tile_keys(Ctx c, uint32_t* __restrict__ keys) {
-    for (uint32_t i = gtid(); i < c.n; i += gnth()) {
+// (keys are laid out in the CALLER'S order, value = where the body is now: the stable sort then
+// breaks ties by the caller's index, as the oracle does, whatever the current internal order)
+__global__ void __launch_bounds__(TPB) k_tile_keys(Ctx c, uint32_t* __restrict__ keys,
+                                                   uint32_t* __restrict__ vals) {
+    for (uint32_t e = gtid(); e < c.n; e += gnth()) {
+        const uint32_t i = c.inv[e];
         const float4 p = c.pose[i];
         const float2 m = c.minv[i];
-        keys[i] = sfp::tile_sort_key(p.x, p.y, c.inv_cell, m.x > 0.0f || m.y > 0.0f);
+        keys[e] = sfp::tile_sort_key(p.x, p.y, c.inv_cell, m.x > 0.0f || m.y > 0.0f);
+        vals[e] = i;
     }
 }
 __global__ void __launch_bounds__(TPB) k_permute_gather(Ctx c, const uint32_t* __restrict__ src) {
@@ -363,9 +368,14 @@ __device__ __forceinline__ int next_bit(unsigned long long m, int after) {
 #endif
 // POLYS: the variant that can collide general polygons (bigger, more registers); the host
 // launches it only for worlds that hold at least one polygon body
-template <bool POLYS>
+// TILES: the solve order with tiles (sfp_math.h): every block first runs the interior colours of
+// its tiles out of shared memory (stage_tiles), then the boundary colours follow in grid-wide
+// phases as before
+template <bool POLYS, bool TILES>
 __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, float h, uint32_t substeps,
                                                        float rest_threshold) {
+    extern __shared__ float4 dyn_smem[];
+    __shared__ uint32_t s_toff[3 * (SFP_MAX_COLOURS + 1)];
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
     // A colour's constraints go to threads in warp-sized runs dealt round-robin over the BLOCKS
@@ -439,7 +449,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
 
     // per-stage wall time (ns, %globaltimer) seen by thread 0 — the phases are grid-wide, so
     // one observer is representative
-    unsigned long long t_prev = 0, acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long t_prev = 0, acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     auto lap = [&](int slot) {
         if (tid == 0) {
             unsigned long long t;
@@ -454,6 +464,10 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
     for (uint32_t i = tid; i < 512u; i += nth) c.cnt->round_flags[i] = 0u;
     grid.sync();
 #endif
+#ifdef SFP_TILE_PROBE
+    for (uint32_t i = tid; i < 512u; i += nth) c.cnt->round_flags[i] = 0u;
+    grid.sync();
+#endif
     lap(-1);
     for (uint32_t s = 0; s < substeps; ++s) {
         stage_integrate(c, h, tid, nth);
@@ -462,6 +476,11 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
         stage_narrowphase<POLYS>(c, tid, nth);
         grid.sync();
         lap(5);
+        if (TILES) {
+            stage_tiles<false>(c, dyn_smem, s_toff, h, rest_threshold);
+            grid.sync();
+            lap(10);
+        }
         have = false;
 #ifdef SFP_PHASE_PROBE
         // development probe (scripts/phase_probe.py).  Per big position phase: the slowest and
@@ -549,6 +568,11 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
         stage_derive(c, inv_h, tid, nth);
         grid.sync();
         lap(7);
+        if (TILES) {
+            stage_tiles<true>(c, dyn_smem, s_toff, h, rest_threshold);
+            grid.sync();
+            lap(11);
+        }
         have = false;
         for (int col = next_bit(big, -1); col < 64; col = next_bit(big, col)) {
             if (have) solve_vel_pair(c, rec_k, rec, rec_lam, h, rest_threshold);
@@ -574,7 +598,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
         lap(9);
     }
     if (tid == 0) {
-        for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
+        for (int k = 4; k < 12; ++k) c.cnt->stage_cycles[k] = acc[k];
         c.cnt->stage_cycles[0] = (unsigned long long)__popcll(big);
 #ifdef SFP_PHASE_PROBE
         unsigned long long smax = 0, smin = 0;
@@ -724,7 +748,11 @@ struct SfpWorld {
     sfp::StateRec* d_state = nullptr;    // device staging, cap_bodies states
     uint32_t pin_cap = 0;
     int coop_max_colour = 0, coop_max_substep = 0, coop_max_substep_poly = 0, n_sm = 0;
-    int coop_max_flow = 0, coop_max_flow_poly = 0;
+    int coop_max_flow = 0, coop_max_flow_poly = 0, coop_max_tiles = 0, coop_max_tiles_poly = 0;
+    // ping-pong partners of the Ctx's pcol_sorted / pperm / jcol_sorted / jperm
+    uint32_t *d_pkeyB = nullptr, *d_ppermB = nullptr, *d_jkeyB = nullptr, *d_jpermB = nullptr;
+    int sort_passes = 1;  // radix passes over the (group, colour, class) key
+    uint32_t max_tiles = 0;
     bool has_polygons = false;
     SfpStats stats;
     std::string err;
@@ -782,6 +810,10 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.claim0, cb, bag));
     TRY(alloc_dev(w, &c.claim1, cb, bag));
     TRY(alloc_dev(w, &c.done, 2 * (size_t)cb, bag));
+    TRY(alloc_dev(w, &c.mask_i, cb, bag));
+    w->max_tiles = cb / SFP_TILE_MIN + 2u;
+    TRY(alloc_dev(w, &c.goff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
+    TRY(alloc_dev(w, &c.jgoff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
     TRY(alloc_dev(w, &c.ekey0, ce, bag));
     TRY(alloc_dev(w, &c.eval0, ce, bag));
     TRY(alloc_dev(w, &c.ekey1, ce, bag));
@@ -790,10 +822,13 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &c.poff, ce + 1, bag));
     TRY(alloc_dev(w, &c.pairs_raw, cp, bag));
     TRY(alloc_dev(w, &c.pairs, cp, bag));
+    TRY(alloc_dev(w, &c.pprio, cp, bag));
     TRY(alloc_dev(w, &c.pcol, cp, bag));
     TRY(alloc_dev(w, &c.unc, cp, bag));
     TRY(alloc_dev(w, &c.pcol_sorted, cp, bag));
     TRY(alloc_dev(w, &c.pperm, cp, bag));
+    TRY(alloc_dev(w, &w->d_pkeyB, cp, bag));
+    TRY(alloc_dev(w, &w->d_ppermB, cp, bag));
     TRY(alloc_dev(w, &c.ca, cp, bag));
     TRY(alloc_dev(w, &c.cb, cp, bag));
     TRY(alloc_dev(w, &c.cp0, cp, bag));
@@ -848,6 +883,8 @@ int ensure_joint_capacity(SfpWorld* w, uint32_t nj) {
     TRY(alloc_dev(w, &c.jcol_sorted, cj, bag));
     TRY(alloc_dev(w, &c.jperm, cj, bag));
     TRY(alloc_dev(w, &w->d_jext, cj, bag));
+    TRY(alloc_dev(w, &w->d_jkeyB, cj, bag));
+    TRY(alloc_dev(w, &w->d_jpermB, cj, bag));
     w->cap_joints = cj;
     // the radix histogram must cover the joint sort too
     if (radix_blocks(cj + 1) > w->hist_blocks) {
@@ -891,12 +928,12 @@ int resort_bodies(SfpWorld* w) {
     Ctx& c = w->ctx;
     cudaStream_t st = w->stream;
     const uint32_t gb = blocks_for(w, w->n);
-    k_tile_keys<<<gb, TPB, 0, st>>>(c, c.ekey1);
+    k_tile_keys<<<gb, TPB, 0, st>>>(c, c.ekey1, c.eval1);
     // four 8-bit passes, 1 -> 0 -> 1 -> 0 -> 1: the sorted order ends in eval1
     for (int pass = 0; pass < 4; ++pass) {
         const bool back = (pass & 1) != 0;
         const uint32_t* ki = back ? c.ekey0 : c.ekey1;
-        const uint32_t* vi = pass == 0 ? nullptr : (back ? c.eval0 : c.eval1);
+        const uint32_t* vi = back ? c.eval0 : c.eval1;
         uint32_t* ko = back ? c.ekey1 : c.ekey0;
         uint32_t* vo = back ? c.eval1 : c.eval0;
         CU(radix_pass(ki, vi, ko, vo, &w->d_cnt->n_bodies, w->cap_bodies, pass * 8, w->d_hist, st));
@@ -966,16 +1003,35 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
         k_colour_record<<<gp, TPB, 0, st>>>(c);
         w->launches += 1;
     }
-    // stable sort of the pairs by (colour, narrowphase class): an 8-bit key, one radix pass
-    CU(radix_pass(c.pcol, nullptr, c.pcol_sorted, c.pperm, &w->d_cnt->n_pairs, w->cap_pairs, 0,
-                  w->d_hist, st));
-    if (w->nj)
-        CU(radix_pass(c.jcol, nullptr, c.jcol_sorted, c.jperm, &w->d_cnt->n_joints, w->cap_joints,
-                      0, w->d_hist, st));
+    // stable sort of the pairs by (group, colour, narrowphase class): 8 bits without tiles (one
+    // radix pass), 8 more per 256 tiles.  The passes alternate between the Ctx's buffers and their
+    // partners such that the LAST one writes the Ctx's.
+    {
+        const uint32_t *ki = c.pcol, *vi = nullptr;
+        for (int pass = 0; pass < w->sort_passes; ++pass) {
+            const bool fin = ((w->sort_passes - 1 - pass) & 1) == 0;
+            uint32_t* ko = fin ? c.pcol_sorted : w->d_pkeyB;
+            uint32_t* vo = fin ? c.pperm : w->d_ppermB;
+            CU(radix_pass(ki, vi, ko, vo, &w->d_cnt->n_pairs, w->cap_pairs, pass * 8, w->d_hist, st));
+            ki = ko;
+            vi = vo;
+        }
+        if (w->nj) {
+            ki = c.jcol, vi = nullptr;
+            for (int pass = 0; pass < w->sort_passes; ++pass) {
+                const bool fin = ((w->sort_passes - 1 - pass) & 1) == 0;
+                uint32_t* ko = fin ? c.jcol_sorted : w->d_jkeyB;
+                uint32_t* vo = fin ? c.jperm : w->d_jpermB;
+                CU(radix_pass(ki, vi, ko, vo, &w->d_cnt->n_joints, w->cap_joints, pass * 8, w->d_hist, st));
+                ki = ko;
+                vi = vo;
+            }
+        }
+    }
     k_gather<<<blocks_for(w, (uint64_t)w->cap_pairs + w->nj), TPB, 0, st>>>(c);
     CU(cudaGetLastError());
-    w->launches += 3 + (w->nj ? 2 : 0) + (radix_blocks(w->cap_pairs) > RADIX_INLINE_BLOCKS ? 1 : 0) +
-                   ((w->nj && radix_blocks(w->cap_joints) > RADIX_INLINE_BLOCKS) ? 1 : 0);
+    w->launches += 1 + w->sort_passes * ((radix_blocks(w->cap_pairs) > RADIX_INLINE_BLOCKS ? 3 : 2) +
+                                         (w->nj ? (radix_blocks(w->cap_joints) > RADIX_INLINE_BLOCKS ? 3 : 2) : 0));
     if (mark) CU(cudaEventRecordWithFlags(w->ev_col, st, w->capturing ? cudaEventRecordExternal : 0));
     return SFP_OK;
 }
@@ -1004,11 +1060,22 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
             (uint32_t)((4ull * w->n + w->nj + SFP_SUB_TPB - 1) / SFP_SUB_TPB) + 1u);
         void* args[] = {&c, &h, &substeps, &rest_threshold};
         w->launches += 1;
+        if (c.tile_b) {
+            // one block per SM; every block walks its share of the tiles
+            const size_t smem = (size_t)c.tile_b * TILE_SMEM_PER_BODY;
+            const int cap = w->has_polygons ? w->coop_max_tiles_poly : w->coop_max_tiles;
+            const void* fn = w->has_polygons ? (const void*)k_substeps_coop<true, true>
+                                             : (const void*)k_substeps_coop<false, true>;
+            const unsigned tblocks = (unsigned)std::max<int>(w->n_sm, std::min<int>(cap, (int)c.n_tiles));
+            CU(cudaLaunchCooperativeKernel(fn, dim3(std::min<unsigned>(tblocks, (unsigned)cap)), dim3(SFP_SUB_TPB),
+                                           args, smem, w->stream));
+            return SFP_OK;
+        }
         if (w->has_polygons) {
             blocks = std::min<uint32_t>(blocks, (uint32_t)w->coop_max_substep_poly);
-            return launch_coop(w, (const void*)k_substeps_coop<true>, blocks, args, SFP_SUB_TPB);
+            return launch_coop(w, (const void*)k_substeps_coop<true, false>, blocks, args, SFP_SUB_TPB);
         }
-        return launch_coop(w, (const void*)k_substeps_coop<false>, blocks, args, SFP_SUB_TPB);
+        return launch_coop(w, (const void*)k_substeps_coop<false, false>, blocks, args, SFP_SUB_TPB);
     }
     Counters k;
     TRY(read_counters(w, &k));
@@ -1149,6 +1216,9 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
     else sfp::default_params(&p);
     if (!sfp::params_valid(p)) return SFP_E_INVALID;
     if (p.solver_order != SFP_ORDER_COLOUR) return SFP_E_INVALID;  // the device path is coloured GS
+    // the tile order lives in the persistent barrier kernel only
+    if ((p.flags & SFP_FLAG_TILES) && (p.flags & (SFP_FLAG_MULTI_KERNEL | SFP_FLAG_FLOW_SOLVE)))
+        return SFP_E_INVALID;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         fprintf(stderr, "libsfp_b200: no CUDA device — this library has no CPU fallback\n");
@@ -1187,11 +1257,11 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
         cudaSuccess)
         return fail("occupancy(colour)", e);
     w->coop_max_colour = std::max(1, per_sm) * w->n_sm;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<false>, SFP_SUB_TPB, 0)) !=
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<false, false>, SFP_SUB_TPB, 0)) !=
         cudaSuccess)
         return fail("occupancy(substeps)", e);
     w->coop_max_substep = std::max(1, per_sm) * w->n_sm;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<true>, SFP_SUB_TPB, 0)) !=
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<true, false>, SFP_SUB_TPB, 0)) !=
         cudaSuccess)
         return fail("occupancy(substeps, polygons)", e);
     w->coop_max_substep_poly = std::max(1, per_sm) * w->n_sm;
@@ -1203,6 +1273,20 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
         cudaSuccess)
         return fail("occupancy(flow, polygons)", e);
     w->coop_max_flow_poly = std::max(1, per_sm) * w->n_sm;
+    const size_t tile_smem = (size_t)SFP_TILE_MAX * TILE_SMEM_PER_BODY;
+    if ((e = cudaFuncSetAttribute(k_substeps_coop<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)tile_smem)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_substeps_coop<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)tile_smem)) != cudaSuccess)
+        return fail("cudaFuncSetAttribute(tiles)", e);
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<false, true>, SFP_SUB_TPB,
+                                                           tile_smem)) != cudaSuccess)
+        return fail("occupancy(tiles)", e);
+    w->coop_max_tiles = std::max(1, per_sm) * w->n_sm;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_substeps_coop<true, true>, SFP_SUB_TPB,
+                                                           tile_smem)) != cudaSuccess)
+        return fail("occupancy(tiles, polygons)", e);
+    w->coop_max_tiles_poly = std::max(1, per_sm) * w->n_sm;
     w->ctx.gx = p.gravity_x;
     w->ctx.gy = p.gravity_y;
     w->ctx.inv_cell = 1.0f / p.cell_size;
@@ -1296,6 +1380,12 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     w->stats.n_dynamic = ndyn;
     w->colour_age = 0;
     w->stepped = false;
+    // tiles of the solve order (sfp_math.h): after the first frame's re-sort the dynamic bodies
+    // are the indices [0, ndyn)
+    c.n_dyn = ndyn;
+    c.tile_b = (w->p.flags & SFP_FLAG_TILES) && ndyn ? sfp::tile_size(ndyn) : 0u;
+    c.n_tiles = c.tile_b ? (ndyn + c.tile_b - 1u) / c.tile_b : 0u;
+    w->sort_passes = c.n_tiles == 0u ? 1 : (c.n_tiles + 1u <= 256u ? 2 : 3);
     return SFP_OK;
 }
 
@@ -1481,9 +1571,15 @@ int fetch_pairs(SfpWorld* w, HostPairs* hp) {
     for (uint32_t i = 0; i < P; ++i)
         hp->ext[i] = make_uint2(hp->ext_of[hp->pairs[i].x], hp->ext_of[hp->pairs[i].y]);
     hp->colour.resize(P);
-    for (uint32_t col = 0; col < SFP_MAX_COLOURS; ++col)
-        for (uint32_t i = hp->k.pair_col_off[col]; i < hp->k.pair_col_off[col + 1] && i < P; ++i)
-            hp->colour[i] = col;
+    if (P) {
+        // colour as reported (sfp_math.h): from the sorted keys, interior colours + 64
+        std::vector<uint32_t> keys(P);
+        CU(cudaMemcpy(keys.data(), w->ctx.pcol_sorted, sizeof(uint32_t) * P, cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < P; ++i) {
+            const uint32_t col = (keys[i] >> SFP_TYPE_BITS) & 63u, group = (keys[i] >> 8) & 0xfffu;
+            hp->colour[i] = col + (group != w->ctx.n_tiles ? SFP_CLASS_INTERIOR : 0u);
+        }
+    }
     hp->order.resize(P);
     for (uint32_t i = 0; i < P; ++i) hp->order[i] = i;
     std::sort(hp->order.begin(), hp->order.end(), [&](uint32_t x, uint32_t y) {
@@ -1521,7 +1617,7 @@ int32_t sfp_get_colours(SfpWorld* w, uint32_t* pair_colours, uint32_t cap, uint3
     if (joint_colours && w->nj && w->stepped) {
         std::vector<uint32_t> jc(w->nj);
         CU(cudaMemcpy(jc.data(), w->ctx.jcol, sizeof(uint32_t) * w->nj, cudaMemcpyDeviceToHost));
-        for (uint32_t i = 0; i < jcap && i < w->nj; ++i) joint_colours[i] = jc[i];
+        for (uint32_t i = 0; i < jcap && i < w->nj; ++i) joint_colours[i] = jc[i] & 0xffu;
     }
     return SFP_OK;
 }
@@ -1690,7 +1786,7 @@ int32_t sfp_get_stats(SfpWorld* w, SfpStats* out) {
     w->stats.n_pairs = w->stepped ? k.n_pairs : 0u;
     w->stats.n_contacts = k.n_contacts;
     w->stats.n_manifolds = k.n_manifolds;
-    w->stats.n_colours = k.n_colours;
+    w->stats.n_colours = k.n_colours + k.n_colours_int;
     w->stats.colour_rounds = k.colour_rounds;
     w->stats.overflow |= k.overflow;
     w->stats.max_penetration = sfp::u2f(k.maxpen_bits);
@@ -1738,11 +1834,11 @@ int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]) {
 /* development aid (not part of include/sfp.h): ns per stage of the last substep kernel, as seen
  * by thread 0: [4] integrate [5] narrowphase [6] head position colours [7] derive
  * [8] head velocity colours [9] tail colours (both passes); [0] = index of the first tail colour */
-__attribute__((visibility("default"))) int32_t sfp_debug_stage_ns(SfpWorld* w, unsigned long long out[10]) {
+__attribute__((visibility("default"))) int32_t sfp_debug_stage_ns(SfpWorld* w, unsigned long long out[12]) {
     if (!w || !out) return SFP_E_INVALID;
     Counters k;
     TRY(read_counters(w, &k));
-    for (int i = 0; i < 10; ++i) out[i] = k.stage_cycles[i];
+    for (int i = 0; i < 12; ++i) out[i] = k.stage_cycles[i];
     return SFP_OK;
 }
 
