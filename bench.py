@@ -8,13 +8,17 @@ One "step" = one 60 Hz frame = 8 substeps over the whole scene.
           on): 100 000 mixed capsule / rounded-rect / circle bodies with friction + restitution.
           The pile is first stepped `--settle` frames (default 240, SURVEY.md §8d: timing window
           is the settled pile, contacts dominant); those frames are not timed.
-  N > 1   workload worlds512 (configs[4]): 1024 independent 512-body worlds PER GPU (8192 at
-          N = 8), world ranges partitioned over ranks, no data-path collective ("weak").
+  N > 1   workload worlds512 (configs[4]) AS STATED: 8192 independent 512-body worlds partitioned
+          over the N GPUs (8192 / N per GPU, "strong" scaling), world ranges partitioned over
+          ranks, no data-path collective.  The line carries its own N = 1 point (`n1_value`: rank 0
+          alone steps all 8192 worlds while the others wait) and `efficiency`.
+          --worlds-per-gpu W runs the weak variant (W worlds on every GPU) instead.
 Prints ONE JSON line on rank 0.  value = units all ranks processed / max-over-ranks device time.
 
 --impl reference: the reference's own CPU step cannot be built or run (tree not mounted, no Rust
-toolchain), so this arm times the CPU oracle (oracle/libsfp_ref.so, sequential
-Gauss-Seidel in reference order, "kind": "port") on the same config, on the box's host cores.
+toolchain), so this arm times the CPU oracle (oracle/libsfp_ref.so, "kind":
+"port") on the SAME config — the full 100 003-body pile, settled on the CPU — with all host
+threads in the solver loops.
 """
 from __future__ import annotations
 
@@ -32,7 +36,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 DT, SUBSTEPS = 1.0 / 60.0, 8
-WORLDS_PER_GPU, BODIES_PER_WORLD = 1024, 512
+TOTAL_WORLDS, BODIES_PER_WORLD = 8192, 512
 
 
 def peaks():
@@ -70,19 +74,36 @@ class ClockSampler:
         except Exception:
             pass
 
+    def _once(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                  "-i", str(self.index)], capture_output=True, text=True, timeout=10).stdout
+            parts = [x.strip() for x in out.strip().split(",")]
+            return parts if len(parts) >= 6 else None
+        except Exception:
+            return None
+
     def __enter__(self):
+        # a sample right before the timed region (the GPU is busy with the warm-up), the stream
+        # during it, one right after: a region shorter than the 50 ms period is still bracketed
+        self.before = self._once()
         self._t.start()
         time.sleep(0.25)  # let the first samples arrive before the timed region starts
         self.rows.clear()
         return self
 
     def __exit__(self, *a):
+        self.after = self._once()
         try:
             if self._proc:
                 self._proc.terminate()
         except Exception:
             pass
         self._t.join(timeout=3)
+        self.during = len(self.rows)
+        for r in (getattr(self, "before", None), self.after):
+            if r:
+                self.rows.append(r)
 
     def summary(self):
         if not self.rows:
@@ -91,7 +112,9 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower() == "active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "samples_during": getattr(self, "during", 0),
+                "note": "streamed every 50 ms during the timed region, plus one sample right before "
+                        "and one right after it"}
 
 
 def ncu_traffic(workload):
@@ -111,6 +134,44 @@ def b_alg(n, pairs, contacts, joints, substeps=SUBSTEPS, whole_step=True):
     if whole_step:
         b += (84.0 + 24.0 * p) / substeps
     return b
+
+
+def stage_rooflines(n, st, br_ms, stage_ns, peak, substeps=SUBSTEPS):
+    """Algorithmic-bytes fraction of the measured HBM peak per stage of one frame (SURVEY.md §8a/d:
+    every stage reads its inputs once and writes its outputs once).  br_ms: CUDA-event times of
+    broadphase / colouring (ms per frame); stage_ns: sfp_last_step_stage_ns (ns per frame)."""
+    p, c, j = st["n_pairs"] / n, st["n_contacts"] / n, st["n_joints"] / n
+    per_frame = {  # bytes per body per FRAME
+        "broadphase": 84.0 + 8.0 * p,               # A2: 48 in + 8 keys + 16 sort + 12 ranges + 8 p out
+        "colouring": 16.0 * p,                      # A8: pairs in, colour-sorted pairs out
+        "integrate": 88.0 * substeps,               # A3
+        "narrowphase": (72.0 * p + 48.0 * c) * substeps,        # A4
+        "position": (168.0 * c + 116.0 * j) * substeps,         # A5 + A6
+        "derive": 48.0 * substeps,                  # A7 i
+        "velocity": 128.0 * c * substeps,           # A7 ii
+    }
+    secs = {"broadphase": br_ms["broadphase"] * 1e-3, "colouring": br_ms["colour"] * 1e-3}
+    small = stage_ns.get("small_colours", 0) * 1e-9  # both passes' small colours: split evenly
+    for k in ("integrate", "narrowphase", "position", "derive", "velocity"):
+        secs[k] = stage_ns[k] * 1e-9 + (0.5 * small if k in ("position", "velocity") else 0.0)
+    out = {}
+    for k, b in per_frame.items():
+        if secs[k] > 0:
+            gbs = b * n / secs[k] / 1e9
+            out[k] = {"us_per_frame": secs[k] * 1e6, "algorithmic_gbytes_per_s": gbs, "frac": gbs / peak}
+    return out
+
+
+def shuffle_scene(bodies, joints, seed=20261107):
+    """the same scene with the body array in a random order (joints re-indexed)"""
+    perm = np.random.default_rng(seed).permutation(len(bodies))
+    inv = np.empty_like(perm)
+    inv[perm] = np.arange(len(bodies))
+    j = joints.copy()
+    if len(j):
+        j["body_a"] = inv[joints["body_a"]]
+        j["body_b"] = inv[joints["body_b"]]
+    return bodies[perm], j
 
 
 def make_scene(workload: str):
@@ -170,6 +231,7 @@ def run_single(args, rank, world_size):
     barrier(world_size)
     torch.cuda.synchronize()
     t_dev = t_sub = t_bp = t_col = 0.0
+    stage_acc = {}
     with ClockSampler(torch.cuda.current_device()) as clk:
         t0 = time.perf_counter()
         for _ in range(args.steps):
@@ -178,6 +240,8 @@ def run_single(args, rank, world_size):
             t_sub += br["substeps"]
             t_bp += br["broadphase"]
             t_col += br["colour"]
+            for k, v in w.last_step_stage_ns().items():
+                stage_acc[k] = stage_acc.get(k, 0) + v / args.steps
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0
     barrier(world_size)
@@ -229,6 +293,8 @@ def run_single(args, rank, world_size):
             "note": "algorithmic bytes = (136 + 72 p + 344 c + 116 j) * N * S, SURVEY.md §8d; "
                     "the kernel is grid-sync latency bound, not bandwidth bound (DESIGN.md)",
         },
+        "roofline_stages": stage_rooflines(n, st, {"broadphase": t_bp / args.steps, "colour": t_col / args.steps},
+                                           stage_acc, peak),
         "roofline_whole_step": {"achieved": bytes_step / (t_dev / args.steps * 1e-3) / 1e9,
                                 "peak": peak, "unit": "GB/s",
                                 "frac": bytes_step / (t_dev / args.steps * 1e-3) / 1e9 / peak},
@@ -254,7 +320,10 @@ def run_single(args, rank, world_size):
         # they are parity-test cases first, these lines are context for the headline
         del w
         out["other_configs"] = {name: quick_config(name, args) for name in ("circles10k", "ropes2k")}
-        out["other_configs"]["worlds512_1gpu"] = quick_worlds(args)
+        out["other_configs"]["worlds512_8192_1gpu"] = quick_worlds(args)
+        # the same pile uploaded in a random body order (the library re-sorts internally)
+        out["shuffled_order"] = quick_config(args.workload, args, shuffle=True)
+        out["shuffled_order"]["vs_spawn_order"] = out["shuffled_order"]["ms_per_step"] / (t_dev / args.steps)
         if not args.no_scale_point:
             # the scale at which HBM bandwidth, not phase latency, bounds
             # the step (state + pair data several times the L2)
@@ -262,12 +331,14 @@ def run_single(args, rank, world_size):
     return out
 
 
-def quick_config(name, args, frames=30):
+def quick_config(name, args, frames=30, shuffle=False):
     import torch
 
     import starframe_b200 as sf
 
     bodies, joints = make_scene(name)
+    if shuffle:
+        bodies, joints = shuffle_scene(bodies, joints)
     w = sf.World(sf.product_api(), device=torch.cuda.current_device())
     w.upload_bodies(bodies)
     w.set_joints(joints)
@@ -294,37 +365,50 @@ def scale_point(args, name="shelves4000000", settle=200, frames=10):
 
     bodies, joints = make_scene(name)
     n = len(bodies)
-    w = sf.World(sf.product_api(), device=torch.cuda.current_device())
-    w.upload_bodies(bodies)
-    for _ in range(settle):
-        w.step(DT, SUBSTEPS)
-    w.sync()
-    t = t_sub = 0.0
-    for _ in range(frames):
-        w.step(DT, SUBSTEPS)
-        w.sync()
-        br = w.last_step_breakdown_ms()
-        t += br["step"]
-        t_sub += br["substeps"]
-    st = w.stats()
     peak, _ = peaks()
+
+    def run(b, j):
+        w = sf.World(sf.product_api(), device=torch.cuda.current_device())
+        w.upload_bodies(b)
+        for _ in range(settle):
+            w.step(DT, SUBSTEPS)
+        w.sync()
+        acc = {"step": 0.0, "substeps": 0.0, "broadphase": 0.0, "colour": 0.0}
+        stages = {}
+        for _ in range(frames):
+            w.step(DT, SUBSTEPS)
+            w.sync()
+            for k, v in w.last_step_breakdown_ms().items():
+                acc[k] += v / frames
+            for k, v in w.last_step_stage_ns().items():
+                stages[k] = stages.get(k, 0) + v / frames
+        return acc, stages, w.stats()
+
+    acc, stages, st = run(bodies, joints)
     b_sub = b_alg(n, st["n_pairs"], st["n_contacts"], 0, whole_step=False) * n * SUBSTEPS
     b_all = b_alg(n, st["n_pairs"], st["n_contacts"], 0) * n * SUBSTEPS
-    return {"workload": name, "bodies": n, "value": n * SUBSTEPS * frames / (t * 1e-3),
-            "unit": "body-substeps/s", "ms_per_step": t / frames,
-            "state_mbytes": n * 88 / 1e6, "pairs_per_body": st["n_pairs"] / n,
-            "contacts_per_body": st["n_contacts"] / n, "colours": st["n_colours"],
-            "roofline_substep_kernel_frac": b_sub / (t_sub / frames * 1e-3) / 1e9 / peak,
-            "roofline_whole_step_frac": b_all / (t / frames * 1e-3) / 1e9 / peak}
+    out = {"workload": name, "bodies": n, "value": n * SUBSTEPS / (acc["step"] * 1e-3),
+           "unit": "body-substeps/s", "ms_per_step": acc["step"],
+           "state_mbytes": n * 88 / 1e6, "pairs_per_body": st["n_pairs"] / n,
+           "contacts_per_body": st["n_contacts"] / n, "colours": st["n_colours"],
+           "breakdown_ms": {"broadphase": acc["broadphase"], "colouring": acc["colour"],
+                            "substep_kernel": acc["substeps"]},
+           "roofline_substep_kernel_frac": b_sub / (acc["substeps"] * 1e-3) / 1e9 / peak,
+           "roofline_whole_step_frac": b_all / (acc["step"] * 1e-3) / 1e9 / peak,
+           "roofline_stages": stage_rooflines(n, st, acc, stages, peak)}
+    acc2, _, _ = run(*shuffle_scene(bodies, joints))
+    out["shuffled_order"] = {"ms_per_step": acc2["step"], "vs_spawn_order": acc2["step"] / acc["step"]}
+    return out
 
 
-def quick_worlds(args, frames=20):
+def quick_worlds(args, frames=10, nw=None):
+    """config 5's N = 1 point: all 8192 worlds on one GPU"""
     import torch
 
     import starframe_b200 as sf
     from starframe_b200 import scenes
 
-    nw = args.worlds_per_gpu
+    nw = nw or (args.worlds_per_gpu or TOTAL_WORLDS)
     b = sf.Batch(sf.product_api(), nw, BODIES_PER_WORLD, device=torch.cuda.current_device())
     b.upload(scenes.worlds(nw, BODIES_PER_WORLD))
     for _ in range(args.settle):
@@ -338,7 +422,7 @@ def quick_worlds(args, frames=20):
     n = nw * BODIES_PER_WORLD
     return {"bodies": n, "worlds": nw, "value": n * SUBSTEPS * frames / (t * 1e-3),
             "unit": "body-substeps/s", "ms_per_step": t / frames,
-            "note": "the per-GPU share of the N>1 workload, for the scaling curve's N=1 point"}
+            "note": "BASELINE.json configs[4] on ONE GPU: the N = 1 point of the strong-scaling curve"}
 
 
 def cpu_baseline_single(bodies, joints, settled_state, frames):
@@ -375,14 +459,26 @@ def run_worlds(args, rank, world_size):
     import starframe_b200 as sf
     from starframe_b200 import scenes
 
-    nw = args.worlds_per_gpu
-    bodies = scenes.worlds(nw, BODIES_PER_WORLD, first_world=world_range(rank, nw).start)
+    # config 5 as BASELINE.json states it: 8192 worlds partitioned over the GPUs (strong scaling);
+    # --worlds-per-gpu W: W worlds on every GPU instead (weak scaling)
+    strong = args.worlds_per_gpu is None
+    total = TOTAL_WORLDS if strong else args.worlds_per_gpu * world_size
+    wr = world_range(rank, world_size, total)
+    nw = len(wr)
+    bodies = scenes.worlds(nw, BODIES_PER_WORLD, first_world=wr.start)
     api = sf.product_api()
     b = sf.Batch(api, nw, BODIES_PER_WORLD, device=torch.cuda.current_device())
     b.upload(bodies)
     for _ in range(args.settle):
         b.step(DT, SUBSTEPS)
     b.sync()
+    # the curve's own N = 1 point, measured in the same run: rank 0 alone steps the single-GPU
+    # workload (all worlds when strong, one GPU's share when weak) while the others wait
+    n1 = None
+    if world_size > 1:
+        if rank == 0:
+            n1 = quick_worlds(args, frames=10, nw=total if strong else nw)
+        barrier(world_size)
     for _ in range(args.warmup):
         b.step(DT, SUBSTEPS)
         b.sync()
@@ -422,10 +518,18 @@ def run_worlds(args, rank, world_size):
     return {
         "metric": "body-substeps/sec", "value": value, "unit": "body-substeps/s",
         "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": t_dev_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": t_dev_max / args.steps, "higher_is_better": True,
+        "scaling": "strong" if strong else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"worlds512: {nw} independent {BODIES_PER_WORLD}-body worlds per GPU "
-                               f"({nw * world_size} total), partitioned by world index",
+        "n1_value": (n1["value"] if n1 else (value if world_size == 1 else None)),
+        "n1_ms_per_step": (n1["ms_per_step"] if n1 else None),
+        "per_gpu_value": value / world_size,
+        "efficiency": (value / (world_size * n1["value"]) if n1 else (1.0 if world_size == 1 else None)),
+        "efficiency_note": "value / (n_gpus * n1_value); n1_value = rank 0 alone stepping the single-GPU "
+                           "workload of this curve in this run (all 8192 worlds when strong)",
+        "config": {"workload": f"worlds512 ({'strong' if strong else 'weak'}): {total} independent "
+                               f"{BODIES_PER_WORLD}-body worlds over {world_size} GPU(s), {nw} on rank 0, "
+                               f"partitioned by world index",
                    "bodies": int(tot[2]), "dt": "1/60", "substeps": SUBSTEPS,
                    "settle_frames": args.settle, "pairs_per_body": tot[0] / tot[2],
                    "contacts_per_body": tot[1] / tot[2],
@@ -466,17 +570,11 @@ def run_reference(args, rank, world_size):
     if args.workload != "worlds512":
         # All host threads: the oracle's colour-order step runs each colour's constraints (and the
         # per-body / per-pair loops) on SFP_REF_THREADS threads, with the same bits as one thread
-        # (scripts/oracle_threads.py); its broadphase and colouring stay sequential.  Sample: a
-        # narrower pile from the same generator with the same depth (100 rows), so per-body work
-        # matches the full scene.
+        # (scripts/oracle_threads.py); its broadphase and colouring stay sequential.  The FULL
+        # scene of the GPU arm, settled on the CPU (a couple of minutes for the 100 k pile).
         os.environ["SFP_REF_THREADS"] = str(cores)
-        if args.workload == "pile100k":
-            n_sample = 30000
-            bodies, joints = scenes.mixed_pile(n_sample, cols=300)
-            what = f"{n_sample}-body slice of pile100k (same generator, 300 columns x 100 rows)"
-        else:
-            bodies, joints = make_scene(args.workload)
-            what = f"the full {args.workload} scene"
+        bodies, joints = make_scene(args.workload)
+        what = f"the full {args.workload} scene ({len(bodies)} bodies, the GPU arm's config)"
         n = len(bodies)
         ref = sf.World(api, solver_order=_ffi.ORDER_COLOUR)
         ref.upload_bodies(bodies)
@@ -499,7 +597,8 @@ def run_reference(args, rank, world_size):
                   f"contacts/body {st['n_contacts'] / n:.2f}); host has {cores} logical cores")
         workload, steps = args.workload, done
     else:
-        nw = min(args.worlds_per_gpu * world_size, 4 * cores)
+        total = TOTAL_WORLDS if args.worlds_per_gpu is None else args.worlds_per_gpu * world_size
+        nw = min(total, 4 * cores)
         worlds = scenes.worlds(nw, BODIES_PER_WORLD)
         ws = []
         for k in range(nw):
@@ -520,16 +619,17 @@ def run_reference(args, rank, world_size):
         n = nw * BODIES_PER_WORLD
         value = n * SUBSTEPS * frames / s
         used = cores
-        sample = (f"{nw} of the {args.worlds_per_gpu * world_size} worlds, settled {args.settle} "
+        sample = (f"{nw} of the {total} worlds (every world is the same amount of work), settled {args.settle} "
                   f"frames on the CPU, then {frames} timed frames; one world per task on {cores} "
                   f"threads")
         workload, steps = "worlds512", frames
     return {
         "impl": "reference", "metric": "body-substeps/sec", "value": value,
         "unit": "body-substeps/s", "n_gpus": world_size, "steps": steps, "warmup": args.warmup,
-        "ms_per_step": s / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": s / steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if (workload == "worlds512" and args.worlds_per_gpu is None) else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload, "dt": "1/60", "substeps": SUBSTEPS,
+        "config": {"workload": workload, "bodies": n, "dt": "1/60", "substeps": SUBSTEPS,
                    "settle_frames": args.settle},
         "cpu_baseline": {"value": value, "unit": "body-substeps/s", "cores": used, "kind": "port",
                          "sample": sample},
@@ -577,9 +677,12 @@ def allreduce_sum(xs, world_size):
     return [float(v) for v in t.tolist()]
 
 
-def world_range(rank, worlds_per_rank):
-    """world indices owned by `rank`: contiguous block partition (no overlap, no gap)"""
-    return range(rank * worlds_per_rank, (rank + 1) * worlds_per_rank)
+def world_range(rank, world_size, total):
+    """world indices owned by `rank`: contiguous block partition of [0, total) (no overlap, no
+    gap; the first total % world_size ranks own one world more)"""
+    base, extra = divmod(total, world_size)
+    start = rank * base + min(rank, extra)
+    return range(start, start + base + (1 if rank < extra else 0))
 
 
 def main():
@@ -590,7 +693,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None)
     ap.add_argument("--settle", type=int, default=240)
-    ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
+    ap.add_argument("--worlds-per-gpu", type=int, default=None,
+                    help="weak scaling: this many worlds on every GPU (default: 8192 / N, strong)")
     ap.add_argument("--cpu-frames", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-configs", action="store_true")

@@ -26,6 +26,8 @@ pub const SFP_JOINT_DISTANCE: u32 = 0;
 pub const SFP_JOINT_ROPE: u32 = 1;
 pub const SFP_FLAG_BROADPHASE_EVERY_SUBSTEP: u32 = 1;
 pub const SFP_FLAG_MULTI_KERNEL: u32 = 2;
+pub const SFP_FLAG_FLOW_SOLVE: u32 = 4;
+pub const SFP_FLAG_TILES: u32 = 8;
 
 #[repr(C)]
 #[derive(Clone, Copy)]
@@ -222,6 +224,7 @@ extern "C" {
     pub fn sfp_free_host_states(p: *mut SfpBodyState) -> i32;
     pub fn sfp_last_step_ms(w: *mut SfpWorld, ms: *mut f32) -> i32;
     pub fn sfp_last_step_breakdown_ms(w: *mut SfpWorld, out: *mut f32) -> i32; // float[4]
+    pub fn sfp_last_step_stage_ns(w: *mut SfpWorld, out: *mut u64) -> i32; // uint64_t[6]
     pub fn sfp_backend() -> *const c_char;
     // ---- batched independent worlds ----
     pub fn sfp_batch_create(params: *const SfpParams, n_worlds: u32, bodies_per_world: u32,

@@ -214,7 +214,12 @@ SFP_API int32_t sfp_create(const SfpParams* params, SfpWorld** out);
 SFP_API int32_t sfp_destroy(SfpWorld* w);
 
 /* Replaces: the scene-graph -> physics sync that hands every `Body` + `Collider` to the
- * step (AoS in, converted to SoA device buffers inside).  Replaces all bodies. */
+ * step (AoS in, converted to SoA device buffers inside).  Replaces all bodies.
+ * Limit: a collider whose box (plus aabb_margin) covers more than 16384 broadphase cells, or 4096
+ * or more cells along one axis — at the default cell_size of 0.5 m a floor of more than 8192 m^2
+ * or longer than 2048 m — is refused here with SFP_E_INVALID (it would take no part in the
+ * broadphase): split it into several static bodies or raise cell_size.  A DYNAMIC body that
+ * grows that large while stepping (a runaway) raises overflow bit 16 -> SFP_E_CAPACITY. */
 SFP_API int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n);
 
 /* Replaces: the vertex data of the reference's convex-polygon colliders (reference file:line
@@ -324,10 +329,13 @@ SFP_API const char* sfp_batch_last_error(SfpBatch* b);
  * substeps and writes the resulting states to out[0..n).  Calls no cudaMalloc / cudaFree /
  * allocating routine, on the device or on the heap: every intermediate lives in a fixed
  * SFP_NOALLOC_SCRATCH_BYTES device array that each GPU loading the library holds until exit.
- * Result: bit-identical to sfp_batch_* on one world.  Worlds beyond the limits are refused with
- * SFP_E_CAPACITY.  The first call on a device does a one-off set-up (make it before any stream
- * capture); calls sharing a GPU must not overlap in time (they share the array); the call is
- * synchronous.  err (optional, err_cap bytes) receives a message on failure. */
+ * Result: bit-identical to sfp_batch_* on one world, including the pair capacity (12 n + 256, or
+ * params->max_pairs up to 12 544).  Worlds beyond the limits are refused with SFP_E_CAPACITY.
+ * The first call on a device does a one-off set-up (make it before any stream capture).  Calls
+ * that name the SAME GPU must not overlap in time (they share the device array and that GPU's
+ * host staging slot); calls on different GPUs may.  The call is synchronous and works on the
+ * calling thread's cudaStreamPerThread.  err (optional, err_cap bytes) receives a message on
+ * failure. */
 #define SFP_NOALLOC_MAX_BODIES 1024u
 #define SFP_NOALLOC_SCRATCH_BYTES (2304u * 1024u)
 SFP_API int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodies,
@@ -343,6 +351,13 @@ SFP_API int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms);
  * out[0] = whole step, out[1] = broadphase (AABBs, cell sort, pair emission),
  * out[2] = colouring + bucketing by colour, out[3] = the persistent substep kernel. */
 SFP_API int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]);
+
+/* wall time of the stages INSIDE the persistent substep kernel of the last sfp_step, in
+ * nanoseconds summed over the frame's substeps, as seen by one thread (%globaltimer; the stages
+ * are grid-wide phases, so one observer is representative): out[0] integrate, out[1] narrowphase,
+ * out[2] position solve (all colour phases), out[3] velocity derivation, out[4] velocity solve,
+ * out[5] the small colours of both passes (run by one block inside one phase). */
+SFP_API int32_t sfp_last_step_stage_ns(SfpWorld* w, uint64_t out[6]);
 
 /* library identification: "cuda-sm_100a" or "cpu-oracle" */
 SFP_API const char* sfp_backend(void);

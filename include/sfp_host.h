@@ -198,6 +198,20 @@ inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4
     mat->w = u2f((uint32_t)d.category | ((uint32_t)d.mask << 16));
 }
 
+/* Does the collider, as uploaded, fit the broadphase grid?  A body whose box (tight box +
+ * aabb_margin) covers more than SFP_MAX_CELLS_PER_BODY cells, or 4096 or more cells along one
+ * axis, would be left out of the broadphase (cell_range() refuses it: it would produce no pairs
+ * and bodies would fall through it).  For a floor or a wall that is a property of the UPLOAD —
+ * statics do not move — so the upload rejects it with a message instead of letting the step
+ * raise the runaway flag later.  At the default 0.5 m cell: 8192 m^2 of box area at most, and
+ * less than 2048 m along either axis. */
+inline bool body_fits_grid(f4 pose, f4 shape, const SfpParams& p) {
+    f4 zero = {0.0f, 0.0f, 0.0f, 0.0f};
+    f4 bb = body_aabb(pose, zero, shape, p.aabb_margin, 0.0f, 0.0f);
+    int x0, y0, x1, y1;
+    return cell_range(bb, 1.0f / p.cell_size, &x0, &y0, &x1, &y1);
+}
+
 static_assert(sizeof(StateRec) == sizeof(SfpBodyState), "StateRec mirrors SfpBodyState");
 
 inline SfpBodyState state_from_records(f4 pose, f4 vel) {

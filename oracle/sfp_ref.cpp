@@ -623,6 +623,11 @@ int32_t sfp_ref_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n
                        &w->polys);
         w->prev[i] = w->pose[i];
         ndyn += is_dynamic(*w, i) ? 1u : 0u;
+        if (!body_fits_grid(w->pose[i], w->shape[i], w->p)) {
+            w->err = "body " + std::to_string(i) + " spans more than 16384 broadphase cells (or 4096 along one axis) at this cell_size: split it or raise cell_size";
+            w->n = 0;
+            return SFP_E_INVALID;
+        }
     }
     w->stats.n_bodies = n;
     w->stats.n_dynamic = ndyn;

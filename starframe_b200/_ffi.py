@@ -113,7 +113,7 @@ PRODUCT_SYMBOLS = [
     "alloc_host_states", "free_host_states",
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_step_host", "batch_set_joints", "batch_set_polygons", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
-    "last_step_breakdown_ms", "backend", "step_small_noalloc",
+    "last_step_breakdown_ms", "last_step_stage_ns", "backend", "step_small_noalloc",
 ]
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
@@ -185,6 +185,7 @@ class Api:
             "step_host": [vp, vp, vp, u32, f32, u32],
             "last_step_ms": [vp, C.POINTER(f32)],
             "last_step_breakdown_ms": [vp, vp],
+            "last_step_stage_ns": [vp, vp],
             "brute_pairs": [vp, f32, vp, u32, C.POINTER(u32)],
             "batch_create": [vp, u32, u32, C.POINTER(vp)],
             "batch_destroy": [vp],
@@ -397,6 +398,13 @@ class World:
         self._check(self.api.fn("last_step_breakdown_ms")(self.h, _ptr(out)), "breakdown")
         return {"step": float(out[0]), "broadphase": float(out[1]), "colour": float(out[2]),
                 "substeps": float(out[3])}
+
+    def last_step_stage_ns(self) -> dict:
+        """ns per stage inside the persistent substep kernel of the last step (whole frame)"""
+        out = np.zeros(6, dtype=np.uint64)
+        self._check(self.api.fn("last_step_stage_ns")(self.h, _ptr(out)), "stage_ns")
+        names = ("integrate", "narrowphase", "position", "derive", "velocity", "small_colours")
+        return {k: int(v) for k, v in zip(names, out)}
 
     def brute_pairs(self, dt: float) -> np.ndarray:
         n = C.c_uint32(0)

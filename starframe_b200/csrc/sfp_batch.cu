@@ -20,8 +20,10 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -681,6 +683,10 @@ int32_t sfp_batch_upload(SfpBatch* b, const SfpBodyDesc* bodies) {
         sfp::body_from_desc(bodies[i], &pose[i], &vel[i], &b->h_minv[i], &shape[i], &mat[i], &b->polys);
         b->has_polygons |= (bodies[i].shape & 0xffu) == SFP_SHAPE_POLYGON;
         if (b->h_minv[i].x > 0.0f || b->h_minv[i].y > 0.0f) b->n_dynamic[i / b->bpw] += 1;
+        if (!sfp::body_fits_grid(pose[i], shape[i], b->p)) {
+            b->err = "body " + std::to_string(i) + " spans more than 16384 broadphase cells (or 4096 along one axis) at this cell_size: split it or raise cell_size";
+            return SFP_E_INVALID;
+        }
     }
     Ctx& c = b->ctx.base;
     BCU(cudaStreamSynchronize(b->stream));
@@ -1020,8 +1026,10 @@ int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms) {
  *
  * The array: g_small_scratch below, SFP_NOALLOC_SCRATCH_BYTES (about 2.2 MiB) of device memory
  * on every GPU that loads the library, held until the process exits.  It bounds the world size:
- * n <= SFP_NOALLOC_MAX_BODIES (1024) and at most 12 n + 256 candidate pairs; larger requests are
- * refused with SFP_E_CAPACITY and a message, nothing is truncated silently.
+ * n <= SFP_NOALLOC_MAX_BODIES (1024) and at most 12 n + 256 candidate pairs (params->max_pairs
+ * if given, up to 12 544) — the same pair capacity sfp_batch_create gives such a world, so the
+ * two also agree on WHEN a dense world overflows; larger requests are refused with
+ * SFP_E_CAPACITY and a message, nothing is truncated silently.
  *
  * In host code the array's name is only a stand-in for the symbol, not a device address, so the
  * address is looked up with cudaGetSymbolAddress — once per device, with that device current,
@@ -1031,10 +1039,13 @@ int32_t sfp_batch_last_step_ms(SfpBatch* b, float* ms) {
  * All calls on one GPU share the array and it keeps whatever the previous call left in it.
  * What has to start from zero (the counters with their sticky overflow bits; the colour table
  * is re-zeroed by the kernel itself every frame) is cleared at the start of each call; the
- * rest is fully rewritten before it is read.  Two calls that overlap in time on the same GPU
- * — from two threads, or two processes' worth of streams — would trample each other's
- * intermediates: serialise them.  The call itself is synchronous (it returns after the
- * result has been copied back) and uses the default stream.
+ * rest is fully rewritten before it is read.  Two calls that overlap in time on the SAME GPU —
+ * from two threads of this process — would trample each other's intermediates on the device
+ * and in that GPU's host staging slot: serialise them.  Calls on DIFFERENT GPUs may run at the
+ * same time: the host staging area below has one slot per device and the per-device set-up is
+ * done under std::call_once.  The call is synchronous (it returns after the result has been
+ * copied back); its copies and launches go to the calling thread's cudaStreamPerThread, not to
+ * the legacy default stream, so it does not serialise against the host's other streams.
  *
  * It performs: host-side conversion of `bodies` into a fixed host staging area, H2D copies into
  * the array, `frames` launches of the frame kernel (the first one colours from scratch, the
@@ -1079,13 +1090,16 @@ static_assert(NA_SCRATCH_BYTES <= (size_t)SFP_NOALLOC_SCRATCH_BYTES, "sfp.h stat
 // the one fixed scratch area (see the comment above)
 static __device__ __align__(256) unsigned char g_small_scratch[SFP_NOALLOC_SCRATCH_BYTES];
 
-// per-device set-up state and the host staging area (fixed size: no heap)
+// per-device set-up state and the host staging area (fixed size: no heap), one slot per device
 constexpr int NA_MAX_DEVICES = 64;
-unsigned char* g_small_scratch_addr[NA_MAX_DEVICES];  // device address of g_small_scratch
-bool g_small_ready[NA_MAX_DEVICES];
-sfp::f4 na_h_pose[NA_MAX_BODIES], na_h_vel[NA_MAX_BODIES], na_h_shape[NA_MAX_BODIES],
-    na_h_mat[NA_MAX_BODIES];
-sfp::f2 na_h_minv[NA_MAX_BODIES];
+struct NaSlot {
+    std::once_flag once;
+    std::atomic<int> setup_rc{-1};    // cudaError_t of the set-up, -1 = not run yet
+    unsigned char* scratch = nullptr;  // device address of g_small_scratch ON THIS DEVICE
+    sfp::f4 pose[NA_MAX_BODIES], vel[NA_MAX_BODIES], shape[NA_MAX_BODIES], mat[NA_MAX_BODIES];
+    sfp::f2 minv[NA_MAX_BODIES];
+};
+NaSlot g_na[NA_MAX_DEVICES];
 
 void na_msg(char* err, uint32_t cap, const char* what, const char* detail) {
     if (err && cap) snprintf(err, cap, "%s%s%s", what, detail ? ": " : "", detail ? detail : "");
@@ -1134,16 +1148,34 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
             return SFP_E_CUDA;                                      \
         }                                                           \
     } while (0)
-    NCU(cudaSetDevice(p.device));
-    if (!g_small_ready[p.device]) {
-        // once per device, with that device current: the symbol's address ON THIS DEVICE
-        unsigned char* ptr = nullptr;
-        NCU(cudaGetSymbolAddress((void**)&ptr, g_small_scratch));
-        NCU(raise_batch_smem_limit(p.device, (size_t)NA_MAX_BODIES * 80u));
-        g_small_scratch_addr[p.device] = ptr;
-        g_small_ready[p.device] = true;
+    const uint32_t pair_cap = p.max_pairs ? p.max_pairs : 12u * n + 256u;
+    if (pair_cap > NA_PAIR_CAP) {
+        if (err && err_cap)
+            snprintf(err, err_cap,
+                     "sfp_step_small_noalloc: max_pairs %u requested, the fixed scratch area holds at "
+                     "most %u candidate pairs",
+                     pair_cap, NA_PAIR_CAP);
+        return SFP_E_CAPACITY;
     }
-    unsigned char* base = g_small_scratch_addr[p.device];
+    NCU(cudaSetDevice(p.device));
+    NaSlot& slot = g_na[p.device];
+    // once per device, with that device current: the symbol's address ON THIS DEVICE and the
+    // kernel's shared-memory limit (two threads naming the same device for the first time: one
+    // runs the set-up, the other waits for it)
+    std::call_once(slot.once, [&] {
+        unsigned char* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_small_scratch);
+        if (e == cudaSuccess) e = raise_batch_smem_limit(p.device, (size_t)NA_MAX_BODIES * 80u);
+        slot.scratch = ptr;
+        slot.setup_rc.store((int)e, std::memory_order_release);
+    });
+    if (slot.setup_rc.load(std::memory_order_acquire) != (int)cudaSuccess) {
+        na_msg(err, err_cap, "sfp_step_small_noalloc: set-up of the scratch area failed",
+               cudaGetErrorString((cudaError_t)slot.setup_rc.load()));
+        return SFP_E_CUDA;
+    }
+    unsigned char* base = slot.scratch;
+    const cudaStream_t st = cudaStreamPerThread;  // a constant handle: nothing is created
 
     BatchCtx ctx;
     std::memset(&ctx, 0, sizeof(ctx));
@@ -1180,7 +1212,7 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
     c.vel_expand = p.vel_expand;
     c.contact_margin = p.contact_margin;
     ctx.bpw = n;
-    ctx.pair_cap = NA_PAIR_CAP;
+    ctx.pair_cap = pair_cap;
     ctx.n_worlds = 1;
     ctx.counters = reinterpret_cast<Counters*>(base + NA_OFF_CNT);
     ctx.scratch = reinterpret_cast<uint32_t*>(base + NA_OFF_CNTOFF);
@@ -1188,18 +1220,26 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
     unsigned long long* tab[2] = {reinterpret_cast<unsigned long long*>(base + NA_OFF_TAB0),
                                   reinterpret_cast<unsigned long long*>(base + NA_OFF_TAB1)};
 
-    for (uint32_t i = 0; i < n; ++i)
-        sfp::body_from_desc(bodies[i], &na_h_pose[i], &na_h_vel[i], &na_h_minv[i], &na_h_shape[i],
-                            &na_h_mat[i]);
-    NCU(cudaMemcpy(c.pose, na_h_pose, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
-    NCU(cudaMemcpy(c.vel, na_h_vel, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
-    NCU(cudaMemcpy(const_cast<float4*>(c.shape), na_h_shape, sizeof(sfp::f4) * n,
-                   cudaMemcpyHostToDevice));
-    NCU(cudaMemcpy(const_cast<float4*>(c.mat), na_h_mat, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice));
-    NCU(cudaMemcpy(const_cast<float2*>(c.minv), na_h_minv, sizeof(sfp::f2) * n,
-                   cudaMemcpyHostToDevice));
+    for (uint32_t i = 0; i < n; ++i) {
+        sfp::body_from_desc(bodies[i], &slot.pose[i], &slot.vel[i], &slot.minv[i], &slot.shape[i],
+                            &slot.mat[i]);
+        if (!sfp::body_fits_grid(slot.pose[i], slot.shape[i], p)) {
+            if (err && err_cap)
+                snprintf(err, err_cap,
+                         "sfp_step_small_noalloc: body %u spans more than 16384 broadphase cells (or "
+                         "4096 along one axis) at this cell_size", i);
+            return SFP_E_INVALID;
+        }
+    }
+    NCU(cudaMemcpyAsync(c.pose, slot.pose, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+    NCU(cudaMemcpyAsync(c.vel, slot.vel, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+    NCU(cudaMemcpyAsync(const_cast<float4*>(c.shape), slot.shape, sizeof(sfp::f4) * n,
+                        cudaMemcpyHostToDevice, st));
+    NCU(cudaMemcpyAsync(const_cast<float4*>(c.mat), slot.mat, sizeof(sfp::f4) * n, cudaMemcpyHostToDevice, st));
+    NCU(cudaMemcpyAsync(const_cast<float2*>(c.minv), slot.minv, sizeof(sfp::f2) * n,
+                        cudaMemcpyHostToDevice, st));
     // the previous call's counters (sticky overflow bits, colour counts) must not leak in
-    NCU(cudaMemset(ctx.counters, 0, sizeof(Counters)));
+    NCU(cudaMemsetAsync(ctx.counters, 0, sizeof(Counters), st));
 
     const float h = dt / (float)substeps;
     const float g = sqrtf(p.gravity_x * p.gravity_x + p.gravity_y * p.gravity_y);
@@ -1207,22 +1247,23 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
         c.warm = (f % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
         c.tab_old = tab[(f + 1u) & 1u];
         c.tab_new = tab[f & 1u];
-        k_batch_frame<true><<<1, BTPB, (size_t)n * 80u, 0>>>(ctx, dt, substeps, 2.0f * g * h);
+        k_batch_frame<true><<<1, BTPB, (size_t)n * 80u, st>>>(ctx, dt, substeps, 2.0f * g * h);
         NCU(cudaGetLastError());
     }
-    NCU(cudaMemcpy(na_h_pose, c.pose, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost));
-    NCU(cudaMemcpy(na_h_vel, c.vel, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost));
+    NCU(cudaMemcpyAsync(slot.pose, c.pose, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost, st));
+    NCU(cudaMemcpyAsync(slot.vel, c.vel, sizeof(sfp::f4) * n, cudaMemcpyDeviceToHost, st));
     Counters k;
-    NCU(cudaMemcpy(&k, ctx.counters, sizeof(k), cudaMemcpyDeviceToHost));
+    NCU(cudaMemcpyAsync(&k, ctx.counters, sizeof(k), cudaMemcpyDeviceToHost, st));
+    NCU(cudaStreamSynchronize(st));
 #undef NCU
-    for (uint32_t i = 0; i < n; ++i) out[i] = sfp::state_from_records(na_h_pose[i], na_h_vel[i]);
+    for (uint32_t i = 0; i < n; ++i) out[i] = sfp::state_from_records(slot.pose[i], slot.vel[i]);
     if (k.overflow) {
         if (err && err_cap)
             snprintf(err, err_cap,
                      "sfp_step_small_noalloc: capacity exceeded inside the fixed scratch area "
                      "(bits %u: 2 = more than %u candidate pairs, 4 = serial group too large, "
                      "16 = runaway body)",
-                     k.overflow, NA_PAIR_CAP);
+                     k.overflow, pair_cap);
         return SFP_E_CAPACITY;
     }
     return SFP_OK;

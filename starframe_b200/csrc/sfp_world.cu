@@ -1349,6 +1349,10 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
                             &w->h_mat[i], &w->polys);
         ndyn += (w->h_minv[i].x > 0.0f || w->h_minv[i].y > 0.0f) ? 1u : 0u;
         polys_used |= (bodies[i].shape & 0xffu) == SFP_SHAPE_POLYGON;
+        if (!sfp::body_fits_grid(pose[i], w->h_shape[i], w->p)) {
+            w->err = "body " + std::to_string(i) + " spans more than 16384 broadphase cells (or 4096 along one axis) at this cell_size: split it or raise cell_size";
+            return SFP_E_INVALID;
+        }
     }
     w->has_polygons = polys_used;
     Ctx& c = w->ctx;
@@ -1828,6 +1832,24 @@ int32_t sfp_last_step_breakdown_ms(SfpWorld* w, float out[4]) {
         CU(cudaEventElapsedTime(&out[2], w->ev_bp, w->ev_col));
         CU(cudaEventElapsedTime(&out[3], w->ev_col, w->ev1));
     }
+    return SFP_OK;
+}
+
+int32_t sfp_last_step_stage_ns(SfpWorld* w, uint64_t out[6]) {
+    if (!w || !out) return SFP_E_INVALID;
+    for (int i = 0; i < 6; ++i) out[i] = 0;
+    if (!w->timed || w->n == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    Counters k;
+    TRY(read_counters(w, &k));
+    // Counters::stage_cycles: 4 integrate, 5 narrowphase, 6 position (+10 tile-interior),
+    // 7 derive, 8 velocity (+11), 9 small colours
+    out[0] = k.stage_cycles[4];
+    out[1] = k.stage_cycles[5];
+    out[2] = k.stage_cycles[6] + k.stage_cycles[10];
+    out[3] = k.stage_cycles[7];
+    out[4] = k.stage_cycles[8] + k.stage_cycles[11];
+    out[5] = k.stage_cycles[9];
     return SFP_OK;
 }
 

@@ -47,7 +47,7 @@ def _rank_main(rank, world_size, port, out):
 
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank,
                             world_size=world_size)
-    mine = bench.world_range(rank, NW_PER_RANK)
+    mine = bench.world_range(rank, world_size, world_size * NW_PER_RANK)
     pairs, contacts, checksum = _step_worlds(mine.start, len(mine))
     bench.barrier(world_size)
     tot = bench.allreduce_sum([pairs, contacts, checksum, float(len(mine))], world_size)
@@ -81,8 +81,10 @@ def test_world_ranges_tile_the_world_list():
     sys.path.insert(0, ROOT)
     import bench
 
-    for ranks in (1, 2, 4, 8):
+    for ranks in (1, 2, 3, 4, 8):
         seen = []
         for r in range(ranks):
-            seen += list(bench.world_range(r, 1024))
-        assert seen == list(range(1024 * ranks))
+            seen += list(bench.world_range(r, ranks, 8192))
+        assert seen == list(range(8192))  # BASELINE.json config 5: 8192 worlds over 1/2/4/8 GPUs
+        sizes = [len(bench.world_range(r, ranks, 8192)) for r in range(ranks)]
+        assert max(sizes) - min(sizes) <= 1
