@@ -25,6 +25,11 @@ using sfp::f4;
 using sfp::v2;
 
 constexpr uint32_t UNCOLOURED = 0xffffffffu;
+// overflow bits 1 (entries) and 2 (pairs): the broadphase ran out of room.  Every later kernel
+// of the frame — and every kernel of the frames queued behind it — then does nothing, so that
+// the world stays exactly as it was before the frame and the host can enlarge the buffers and
+// run those frames again (sfp_world.cu, recover_capacity).
+constexpr uint32_t OVERFLOW_CAPACITY = 3u;
 constexpr int MAX_ROUNDS = 512;
 
 struct Counters {
@@ -35,6 +40,8 @@ struct Counters {
     uint32_t n_contacts, n_manifolds, maxpen_bits;
     uint32_t n_unc;  // length of Ctx::unc (pairs still uncoloured after the warm start)
     uint32_t n_colours_int;  // interior colours in use (tiles; n_colours counts the boundary ones)
+    uint32_t frames_done;    // frames whose substep kernel ran to the end (capacity recovery)
+    uint32_t pad_[3];
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
     uint32_t round_flags[MAX_ROUNDS];

@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(TPB) k_permute_gather(Ctx c, const uint32_t* _
 }
 __global__ void __launch_bounds__(TPB) k_permute_store(Ctx c, uint32_t* __restrict__ ext,
                                                        uint32_t* __restrict__ inv) {
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;  // a frame behind a failed one: no-op
     for (uint32_t j = gtid(); j < c.n; j += gnth()) {
         c.pose[j] = c.ca[j];
         c.prev[j] = c.cb[j];
@@ -136,6 +137,33 @@ __global__ void __launch_bounds__(TPB) k_remap_joints(Ctx c, const uint2* __rest
     for (uint32_t k = gtid(); k < c.nj; k += gnth()) {
         const uint2 j = jext[k];
         const_cast<uint2*>(c.jbod_in)[k] = make_uint2(c.inv[j.x], c.inv[j.y]);
+    }
+}
+// state before the frame (after its re-sort), for the capacity recovery; a frame queued behind a
+// failed one must not overwrite it
+__global__ void __launch_bounds__(TPB) k_snapshot(Ctx c, float4* __restrict__ pose_bak,
+                                                  float4* __restrict__ vel_bak) {
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;
+    for (uint32_t i = gtid(); i < c.n; i += gnth()) {
+        pose_bak[i] = c.pose[i];
+        vel_bak[i] = c.vel[i];
+    }
+}
+__global__ void __launch_bounds__(TPB) k_clear_table(Ctx c, unsigned long long* __restrict__ tab,
+                                                     uint32_t slots) {
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;
+    for (uint32_t i = gtid(); i < slots; i += gnth()) tab[i] = 0ull;
+}
+// colour table into a larger one (capacity recovery)
+__global__ void __launch_bounds__(TPB) k_rehash(const unsigned long long* __restrict__ from,
+                                                uint32_t from_slots, unsigned long long* __restrict__ to,
+                                                uint32_t to_mask) {
+    for (uint32_t i = gtid(); i < from_slots; i += gnth()) {
+        const unsigned long long e = from[i];
+        if (e == 0ull) continue;
+        const uint32_t a = (uint32_t)((e >> 22) & 0x3fffffu), b = (uint32_t)(e & 0x3fffffu);
+        uint32_t h = sfp::ctab_hash(a, b) & to_mask;
+        while (atomicCAS(&to[h], 0ull, e) != 0ull) h = (h + 1u) & to_mask;
     }
 }
 __global__ void __launch_bounds__(TPB) k_identity(uint32_t* __restrict__ a, uint32_t* __restrict__ b,
@@ -312,6 +340,9 @@ __global__ void __launch_bounds__(TPB) k_unpack_states(const sfp::StateRec* __re
 __global__ void __launch_bounds__(TPB) k_colour_coop(Ctx c) {
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
+    // the broadphase ran out of room (this frame or an earlier one): keep last frame's colours
+    // and table untouched for the re-run (every thread takes this exit, before any grid barrier)
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;
     // wall time of the parts (ns, thread 0) -> stage_cycles[1..3]: init + warm, rounds, record
     unsigned long long t0 = 0, t1 = 0, t2 = 0;
     auto now = [&]() {
@@ -378,6 +409,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
     __shared__ uint32_t s_toff[3 * (SFP_MAX_COLOURS + 1)];
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;  // see k_colour_coop
     // A colour's constraints go to threads in warp-sized runs dealt round-robin over the BLOCKS
     // (run r -> block r % gridDim, warp r / gridDim), not block after block: a phase lasts as
     // long as its slowest warp, and a colour of a few thousand constraints would otherwise fill
@@ -598,6 +630,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
         lap(9);
     }
     if (tid == 0) {
+        c.cnt->frames_done += 1u;
         for (int k = 4; k < 12; ++k) c.cnt->stage_cycles[k] = acc[k];
         c.cnt->stage_cycles[0] = (unsigned long long)__popcll(big);
 #ifdef SFP_PHASE_PROBE
@@ -627,6 +660,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS)
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
     const uint32_t lane = threadIdx.x & 31u;
+    if (vload(&c.cnt->overflow) & OVERFLOW_CAPACITY) return;  // see k_colour_coop
     // consecutive runs go to different SMs
     const uint32_t gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
@@ -684,6 +718,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS)
         lap(8);
     }
     if (tid == 0) {
+        c.cnt->frames_done += 1u;
         for (int k = 4; k < 10; ++k) c.cnt->stage_cycles[k] = acc[k];
         c.cnt->stage_cycles[0] = (unsigned long long)s_fo.n;
     }
@@ -714,7 +749,15 @@ struct SfpWorld {
     uint32_t n = 0, nj = 0;
     uint32_t cap_bodies = 0, cap_joints = 0, cap_entries = 0, cap_pairs = 0;
     Ctx ctx;
-    std::vector<void*> body_allocs, joint_allocs;
+    std::vector<void*> body_allocs, pair_allocs, joint_allocs;
+    // capacity recovery: the state before the last frame, and what the frames since were
+    float4 *d_pose_bak = nullptr, *d_vel_bak = nullptr;
+    struct FrameLog {
+        float dt;
+        uint32_t substeps, colour_age;
+    } frame_log[1024];
+    uint64_t frames_launched = 0;  // sfp_step calls since the last upload
+    uint32_t grows = 0;            // times the entry / pair buffers were enlarged
     uint32_t *d_scan_tiles = nullptr, *d_hist = nullptr;
     uint32_t hist_blocks = 0;
     unsigned long long* d_tab[2] = {nullptr, nullptr};
@@ -784,36 +827,11 @@ void free_bag(std::vector<void*>& bag) {
         if (rc_ != SFP_OK) return rc_; \
     } while (0)
 
-int ensure_body_capacity(SfpWorld* w, uint32_t n) {
-    if (n <= w->cap_bodies && w->cap_bodies > 0) return SFP_OK;
-    CU(cudaStreamSynchronize(w->stream));
-    free_bag(w->body_allocs);
-    if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
-    if (w->d_hist) cudaFree(w->d_hist);
-    w->d_scan_tiles = w->d_hist = nullptr;
-    uint32_t cb = std::max<uint32_t>(std::max(n, w->p.max_bodies), 1u);
-    uint32_t ce = std::max<uint32_t>(w->p.max_entries, 8u * cb + 8192u);
-    uint32_t cp = std::max<uint32_t>(w->p.max_pairs, 12u * cb + 4096u);
+// entry- and pair-sized buffers (scratch of one frame, plus the two colour tables); separate from
+// the body-sized ones so that the capacity recovery can enlarge them without touching the state
+int alloc_pair_arrays(SfpWorld* w, uint32_t ce, uint32_t cp) {
     Ctx& c = w->ctx;
-    auto& bag = w->body_allocs;
-    TRY(alloc_dev(w, &c.pose, cb, bag));
-    TRY(alloc_dev(w, &c.prev, cb, bag));
-    TRY(alloc_dev(w, &c.vel, cb, bag));
-    TRY(alloc_dev(w, const_cast<float4**>(&c.shape), cb, bag));
-    TRY(alloc_dev(w, const_cast<float4**>(&c.mat), cb, bag));
-    TRY(alloc_dev(w, const_cast<float2**>(&c.minv), cb, bag));
-    TRY(alloc_dev(w, &c.aabb, cb, bag));
-    TRY(alloc_dev(w, &c.meta, cb, bag));
-    TRY(alloc_dev(w, &c.cell_cnt, cb + 1, bag));
-    TRY(alloc_dev(w, &c.cell_off, cb + 1, bag));
-    TRY(alloc_dev(w, &c.mask, cb, bag));
-    TRY(alloc_dev(w, &c.claim0, cb, bag));
-    TRY(alloc_dev(w, &c.claim1, cb, bag));
-    TRY(alloc_dev(w, &c.done, 2 * (size_t)cb, bag));
-    TRY(alloc_dev(w, &c.mask_i, cb, bag));
-    w->max_tiles = cb / SFP_TILE_MIN + 2u;
-    TRY(alloc_dev(w, &c.goff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
-    TRY(alloc_dev(w, &c.jgoff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
+    auto& bag = w->pair_allocs;
     TRY(alloc_dev(w, &c.ekey0, ce, bag));
     TRY(alloc_dev(w, &c.eval0, ce, bag));
     TRY(alloc_dev(w, &c.ekey1, ce, bag));
@@ -838,26 +856,64 @@ int ensure_body_capacity(SfpWorld* w, uint32_t n) {
     TRY(alloc_dev(w, &w->d_evt_flag, cp + 1, bag));
     TRY(alloc_dev(w, &w->d_evt_off, cp + 1, bag));
     TRY(alloc_dev(w, &w->d_events, cp, bag));
-    TRY(alloc_dev(w, &w->d_idx, cb, bag));
-    TRY(alloc_dev(w, &w->d_ext, cb, bag));
-    TRY(alloc_dev(w, &w->d_inv, cb, bag));
-    c.ext = w->d_ext;
-    c.inv = w->d_inv;
     uint32_t slots = 1024;
     while (slots < 2u * cp) slots <<= 1;
     TRY(alloc_dev(w, &w->d_tab[0], slots, bag));
     TRY(alloc_dev(w, &w->d_tab[1], slots, bag));
     w->tab_slots = slots;
     c.tab_mask = slots - 1u;
-    w->cap_bodies = cb;
     w->cap_entries = ce;
     w->cap_pairs = cp;
     c.cap_entries = ce;
     c.cap_pairs = cp;
-    uint32_t biggest = std::max(std::max(ce, cp), std::max(cb, w->cap_joints)) + 1;
+    uint32_t biggest = std::max(std::max(ce, cp), std::max(w->cap_bodies, w->cap_joints)) + 1;
     w->hist_blocks = radix_blocks(biggest);
-    CU(cudaMalloc(&w->d_scan_tiles, sizeof(uint32_t) * (biggest / SCAN_TILE + 4)));
-    CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * ((size_t)w->hist_blocks + 1)));
+    uint32_t *tiles = nullptr, *hist = nullptr;
+    TRY(alloc_dev(w, &tiles, biggest / SCAN_TILE + 4, bag));
+    TRY(alloc_dev(w, &hist, RADIX_BINS * ((size_t)w->hist_blocks + 1), bag));
+    w->d_scan_tiles = tiles;
+    w->d_hist = hist;
+    return SFP_OK;
+}
+
+int ensure_body_capacity(SfpWorld* w, uint32_t n) {
+    if (n <= w->cap_bodies && w->cap_bodies > 0) return SFP_OK;
+    CU(cudaStreamSynchronize(w->stream));
+    free_bag(w->body_allocs);
+    free_bag(w->pair_allocs);
+    w->d_scan_tiles = w->d_hist = nullptr;
+    uint32_t cb = std::max<uint32_t>(std::max(n, w->p.max_bodies), 1u);
+    uint32_t ce = std::max<uint32_t>(w->p.max_entries, 8u * cb + 8192u);
+    uint32_t cp = std::max<uint32_t>(w->p.max_pairs, 12u * cb + 4096u);
+    Ctx& c = w->ctx;
+    auto& bag = w->body_allocs;
+    TRY(alloc_dev(w, &c.pose, cb, bag));
+    TRY(alloc_dev(w, &c.prev, cb, bag));
+    TRY(alloc_dev(w, &c.vel, cb, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.shape), cb, bag));
+    TRY(alloc_dev(w, const_cast<float4**>(&c.mat), cb, bag));
+    TRY(alloc_dev(w, const_cast<float2**>(&c.minv), cb, bag));
+    TRY(alloc_dev(w, &c.aabb, cb, bag));
+    TRY(alloc_dev(w, &c.meta, cb, bag));
+    TRY(alloc_dev(w, &c.cell_cnt, cb + 1, bag));
+    TRY(alloc_dev(w, &c.cell_off, cb + 1, bag));
+    TRY(alloc_dev(w, &c.mask, cb, bag));
+    TRY(alloc_dev(w, &c.claim0, cb, bag));
+    TRY(alloc_dev(w, &c.claim1, cb, bag));
+    TRY(alloc_dev(w, &c.done, 2 * (size_t)cb, bag));
+    TRY(alloc_dev(w, &c.mask_i, cb, bag));
+    w->max_tiles = cb / SFP_TILE_MIN + 2u;
+    TRY(alloc_dev(w, &c.goff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
+    TRY(alloc_dev(w, &c.jgoff, ((size_t)w->max_tiles + 1u) * SFP_MAX_COLOURS + 1u, bag));
+    TRY(alloc_dev(w, &w->d_idx, cb, bag));
+    TRY(alloc_dev(w, &w->d_ext, cb, bag));
+    TRY(alloc_dev(w, &w->d_inv, cb, bag));
+    TRY(alloc_dev(w, &w->d_pose_bak, cb, bag));
+    TRY(alloc_dev(w, &w->d_vel_bak, cb, bag));
+    c.ext = w->d_ext;
+    c.inv = w->d_inv;
+    w->cap_bodies = cb;
+    TRY(alloc_pair_arrays(w, ce, cp));
     if (w->pin_state) cudaFreeHost(w->pin_state);
     w->pin_state = nullptr;
     CU(cudaMallocHost(&w->pin_state, sizeof(SfpBodyState) * cb));
@@ -886,11 +942,14 @@ int ensure_joint_capacity(SfpWorld* w, uint32_t nj) {
     TRY(alloc_dev(w, &w->d_jkeyB, cj, bag));
     TRY(alloc_dev(w, &w->d_jpermB, cj, bag));
     w->cap_joints = cj;
-    // the radix histogram must cover the joint sort too
-    if (radix_blocks(cj + 1) > w->hist_blocks) {
-        if (w->d_hist) cudaFree(w->d_hist);
+    // the radix histogram (and the scan's tile sums) must cover the joint sort too
+    if (radix_blocks(cj + 1) > w->hist_blocks && w->cap_bodies) {
         w->hist_blocks = radix_blocks(cj + 1);
-        CU(cudaMalloc(&w->d_hist, sizeof(uint32_t) * RADIX_BINS * ((size_t)w->hist_blocks + 1)));
+        uint32_t *tiles = nullptr, *hist = nullptr;
+        TRY(alloc_dev(w, &tiles, (size_t)cj / SCAN_TILE + 4, w->pair_allocs));
+        TRY(alloc_dev(w, &hist, RADIX_BINS * ((size_t)w->hist_blocks + 1), w->pair_allocs));
+        w->d_scan_tiles = tiles;
+        w->d_hist = hist;
     }
     return SFP_OK;
 }
@@ -954,6 +1013,10 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     // the frames whose colouring starts from scratch also renew the body order
     if ((w->colour_age % SFP_RECOLOUR_PERIOD) == 0u) TRY(resort_bodies(w));
     const bool mark = !(w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP);
+    if (mark) {  // the state this frame starts from, for the capacity recovery
+        k_snapshot<<<gb, TPB, 0, st>>>(c, w->d_pose_bak, w->d_vel_bak);
+        w->launches += 1;
+    }
     k_aabb_count<<<gb, TPB, 0, st>>>(c, dt);
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
                       &w->d_cnt->n_entries, st));
@@ -974,7 +1037,8 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     c.tab_old = w->d_tab[(w->colour_age + 1u) & 1u];
     c.tab_new = w->d_tab[w->colour_age & 1u];
     w->colour_age += 1;
-    CU(cudaMemsetAsync(c.tab_new, 0, sizeof(unsigned long long) * w->tab_slots, st));
+    k_clear_table<<<blocks_for(w, w->tab_slots), TPB, 0, st>>>(c, c.tab_new, w->tab_slots);
+    w->launches += 1;
     if (!multi) {
         // a grid barrier costs 1.2 us with 2-3 CTAs per SM and ~3 us with 8, and the kernel is a
         // dozen barriers around loops that are short for a 100 k-body world (measured: 3 CTAs
@@ -1184,17 +1248,86 @@ int read_counters(SfpWorld* w, Counters* out) {
     return SFP_OK;
 }
 
-int check_overflow(SfpWorld* w, const Counters& k) {
-    if (k.overflow) {
-        w->stats.overflow |= k.overflow;
-        char buf[160];
-        snprintf(buf, sizeof(buf),
-                 "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=serial group>1024, "
-                 "8=colour rounds, 16=runaway or non-finite body)",
-                 k.overflow, w->cap_entries, w->cap_pairs);
-        w->err = buf;
-        return SFP_E_CAPACITY;
+int capacity_error(SfpWorld* w, uint32_t bits) {
+    w->stats.overflow |= bits;
+    char buf[200];
+    snprintf(buf, sizeof(buf),
+             "device capacity exceeded (bits %u: 1=entries cap %u, 2=pairs cap %u, 4=serial group>1024, "
+             "8=colour rounds, 16=runaway or non-finite body, 32=solver wait)",
+             bits, w->cap_entries, w->cap_pairs);
+    w->err = buf;
+    return SFP_E_CAPACITY;
+}
+
+// The broadphase ran out of entry / pair room in some frame since the last synchronisation.
+// Every kernel after that point was a no-op (OVERFLOW_CAPACITY), so the device still holds the
+// state that frame started from (k_snapshot), last frame's colours and the body order.  Enlarge
+// the buffers, carry the colour tables over, put the state back and run the lost frames again
+// — with the same dt, substeps and colouring age, so the result is what a large enough world
+// would have produced (and what the oracle, which has no capacities, produces).
+int recover_capacity(SfpWorld* w, Counters* k) {
+    for (int attempt = 0; attempt < 12; ++attempt) {
+        if (!(k->overflow & OVERFLOW_CAPACITY) || (k->overflow & ~OVERFLOW_CAPACITY)) break;
+        const bool fixed_e = (k->overflow & 1u) && w->p.max_entries != 0u;
+        const bool fixed_p = (k->overflow & 2u) && w->p.max_pairs != 0u;
+        // explicit capacities are a contract, and the debug modes keep the old behaviour
+        if (fixed_e || fixed_p || (w->p.flags & (SFP_FLAG_BROADPHASE_EVERY_SUBSTEP | SFP_FLAG_MULTI_KERNEL)))
+            break;
+        const uint64_t lost = w->frames_launched - (uint64_t)k->frames_done;
+        if (lost == 0 || lost > 1024u) break;
+        const uint64_t ce64 = (k->overflow & 1u) ? 2ull * w->cap_entries : w->cap_entries;
+        const uint64_t cp64 = (k->overflow & 2u) ? 2ull * w->cap_pairs : w->cap_pairs;
+        if (ce64 > 0x7fffffffull || cp64 > 0x7fffffffull) break;
+        CU(cudaStreamSynchronize(w->stream));
+        drop_graphs(w);  // the buffers are kernel arguments
+        // keep the old tables until they are rehashed
+        std::vector<void*> old;
+        old.swap(w->pair_allocs);
+        unsigned long long* old_tab[2] = {w->d_tab[0], w->d_tab[1]};
+        const uint32_t old_slots = w->tab_slots;
+        int rc = alloc_pair_arrays(w, (uint32_t)ce64, (uint32_t)cp64);
+        if (rc != SFP_OK) {
+            free_bag(old);
+            return rc;
+        }
+        for (int t = 0; t < 2; ++t)
+            k_rehash<<<blocks_for(w, old_slots), TPB, 0, w->stream>>>(old_tab[t], old_slots, w->d_tab[t],
+                                                                     w->tab_slots - 1u);
+        CU(cudaMemcpyAsync(w->ctx.pose, w->d_pose_bak, sizeof(float4) * w->n, cudaMemcpyDeviceToDevice,
+                           w->stream));
+        CU(cudaMemcpyAsync(w->ctx.vel, w->d_vel_bak, sizeof(float4) * w->n, cudaMemcpyDeviceToDevice,
+                           w->stream));
+        const uint32_t zero = 0;
+        CU(cudaMemcpyAsync(&w->d_cnt->overflow, &zero, sizeof(zero), cudaMemcpyHostToDevice, w->stream));
+        CU(cudaStreamSynchronize(w->stream));
+        free_bag(old);
+        w->grows += 1;
+        // run the lost frames again
+        const uint64_t first = w->frames_launched - lost;
+        w->colour_age = w->frame_log[first % 1024u].colour_age;
+        for (uint64_t f = first; f < w->frames_launched; ++f) {
+            const SfpWorld::FrameLog& e = w->frame_log[f % 1024u];
+            w->launches = 0;
+            TRY(frame_graphed(w, e.dt, e.substeps));
+        }
+        TRY(read_counters(w, k));
     }
+    return SFP_OK;
+}
+
+// reports errors; recovers from a capacity overflow if there was one
+int check_overflow(SfpWorld* w, Counters& k) {
+    if (k.overflow & OVERFLOW_CAPACITY) TRY(recover_capacity(w, &k));
+    if (k.overflow) return capacity_error(w, k.overflow);
+    return SFP_OK;
+}
+// Waits for the queued frames and makes sure they really happened (capacity recovery) BEFORE
+// anything reads their results or changes the world underneath them.
+int settle(SfpWorld* w, Counters* k_out = nullptr) {
+    Counters k;
+    TRY(read_counters(w, &k));
+    TRY(check_overflow(w, k));
+    if (k_out) *k_out = k;
     return SFP_OK;
 }
 
@@ -1303,9 +1436,8 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->stream) cudaStreamSynchronize(w->stream);
     drop_graphs(w);
     free_bag(w->body_allocs);
+    free_bag(w->pair_allocs);
     free_bag(w->joint_allocs);
-    if (w->d_scan_tiles) cudaFree(w->d_scan_tiles);
-    if (w->d_hist) cudaFree(w->d_hist);
     if (w->d_cnt) cudaFree(w->d_cnt);
     if (w->pin_state) cudaFreeHost(w->pin_state);
     if (w->d_rays) cudaFree(w->d_rays);
@@ -1384,6 +1516,7 @@ int32_t sfp_upload_bodies(SfpWorld* w, const SfpBodyDesc* bodies, uint32_t n) {
     w->stats.n_dynamic = ndyn;
     w->colour_age = 0;
     w->stepped = false;
+    w->frames_launched = 0;  // (the device's frames_done was zeroed with the counters)
     // tiles of the solve order (sfp_math.h): after the first frame's re-sort the dynamic bodies
     // are the indices [0, ndyn)
     c.n_dyn = ndyn;
@@ -1426,6 +1559,7 @@ int32_t sfp_set_joints(SfpWorld* w, const SfpJointDesc* joints, uint32_t nj) {
             return SFP_E_INVALID;
         }
     CU(cudaSetDevice(w->device));
+    if (w->stepped) TRY(settle(w));
     drop_graphs(w);
     TRY(ensure_joint_capacity(w, nj));
     std::vector<uint2> jb(nj);
@@ -1464,6 +1598,8 @@ int32_t sfp_step(SfpWorld* w, float dt, uint32_t substeps) {
     CU(cudaSetDevice(w->device));
     CU(cudaEventRecord(w->ev0, w->stream));
     w->launches = 0;
+    w->frame_log[w->frames_launched % 1024u] = {dt, substeps, w->colour_age};
+    w->frames_launched += 1;
     int rc = frame_graphed(w, dt, substeps);
     if (rc != SFP_OK) return rc;
     CU(cudaEventRecord(w->ev1, w->stream));
@@ -1479,9 +1615,7 @@ int32_t sfp_sync(SfpWorld* w) {
     if (!w) return SFP_E_INVALID;
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
-    Counters k;
-    TRY(read_counters(w, &k));
-    return check_overflow(w, k);
+    return settle(w);
 }
 
 namespace {
@@ -1512,6 +1646,7 @@ int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
     if (!w || (n && !out) || n > w->n) return SFP_E_INVALID;
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
+    TRY(settle(w));
     const bool direct = n && host_pinned(out);
     if (n) {
         // states are packed on the device (incl. the angle), one D2H copy, no per-body host work
@@ -1519,11 +1654,10 @@ int32_t sfp_download_bodies(SfpWorld* w, SfpBodyState* out, uint32_t n) {
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(direct ? out : w->pin_state, w->d_state, sizeof(SfpBodyState) * n,
                            cudaMemcpyDeviceToHost, w->stream));
+        CU(cudaStreamSynchronize(w->stream));
     }
-    Counters k;
-    TRY(read_counters(w, &k));
     if (n && !direct) std::memcpy(out, w->pin_state, sizeof(SfpBodyState) * n);
-    return check_overflow(w, k);
+    return SFP_OK;
 }
 
 int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, uint32_t n, float dt,
@@ -1532,7 +1666,7 @@ int32_t sfp_step_host(SfpWorld* w, const SfpBodyState* in, SfpBodyState* out, ui
     if (!(dt > 0.0f) || substeps == 0 || substeps > 1024) return SFP_E_INVALID;
     if (w->sticky != SFP_OK) return w->sticky;
     CU(cudaSetDevice(w->device));
-    CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
+    TRY(settle(w));  // (also: the staging buffer is reused)
     // (a state that carries its rotation in `angle` only is given its rotor by the unpack
     // kernel: no pass over the states on the host)
     const SfpBodyState* src = in;
@@ -1559,8 +1693,7 @@ struct HostPairs {
     Counters k;
 };
 int fetch_pairs(SfpWorld* w, HostPairs* hp) {
-    TRY(read_counters(w, &hp->k));
-    TRY(check_overflow(w, hp->k));
+    TRY(settle(w, &hp->k));
     uint32_t P = w->stepped ? hp->k.n_pairs : 0u;
     hp->pairs.resize(P);
     hp->ext_of.resize(w->n);
@@ -1672,6 +1805,7 @@ int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap, 
     *n_out = 0;
     if (!w->stepped || w->n == 0) return SFP_OK;
     CU(cudaSetDevice(w->device));
+    TRY(settle(w));
     cudaStream_t st = w->stream;
     const uint32_t gp = blocks_for(w, w->cap_pairs);
     k_event_flags<<<gp, TPB, 0, st>>>(w->ctx, w->d_evt_flag);
@@ -1682,9 +1816,7 @@ int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32_t cap, 
     CU(cudaGetLastError());
     uint32_t total = 0;
     CU(cudaMemcpyAsync(&total, w->d_evt_flag + w->cap_pairs, sizeof(total), cudaMemcpyDeviceToHost, st));
-    Counters k;
-    TRY(read_counters(w, &k));  // synchronises
-    TRY(check_overflow(w, k));
+    CU(cudaStreamSynchronize(st));
     *n_out = total;
     const uint32_t m = std::min(total, cap);
     if (m == 0) return SFP_OK;
@@ -1708,6 +1840,7 @@ int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hit
         return SFP_OK;
     }
     CU(cudaSetDevice(w->device));
+    TRY(settle(w));
     cudaStream_t st = w->stream;
     if (m > w->ray_cap) {
         CU(cudaStreamSynchronize(st));
@@ -1733,9 +1866,17 @@ int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hit
     k_ray_cast<<<blocks_for(w, m), TPB, 0, st>>>(c, w->d_rays, m, w->d_hits, w->p.cell_size);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(hits, w->d_hits, sizeof(SfpRayHit) * (size_t)m, cudaMemcpyDeviceToHost, st));
+    // the query's own hash can run out of entry room (bodies have moved since the frame's): the
+    // entry buffers are then enlarged by the next frame's recovery; here it is an error
     Counters k;
     TRY(read_counters(w, &k));
-    return check_overflow(w, k);
+    if (k.overflow) {
+        const uint32_t zero = 0;
+        if (!(k.overflow & ~OVERFLOW_CAPACITY))
+            CU(cudaMemcpy(&w->d_cnt->overflow, &zero, sizeof(zero), cudaMemcpyHostToDevice));
+        return capacity_error(w, k.overflow);
+    }
+    return SFP_OK;
 }
 
 int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y, uint32_t mask,
@@ -1745,6 +1886,7 @@ int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi
     *n_out = 0;
     if (w->n == 0) return SFP_OK;
     CU(cudaSetDevice(w->device));
+    TRY(settle(w));
     cudaStream_t st = w->stream;
     const uint32_t gb = blocks_for(w, w->n);
     k_box_flags<<<gb, TPB, 0, st>>>(w->ctx, make_float4(lo_x, lo_y, hi_x, hi_y), mask, w->d_evt_flag);
@@ -1768,7 +1910,7 @@ int32_t sfp_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* 
         if (idx[k] >= w->n) return SFP_E_INVALID;
     if (m == 0) return SFP_OK;
     CU(cudaSetDevice(w->device));
-    CU(cudaStreamSynchronize(w->stream));  // the staging buffer is reused
+    TRY(settle(w));  // (also: the staging buffer is reused)
     std::memcpy(w->pin_state, states, sizeof(SfpBodyState) * m);
     CU(cudaMemcpyAsync(w->d_state, w->pin_state, sizeof(SfpBodyState) * m, cudaMemcpyHostToDevice,
                        w->stream));
@@ -1786,6 +1928,7 @@ int32_t sfp_get_stats(SfpWorld* w, SfpStats* out) {
     CU(cudaSetDevice(w->device));
     Counters k;
     TRY(read_counters(w, &k));
+    if (k.overflow & OVERFLOW_CAPACITY) TRY(recover_capacity(w, &k));
     w->stats.n_entries = k.n_entries;
     w->stats.n_pairs = w->stepped ? k.n_pairs : 0u;
     w->stats.n_contacts = k.n_contacts;

@@ -288,3 +288,45 @@ def test_worlds_driven_from_different_threads(gpu_api, ref_api):
         ro = r.download_bodies()
         for f in FIELDS:
             assert np.array_equal(results[k][f].view(np.uint32), ro[f].view(np.uint32)), (k, f)
+
+
+@pytest.mark.parametrize("cell,frames_queued", [(0.5, 1), (0.1, 3)])
+def test_capacity_overflow_grows_and_redoes_the_frames(gpu_api, ref_api, cell, frames_queued):
+    """A dense blob has several times more candidate pairs (and, with small cells, entries) than
+    the default capacities (12 n + 4096 pairs, 8 n + 8192 entries) hold.  The library notices at
+    the next synchronisation, enlarges its buffers, puts the pre-frame state back and runs the
+    queued frames again: the result must be the oracle's (which has no capacities) bit for bit.
+    With explicit max_pairs the same world is an SFP_E_CAPACITY error."""
+    from starframe_b200._ffi import SfpError, SFP_E_CAPACITY
+
+    # a loose grid of circles with a wide AABB margin: ~22 candidate pairs per body (few of them
+    # touch), and with 0.1 m cells ~70 broadphase entries per body
+    n_side, pitch = 45, 0.2
+    b = scenes.empty_bodies(n_side * n_side)
+    k = np.arange(n_side * n_side)
+    b["x"] = pitch * (k % n_side) + 0.003 * scenes.uniform(99, 1, len(k))
+    b["y"] = 0.12 + pitch * (k // n_side) + 0.003 * scenes.uniform(99, 2, len(k))
+    b["vy"] = -1.0
+    b["shape"], b["radius"] = 0, 0.09
+    b = np.concatenate([b, scenes.static_rect(4.4, -0.5, 8.0, 0.5)])
+    j = scenes.no_joints()
+    n = len(b)
+    g, r = make_worlds(gpu_api, ref_api, b, j, cell_size=cell, aabb_margin=0.26)
+    for _ in range(2):
+        for _ in range(frames_queued):
+            g.step()
+            r.step()
+        assert_same_discrete(g, r)   # (the first call that synchronises triggers the recovery)
+        assert_same_state(g, r)
+    st = g.stats()
+    assert st["n_pairs"] > 12 * n + 4096, st["n_pairs"]
+    if cell < 0.2:
+        assert st["n_entries"] > 8 * n + 8192, st["n_entries"]
+    assert st["overflow"] == 0
+    # explicit capacity: a contract, not a hint
+    fixed = sf.World(gpu_api, cell_size=cell, aabb_margin=0.26, max_pairs=12 * n + 4096)
+    fixed.upload_bodies(b)
+    fixed.step()
+    with pytest.raises(SfpError) as e:
+        fixed.sync()
+    assert e.value.code == SFP_E_CAPACITY
