@@ -515,6 +515,18 @@ def run_worlds(args, rank, world_size):
         b.step_host(buf[(k + 1) & 1], DT, SUBSTEPS, out=buf[k & 1])
     e2e_s = time.perf_counter() - t0
     e2e_val = allreduce_sum([n * SUBSTEPS * e2e_steps / e2e_s], world_size)[0]
+    # the same workload through the library's own multi-GPU entry, from ONE process (what a
+    # single-process engine would call): rank 0 drives all N GPUs, the other ranks wait on the CPU
+    single = None
+    if world_size > 1:
+        del b, buf
+        cpu_barrier()
+        if rank == 0:
+            try:
+                single = single_process_multi(args, world_size, total)
+            except Exception as e:  # a box that hides the other GPUs from rank 0
+                single = {"error": str(e)}
+        cpu_barrier()
     return {
         "metric": "body-substeps/sec", "value": value, "unit": "body-substeps/s",
         "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
@@ -548,7 +560,37 @@ def run_worlds(args, rank, world_size):
                 "call": "sfp_batch_step_host with host SfpBodyState arrays from sfp_alloc_host_states "
                         "(pinned), one process per GPU; bytes are whole-job"},
         "gpu_launches": args.steps, "clocks": clk.summary(),
+        "single_process_multi_gpu": single,
     }
+
+
+def single_process_multi(args, n_dev, total, frames=10):
+    """sfp_batch_create_multi over devices 0..n_dev-1 from this process: wall time per frame of
+    step + sync (the fan-out to the per-device worker threads included)"""
+    import torch
+
+    import starframe_b200 as sf
+    from starframe_b200 import scenes
+
+    if torch.cuda.device_count() < n_dev:
+        raise RuntimeError(f"rank 0 sees {torch.cuda.device_count()} of {n_dev} GPUs")
+    m = sf.BatchMulti(sf.product_api(), total, BODIES_PER_WORLD, list(range(n_dev)))
+    m.upload(scenes.worlds(total, BODIES_PER_WORLD))
+    for _ in range(args.settle):
+        m.step(DT, SUBSTEPS)
+    m.sync()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(frames):
+        m.step(DT, SUBSTEPS)
+        m.sync()
+        dev_ms += m.last_step_ms()
+    wall = time.perf_counter() - t0
+    n = total * BODIES_PER_WORLD
+    return {"value": n * SUBSTEPS * frames / wall, "unit": "body-substeps/s",
+            "ms_per_step_wall": wall / frames * 1e3, "ms_per_step_slowest_device": dev_ms / frames,
+            "call": f"sfp_batch_create_multi({total} worlds, devices 0..{n_dev - 1}) + sfp_batch_multi_step "
+                    f"/ _sync from rank 0's process; partition {m.partition()}"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -647,6 +689,25 @@ def barrier(world_size):
         import torch.distributed as dist
 
         dist.barrier()
+
+
+_CPU_GROUP = None
+
+
+def cpu_barrier():
+    """a barrier that leaves the GPUs alone (an NCCL barrier parks a spinning kernel on every
+    waiting rank's GPU): a gloo group next to the NCCL one"""
+    global _CPU_GROUP
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    if dist.get_backend() == "gloo":
+        dist.barrier()
+        return
+    if _CPU_GROUP is None:
+        _CPU_GROUP = dist.new_group(backend="gloo")
+    dist.barrier(group=_CPU_GROUP)
 
 
 def _reduce_device():

@@ -14,7 +14,6 @@ pub const SFP_OK: i32 = 0;
 pub const SFP_E_INVALID: i32 = -1;
 pub const SFP_E_CUDA: i32 = -2;
 pub const SFP_E_CAPACITY: i32 = -3;
-pub const SFP_E_NCCL: i32 = -4;
 pub const SFP_E_NOMEM: i32 = -5;
 
 pub const SFP_SHAPE_CIRCLE: u32 = 0;
@@ -193,6 +192,10 @@ pub struct SfpWorld {
 pub struct SfpBatch {
     _private: [u8; 0],
 }
+#[repr(C)]
+pub struct SfpBatchMulti {
+    _private: [u8; 0],
+}
 
 extern "C" {
     // ---- single world ----
@@ -242,6 +245,24 @@ extern "C" {
     pub fn sfp_batch_stats(b: *mut SfpBatch, out: *mut SfpStats) -> i32;
     pub fn sfp_batch_last_error(b: *mut SfpBatch) -> *const c_char;
     pub fn sfp_batch_last_step_ms(b: *mut SfpBatch, ms: *mut f32) -> i32;
+    // ---- batched worlds over several GPUs from one process ----
+    pub fn sfp_batch_create_multi(params: *const SfpParams, n_worlds: u32, bodies_per_world: u32,
+                                  device_ids: *const i32, n_dev: u32, out: *mut *mut SfpBatchMulti) -> i32;
+    pub fn sfp_batch_multi_destroy(m: *mut SfpBatchMulti) -> i32;
+    pub fn sfp_batch_multi_partition(m: *mut SfpBatchMulti, dev_index: u32, device: *mut i32,
+                                     first_world: *mut u32, n_worlds: *mut u32) -> i32;
+    pub fn sfp_batch_multi_upload(m: *mut SfpBatchMulti, bodies: *const SfpBodyDesc) -> i32;
+    pub fn sfp_batch_multi_set_polygons(m: *mut SfpBatchMulti, polys: *const SfpPolygon, n: u32) -> i32;
+    pub fn sfp_batch_multi_set_joints(m: *mut SfpBatchMulti, joints: *const SfpJointDesc,
+                                      joints_per_world: u32, counts: *const u32) -> i32;
+    pub fn sfp_batch_multi_step(m: *mut SfpBatchMulti, dt: f32, substeps: u32) -> i32;
+    pub fn sfp_batch_multi_sync(m: *mut SfpBatchMulti) -> i32;
+    pub fn sfp_batch_multi_download(m: *mut SfpBatchMulti, out: *mut SfpBodyState) -> i32;
+    pub fn sfp_batch_multi_step_host(m: *mut SfpBatchMulti, input: *const SfpBodyState,
+                                     out: *mut SfpBodyState, dt: f32, substeps: u32) -> i32;
+    pub fn sfp_batch_multi_stats(m: *mut SfpBatchMulti, out: *mut SfpStats) -> i32;
+    pub fn sfp_batch_multi_last_step_ms(m: *mut SfpBatchMulti, ms: *mut f32) -> i32;
+    pub fn sfp_batch_multi_last_error(m: *mut SfpBatchMulti) -> *const c_char;
     // ---- one small world without any allocation ----
     pub fn sfp_step_small_noalloc(params: *const SfpParams, bodies: *const SfpBodyDesc, n: u32,
                                   dt: f32, substeps: u32, frames: u32, out: *mut SfpBodyState,

@@ -45,7 +45,8 @@ enum {
     SFP_E_INVALID = -1,  /* bad argument / bad state */
     SFP_E_CUDA = -2,     /* a CUDA call failed; sfp_last_error() has the string */
     SFP_E_CAPACITY = -3, /* a device buffer (entries / pairs / colours) overflowed */
-    SFP_E_NCCL = -4,
+    /* -4 is unused: the library holds no collective (statistics of batched worlds are per-world
+     * records, concatenated on the host — sfp_batch_multi_stats) */
     SFP_E_NOMEM = -5
 };
 
@@ -204,6 +205,7 @@ typedef struct SfpStats {
 
 typedef struct SfpWorld SfpWorld;
 typedef struct SfpBatch SfpBatch;
+typedef struct SfpBatchMulti SfpBatchMulti;
 
 /* ---- single world ----------------------------------------------------------------- */
 
@@ -319,6 +321,36 @@ SFP_API int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBody
 /* per-world stats: out has room for n_worlds entries (n_pairs, n_contacts, n_colours ...) */
 SFP_API int32_t sfp_batch_stats(SfpBatch* b, SfpStats* out);
 SFP_API const char* sfp_batch_last_error(SfpBatch* b);
+
+/* ---- batched worlds over several GPUs from one process ------------------------------- */
+/* Replaces: nothing in the reference (a single-process CPU engine; reference file:line
+ * unavailable); BASELINE.json config 5 asks for the batch to be partitioned over the GPUs of one
+ * box, and an engine is one process.  n_worlds worlds are cut into n_dev contiguous blocks
+ * (the first n_worlds % n_dev devices own one world more); device_ids[d] is the CUDA ordinal of
+ * block d (an ordinal may repeat).  The library keeps one SfpBatch and one worker thread per
+ * block; every call below fans out to the workers and returns when all have finished, with the
+ * first error.  Arrays are world-major over ALL worlds, exactly as for sfp_batch_*; there is no
+ * exchange between worlds and therefore no collective.  Not thread-safe (one caller at a time). */
+SFP_API int32_t sfp_batch_create_multi(const SfpParams* params, uint32_t n_worlds,
+                                       uint32_t bodies_per_world, const int32_t* device_ids,
+                                       uint32_t n_dev, SfpBatchMulti** out);
+SFP_API int32_t sfp_batch_multi_destroy(SfpBatchMulti* m);
+/* which worlds block dev_index holds, and on which device (any out pointer may be NULL) */
+SFP_API int32_t sfp_batch_multi_partition(SfpBatchMulti* m, uint32_t dev_index, int32_t* device,
+                                          uint32_t* first_world, uint32_t* n_worlds);
+SFP_API int32_t sfp_batch_multi_upload(SfpBatchMulti* m, const SfpBodyDesc* bodies);
+SFP_API int32_t sfp_batch_multi_set_polygons(SfpBatchMulti* m, const SfpPolygon* polys, uint32_t n);
+SFP_API int32_t sfp_batch_multi_set_joints(SfpBatchMulti* m, const SfpJointDesc* joints,
+                                           uint32_t joints_per_world, const uint32_t* counts);
+SFP_API int32_t sfp_batch_multi_step(SfpBatchMulti* m, float dt, uint32_t substeps);
+SFP_API int32_t sfp_batch_multi_sync(SfpBatchMulti* m);
+SFP_API int32_t sfp_batch_multi_download(SfpBatchMulti* m, SfpBodyState* out);
+SFP_API int32_t sfp_batch_multi_step_host(SfpBatchMulti* m, const SfpBodyState* in, SfpBodyState* out,
+                                          float dt, uint32_t substeps);
+SFP_API int32_t sfp_batch_multi_stats(SfpBatchMulti* m, SfpStats* out);
+/* device time of the last step: the slowest block's */
+SFP_API int32_t sfp_batch_multi_last_step_ms(SfpBatchMulti* m, float* ms);
+SFP_API const char* sfp_batch_multi_last_error(SfpBatchMulti* m);
 
 /* ---- one small world without any allocation ------------------------------------------ */
 /* No counterpart in the reference (its step is CPU code and owns no device memory); added for

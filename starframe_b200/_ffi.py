@@ -19,7 +19,6 @@ SFP_OK = 0
 SFP_E_INVALID = -1
 SFP_E_CUDA = -2
 SFP_E_CAPACITY = -3
-SFP_E_NCCL = -4
 SFP_E_NOMEM = -5
 
 SHAPE_CIRCLE, SHAPE_CAPSULE, SHAPE_RECT, SHAPE_POLYGON = 0, 1, 2, 3
@@ -114,6 +113,10 @@ PRODUCT_SYMBOLS = [
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_step_host", "batch_set_joints", "batch_set_polygons", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
     "last_step_breakdown_ms", "last_step_stage_ns", "backend", "step_small_noalloc",
+    "batch_create_multi", "batch_multi_destroy", "batch_multi_partition", "batch_multi_upload",
+    "batch_multi_set_polygons", "batch_multi_set_joints", "batch_multi_step", "batch_multi_sync",
+    "batch_multi_download", "batch_multi_step_host", "batch_multi_stats", "batch_multi_last_step_ms",
+    "batch_multi_last_error",
 ]
 ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
@@ -128,7 +131,7 @@ class SfpError(RuntimeError):
     def __init__(self, code: int, what: str, detail: str = ""):
         self.code = code
         names = {-1: "SFP_E_INVALID", -2: "SFP_E_CUDA", -3: "SFP_E_CAPACITY",
-                 -4: "SFP_E_NCCL", -5: "SFP_E_NOMEM"}
+                 -5: "SFP_E_NOMEM"}
         super().__init__(f"{what}: {names.get(code, code)}" + (f" ({detail})" if detail else ""))
 
 
@@ -199,6 +202,18 @@ class Api:
             "batch_stats": [vp, vp],
             "batch_last_step_ms": [vp, C.POINTER(f32)],
             "step_small_noalloc": [vp, vp, u32, f32, u32, u32, vp, C.c_char_p, u32],
+            "batch_create_multi": [vp, u32, u32, vp, u32, C.POINTER(vp)],
+            "batch_multi_destroy": [vp],
+            "batch_multi_partition": [vp, u32, C.POINTER(i32), C.POINTER(u32), C.POINTER(u32)],
+            "batch_multi_upload": [vp, vp],
+            "batch_multi_set_polygons": [vp, vp, u32],
+            "batch_multi_set_joints": [vp, vp, u32, vp],
+            "batch_multi_step": [vp, f32, u32],
+            "batch_multi_sync": [vp],
+            "batch_multi_download": [vp, vp],
+            "batch_multi_step_host": [vp, vp, vp, f32, u32],
+            "batch_multi_stats": [vp, vp],
+            "batch_multi_last_step_ms": [vp, C.POINTER(f32)],
         }
         for name, args in sig.items():
             if not self.has(name):
@@ -206,7 +221,7 @@ class Api:
             f = self.fn(name)
             f.argtypes = args
             f.restype = i32
-        for name in ("last_error", "batch_last_error"):
+        for name in ("last_error", "batch_last_error", "batch_multi_last_error"):
             if self.has(name):
                 f = self.fn(name)
                 f.argtypes = [vp]
@@ -497,4 +512,84 @@ class Batch:
     def last_step_ms(self) -> float:
         ms = C.c_float(0)
         self._check(self.api.fn("batch_last_step_ms")(self.h, C.byref(ms)), "batch_last_step_ms")
+        return float(ms.value)
+
+
+class BatchMulti:
+    """n_worlds worlds spread over several GPUs by the library itself, from this one process
+    (sfp_batch_create_multi): world-major arrays over ALL worlds, as for Batch."""
+
+    def __init__(self, api: Api, n_worlds: int, bodies_per_world: int, devices, params: np.ndarray | None = None,
+                 **overrides):
+        self.api = api
+        p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1).copy()
+        for k, v in overrides.items():
+            p[k] = v
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        rc = api.fn("batch_create_multi")(_ptr(p), n_worlds, bodies_per_world, _ptr(dev), len(dev), C.byref(h))
+        if rc != SFP_OK:
+            raise SfpError(rc, "batch_create_multi")
+        self.h = h
+        self.n_worlds, self.bpw, self.n_dev = n_worlds, bodies_per_world, len(dev)
+
+    def _check(self, rc: int, what: str):
+        if rc != SFP_OK:
+            detail = self.api.fn("batch_multi_last_error")(self.h)
+            raise SfpError(rc, what, detail.decode() if detail else "")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.api.fn("batch_multi_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def partition(self):
+        """[(device, first_world, n_worlds)] per block"""
+        out = []
+        for d in range(self.n_dev):
+            dev, first, n = C.c_int32(0), C.c_uint32(0), C.c_uint32(0)
+            self._check(self.api.fn("batch_multi_partition")(self.h, d, C.byref(dev), C.byref(first),
+                                                             C.byref(n)), "partition")
+            out.append((dev.value, first.value, n.value))
+        return out
+
+    def upload(self, bodies: np.ndarray):
+        b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE).reshape(-1)
+        assert b.shape[0] == self.n_worlds * self.bpw
+        self._check(self.api.fn("batch_multi_upload")(self.h, _ptr(b)), "batch_multi_upload")
+
+    def step(self, dt: float = 1.0 / 60.0, substeps: int = 8):
+        self._check(self.api.fn("batch_multi_step")(self.h, dt, substeps), "batch_multi_step")
+
+    def sync(self):
+        self._check(self.api.fn("batch_multi_sync")(self.h), "batch_multi_sync")
+
+    def download(self) -> np.ndarray:
+        out = np.zeros(self.n_worlds * self.bpw, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("batch_multi_download")(self.h, _ptr(out)), "batch_multi_download")
+        return out.reshape(self.n_worlds, self.bpw)
+
+    def step_host(self, states: np.ndarray, dt: float = 1.0 / 60.0, substeps: int = 8,
+                  out: np.ndarray | None = None) -> np.ndarray:
+        s = np.ascontiguousarray(states, dtype=BODY_STATE_DTYPE).reshape(-1)
+        if out is None:
+            out = np.zeros(self.n_worlds * self.bpw, dtype=BODY_STATE_DTYPE)
+        self._check(self.api.fn("batch_multi_step_host")(self.h, _ptr(s), _ptr(out), dt, substeps),
+                    "batch_multi_step_host")
+        return out
+
+    def stats(self) -> np.ndarray:
+        out = np.zeros(self.n_worlds, dtype=STATS_DTYPE)
+        self._check(self.api.fn("batch_multi_stats")(self.h, _ptr(out)), "batch_multi_stats")
+        return out
+
+    def last_step_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self.api.fn("batch_multi_last_step_ms")(self.h, C.byref(ms)), "batch_multi_last_step_ms")
         return float(ms.value)

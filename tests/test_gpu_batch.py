@@ -225,3 +225,51 @@ def test_batch_set_joints_rejects_bad_arguments(gpu_api):
         batch.set_joints(bad, counts)
     with pytest.raises(sf.SfpError):
         batch.set_joints(joints, counts + joints.shape[1])  # more than the slots
+
+
+def _device_count():
+    import ctypes
+
+    try:
+        rt = ctypes.CDLL("libcudart.so")
+    except OSError:
+        import torch
+
+        return torch.cuda.device_count()
+    n = ctypes.c_int(0)
+    rt.cudaGetDeviceCount(ctypes.byref(n))
+    return n.value
+
+
+@pytest.mark.parametrize("n_blocks", [2, 3])
+def test_multi_gpu_entry_equals_single_device_batch(gpu_api, n_blocks):
+    """sfp_batch_create_multi: the library spreads the worlds over the devices it is given (one
+    SfpBatch + worker thread per block).  Block d runs on GPU d when the box has that many GPUs,
+    otherwise the blocks share GPU 0 — the fan-out / join / partition code is the same."""
+    nw, bpw, frames = 37, 128, 25   # 37 worlds over 2 / 3 blocks: uneven partition
+    bodies = scenes.worlds(nw, bpw)
+    ndev = max(1, _device_count())
+    devices = [d % ndev for d in range(n_blocks)]
+    m = sf.BatchMulti(gpu_api, nw, bpw, devices)
+    part = m.partition()
+    assert [p[0] for p in part] == devices
+    assert part[0][1] == 0 and sum(p[2] for p in part) == nw
+    assert all(part[d][1] + part[d][2] == part[d + 1][1] for d in range(n_blocks - 1))
+    assert max(p[2] for p in part) - min(p[2] for p in part) <= 1
+    one = sf.Batch(gpu_api, nw, bpw)
+    m.upload(bodies)
+    one.upload(bodies)
+    for _ in range(frames):
+        m.step()
+        one.step()
+    m.sync()
+    a, b = m.download(), one.download()
+    assert a.tobytes() == b.tobytes()
+    sa, sb = m.stats(), one.stats()
+    for k in ("n_pairs", "n_contacts", "n_colours", "overflow"):
+        assert np.array_equal(sa[k], sb[k]), k
+    # the per-frame host round trip through the same entry
+    out_m = m.step_host(a.reshape(-1))
+    out_1 = one.step_host(b.reshape(-1))
+    assert out_m.tobytes() == out_1.tobytes()
+    assert m.last_step_ms() > 0.0
