@@ -1306,9 +1306,35 @@ SFP_HD_COLD bool ray_polygon(v2 o, v2 d, float tmax, v2 x, v2 q, f4 shape, const
         n_out);
 }
 
-/* closest hit of a ray with one collider; true if hit within [0, tmax] */
+/* closest hit of a ray with one collider; true if hit within [0, tmax].
+ * A ray that starts far from the collider (kilometres away: the quadratic of a disc then loses
+ * every digit to cancellation, |o - c|^2 against r^2) is first moved along itself to a point two
+ * bounding radii in front of the collider's centre; the hit parameter is the sum.  Near rays
+ * — every ray whose origin is within four bounding radii, measured along the ray — take the
+ * direct route, bit for bit as before. */
+SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f4* table, float* t_out,
+                         v2* n_out);
+SFP_HD bool ray_collider_near(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f4* table,
+                              float* t_out, v2* n_out);
 SFP_HD bool ray_collider(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f4* table, float* t_out,
                          v2* n_out) {
+    float dd = dot(d, d);
+    if (!(dd > 0.0f)) return false;
+    float bound = sqrtf(shape.x * shape.x + shape.y * shape.y) + shape.z;
+    float reach = bound / sqrtf(dd);                      /* the bounding radius in units of t */
+    float tc = dot(mk(pose.x, pose.y) - o, d) / dd;       /* closest approach to the centre */
+    if (tc > 4.0f * reach && reach > 0.0f) {
+        float tb = tc - 2.0f * reach;
+        if (tb >= tmax) return false;
+        float t;
+        if (!ray_collider_near(o + tb * d, d, tmax - tb, pose, shape, table, &t, n_out)) return false;
+        *t_out = tb + t;
+        return true;
+    }
+    return ray_collider_near(o, d, tmax, pose, shape, table, t_out, n_out);
+}
+SFP_HD bool ray_collider_near(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f4* table,
+                              float* t_out, v2* n_out) {
     v2 x = mk(pose.x, pose.y), q = mk(pose.z, pose.w);
     float r = shape.z;
     uint32_t type = shape_type(shape);

@@ -42,6 +42,7 @@ struct Counters {
     uint32_t n_colours_int;  // interior colours in use (tiles; n_colours counts the boundary ones)
     uint32_t frames_done;    // frames whose substep kernel ran to the end (capacity recovery)
     uint32_t pad_[3];
+    int qbox[4];             // spatial queries: cell bounding box of all bodies (x0, y0, x1, y1)
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
     uint32_t round_flags[MAX_ROUNDS];
@@ -51,7 +52,15 @@ struct Counters {
     unsigned long long stage_cycles[12];  // [10] / [11]: tile-interior position / velocity solve
 };
 
+// step lengths of the current frame.  They live in device memory (written before the frame's
+// launches), not in kernel arguments: a captured frame graph then serves ANY dt, where a graph
+// with dt baked in missed the cache whenever a host passed its measured frame delta.
+struct FrameParams {
+    float dt, h, rest_threshold, pad;
+};
+
 struct Ctx {
+    const FrameParams* fp;
     // body state
     float4 *pose, *prev, *vel;
     const float4 *shape, *mat;
@@ -153,6 +162,12 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
         int dyn = (mi.x > 0.0f || mi.y > 0.0f) ? 1 : 0;
         c.meta[i] = make_int4(x0, y0, (int)sfp::f2u(c.mat[i].w), dyn);
         c.cell_cnt[i] = (uint32_t)(x1 - x0 + 1) * (uint32_t)(y1 - y0 + 1);
+        if (!new_frame && x1 >= x0) {  // query hash: the world's cell bounding box
+            atomicMin(&c.cnt->qbox[0], x0);
+            atomicMin(&c.cnt->qbox[1], y0);
+            atomicMax(&c.cnt->qbox[2], x1);
+            atomicMax(&c.cnt->qbox[3], y1);
+        }
     }
     if (tid == 0 && new_frame) {
         // per-frame counters

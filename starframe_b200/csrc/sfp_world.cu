@@ -37,8 +37,8 @@ __device__ __forceinline__ uint32_t vload(const uint32_t* p) {
 }
 
 // ---- one kernel per stage (broadphase always; the rest only with SFP_FLAG_MULTI_KERNEL) ----
-__global__ void __launch_bounds__(TPB) k_aabb_count(Ctx c, float dt) {
-    stage_aabb_count(c, dt, gtid(), gnth());
+__global__ void __launch_bounds__(TPB) k_aabb_count(Ctx c) {
+    stage_aabb_count(c, c.fp->dt, gtid(), gnth());
 }
 __global__ void __launch_bounds__(TPB) k_emit_entries(Ctx c) { stage_emit_entries(c, gtid(), gnth()); }
 __global__ void __launch_bounds__(TPB) k_pair_count(Ctx c) {
@@ -190,18 +190,52 @@ __global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __re
         uint32_t best_body = 0xffffffffu;
         float best_t = r.max_t;
         v2 best_n = sfp::mk(0.0f, 0.0f);
-        int cx = sfp::cell_coord(o.x, c.inv_cell), cy = sfp::cell_coord(o.y, c.inv_cell);
-        const int sx = d.x > 0.0f ? 1 : -1, sy = d.y > 0.0f ? 1 : -1;
-        const float inf = 3.0e38f;
-        float tmx = d.x != 0.0f ? (((float)(cx + (sx > 0 ? 1 : 0))) * cell - o.x) / d.x : inf;
-        float tmy = d.y != 0.0f ? (((float)(cy + (sy > 0 ? 1 : 0))) * cell - o.y) / d.y : inf;
-        const float tdx = d.x != 0.0f ? fabsf(cell / d.x) : inf;
-        const float tdy = d.y != 0.0f ? fabsf(cell / d.y) : inf;
         if (!(d.x != 0.0f || d.y != 0.0f)) {
             hits[k] = sfp::RayHitRec{0xffffffffu, 0.0f, 0.0f, 0.0f};
             continue;
         }
-        for (int step = 0; step < 16384; ++step) {
+        // The walk is confined to the cell bounding box of the bodies (Counters::qbox): a ray
+        // that starts outside enters it at t0 (slab clip), and the walk ends when it leaves —
+        // its length is bounded by the world's extent, not by a step budget, however long the
+        // ray is.
+        const int bx0 = c.cnt->qbox[0], by0 = c.cnt->qbox[1], bx1 = c.cnt->qbox[2], by1 = c.cnt->qbox[3];
+        const float inf = 3.0e38f;
+        float t0 = 0.0f, t1 = r.max_t;
+        {
+            // (one cell of slack: the clip only has to be conservative)
+            const float lo_x = (float)(bx0 - 1) * cell, hi_x = (float)(bx1 + 2) * cell;
+            const float lo_y = (float)(by0 - 1) * cell, hi_y = (float)(by1 + 2) * cell;
+            if (d.x != 0.0f) {
+                const float a = (lo_x - o.x) / d.x, b = (hi_x - o.x) / d.x;
+                t0 = fmaxf(t0, fminf(a, b));
+                t1 = fminf(t1, fmaxf(a, b));
+            } else if (o.x < lo_x || o.x > hi_x) {
+                t1 = -1.0f;
+            }
+            if (d.y != 0.0f) {
+                const float a = (lo_y - o.y) / d.y, b = (hi_y - o.y) / d.y;
+                t0 = fmaxf(t0, fminf(a, b));
+                t1 = fminf(t1, fmaxf(a, b));
+            } else if (o.y < lo_y || o.y > hi_y) {
+                t1 = -1.0f;
+            }
+        }
+        if (bx1 < bx0 || t1 < t0) {  // no bodies, or the ray misses the box
+            hits[k] = sfp::RayHitRec{0xffffffffu, 0.0f, 0.0f, 0.0f};
+            continue;
+        }
+        // The walk runs in a parameter local to the entry point (p0 = o + t0 d, t' = t - t0): far
+        // from the scene t itself is a large float whose steps are coarser than a cell.  The hit
+        // tests below still use the caller's ray, so the reported t is the oracle's.
+        const float p0x = o.x + t0 * d.x, p0y = o.y + t0 * d.y;
+        int cx = min(max(sfp::cell_coord(p0x, c.inv_cell), bx0), bx1);
+        int cy = min(max(sfp::cell_coord(p0y, c.inv_cell), by0), by1);
+        const int sx = d.x > 0.0f ? 1 : -1, sy = d.y > 0.0f ? 1 : -1;
+        float tmx = d.x != 0.0f ? (((float)(cx + (sx > 0 ? 1 : 0))) * cell - p0x) / d.x : inf;
+        float tmy = d.y != 0.0f ? (((float)(cy + (sy > 0 ? 1 : 0))) * cell - p0y) / d.y : inf;
+        const float tdx = d.x != 0.0f ? fabsf(cell / d.x) : inf;
+        const float tdy = d.y != 0.0f ? fabsf(cell / d.y) : inf;
+        for (;;) {
             const uint32_t key = sfp::cell_key(cx, cy);
             uint32_t lo = 0, hi = E;  // lower bound of key among the sorted entries
             while (lo < hi) {
@@ -224,9 +258,11 @@ __global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __re
                     best_n = n;
                 }
             }
-            const float t_exit = fminf(tmx, tmy);
-            if (best_body != 0xffffffffu && best_t <= t_exit) break;  // nothing nearer ahead
-            if (t_exit > r.max_t) break;
+            // this cell is left at t0 + t_exit; stop when the best hit lies before that (with a
+            // margin for the rounding of the large sum: stopping late only costs a cell)
+            const float t_exit = t0 + fminf(tmx, tmy);
+            if (best_body != 0xffffffffu && best_t <= t_exit - 2.0e-6f * fabsf(t_exit)) break;
+            if (t_exit - 2.0e-6f * fabsf(t_exit) > r.max_t) break;
             if (tmx < tmy) {
                 cx += sx;
                 tmx += tdx;
@@ -234,7 +270,7 @@ __global__ void __launch_bounds__(TPB) k_ray_cast(Ctx c, const sfp::RayRec* __re
                 cy += sy;
                 tmy += tdy;
             }
-            if (cx < SFP_CELL_MIN || cx > SFP_CELL_MAX || cy < SFP_CELL_MIN || cy > SFP_CELL_MAX) break;
+            if (cx < bx0 || cx > bx1 || cy < by0 || cy > by1) break;  // left the world
         }
         hits[k] = sfp::RayHitRec{best_body, best_body == 0xffffffffu ? 0.0f : best_t, best_n.x,
                                  best_n.y};
@@ -403,8 +439,8 @@ __device__ __forceinline__ int next_bit(unsigned long long m, int after) {
 // its tiles out of shared memory (stage_tiles), then the boundary colours follow in grid-wide
 // phases as before
 template <bool POLYS, bool TILES>
-__global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, float h, uint32_t substeps,
-                                                       float rest_threshold) {
+__global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(Ctx c, uint32_t substeps) {
+    const float h = c.fp->h, rest_threshold = c.fp->rest_threshold;
     extern __shared__ float4 dyn_smem[];
     __shared__ uint32_t s_toff[3 * (SFP_MAX_COLOURS + 1)];
     cg::grid_group grid = cg::this_grid();
@@ -656,7 +692,8 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
 // 3 + 2 x (big colours + 1).
 template <bool POLYS>
 __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS)
-    k_substeps_flow(Ctx c, float h, uint32_t substeps, float rest_threshold) {
+    k_substeps_flow(Ctx c, uint32_t substeps) {
+    const float h = c.fp->h, rest_threshold = c.fp->rest_threshold;
     cg::grid_group grid = cg::this_grid();
     const uint32_t tid = gtid(), nth = gnth();
     const uint32_t lane = threadIdx.x & 31u;
@@ -763,15 +800,16 @@ struct SfpWorld {
     unsigned long long* d_tab[2] = {nullptr, nullptr};
     uint32_t tab_slots = 0;
     uint32_t colour_age = 0;  // colourings since the last upload (warm start, sfp_math.h)
-    // the frame's launch sequence captured as CUDA graphs (one per (dt, substeps, table parity,
-    // warm) combination); falls back to plain launches if capture is refused
+    // the frame's launch sequence captured as CUDA graphs (one per (substeps, table parity, warm)
+    // combination; dt travels in FrameParams); falls back to plain launches if capture is refused
     struct FrameGraph {
         cudaGraphExec_t exec = nullptr;
-        uint32_t dt_bits = 0, substeps = 0, parity = 0, warm = 0, launches = 0;
-    } graphs[4];
+        uint32_t substeps = 0, parity = 0, warm = 0, launches = 0;
+    } graphs[6];
     uint32_t graph_next = 0;
     bool graphs_ok = true, capturing = false;
     Counters* d_cnt = nullptr;
+    FrameParams* d_fp = nullptr;  // dt / h / rest threshold of the frame being queued
     // internal body order (re-sort): internal -> caller's index and back; joints as uploaded
     uint32_t *d_ext = nullptr, *d_inv = nullptr;
     uint2* d_jext = nullptr;
@@ -1017,7 +1055,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
         k_snapshot<<<gb, TPB, 0, st>>>(c, w->d_pose_bak, w->d_vel_bak);
         w->launches += 1;
     }
-    k_aabb_count<<<gb, TPB, 0, st>>>(c, dt);
+    k_aabb_count<<<gb, TPB, 0, st>>>(c);  // (dt from the frame's parameter block)
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
                       &w->d_cnt->n_entries, st));
     k_emit_entries<<<gb, TPB, 0, st>>>(c);
@@ -1110,7 +1148,7 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
     float rest_threshold = 2.0f * g * h;
     if (!multi && (w->p.flags & SFP_FLAG_FLOW_SOLVE)) {
         const uint32_t want = (uint32_t)((4ull * w->n + w->nj + SFP_SUB_TPB - 1) / SFP_SUB_TPB) + 1u;
-        void* args[] = {&c, &h, &substeps, &rest_threshold};
+        void* args[] = {&c, &substeps};
         w->launches += 1;
         if (w->has_polygons)
             return launch_coop(w, (const void*)k_substeps_flow<true>,
@@ -1122,7 +1160,7 @@ int run_substeps(SfpWorld* w, float h, uint32_t substeps) {
         uint32_t blocks = std::min<uint32_t>(
             (uint32_t)w->coop_max_substep,
             (uint32_t)((4ull * w->n + w->nj + SFP_SUB_TPB - 1) / SFP_SUB_TPB) + 1u);
-        void* args[] = {&c, &h, &substeps, &rest_threshold};
+        void* args[] = {&c, &substeps};
         w->launches += 1;
         if (c.tile_b) {
             // one block per SM; every block walks its share of the tiles
@@ -1194,14 +1232,25 @@ void drop_graphs(SfpWorld* w) {
 
 // one cudaGraphLaunch per frame instead of ~30 kernel launches
 int frame_graphed(SfpWorld* w, float dt, uint32_t substeps) {
+    // this frame's step lengths go to device memory ahead of the launches (pageable source: the
+    // driver stages it before the call returns), so one captured graph serves every dt
+    {
+        const float h = dt / (float)substeps;
+        const float g = sqrtf(w->p.gravity_x * w->p.gravity_x + w->p.gravity_y * w->p.gravity_y);
+        FrameParams fp;
+        fp.dt = (w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP) ? h : dt;
+        fp.h = h;
+        fp.rest_threshold = 2.0f * g * h;
+        fp.pad = 0.0f;
+        CU(cudaMemcpyAsync(w->d_fp, &fp, sizeof(fp), cudaMemcpyHostToDevice, w->stream));
+    }
     const bool direct = !w->graphs_ok || w->n == 0 ||
                         (w->p.flags & (SFP_FLAG_MULTI_KERNEL | SFP_FLAG_BROADPHASE_EVERY_SUBSTEP));
     if (direct) return frame(w, dt, substeps);
-    const uint32_t dt_bits = sfp::f2u(dt), parity = w->colour_age & 1u;
+    const uint32_t parity = w->colour_age & 1u;
     const uint32_t warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
     for (auto& g : w->graphs)
-        if (g.exec && g.dt_bits == dt_bits && g.substeps == substeps && g.parity == parity &&
-            g.warm == warm) {
+        if (g.exec && g.substeps == substeps && g.parity == parity && g.warm == warm) {
             CU(cudaGraphLaunch(g.exec, w->stream));
             w->colour_age += 1;
             w->launches = g.launches;
@@ -1230,10 +1279,11 @@ int frame_graphed(SfpWorld* w, float dt, uint32_t substeps) {
         w->colour_age = age0;
         return frame(w, dt, substeps);
     }
-    auto& slot = w->graphs[w->graph_next++ & 3u];
+    // (substeps, table parity, warm): 2 x 2 combinations per substep count; six slots hold a
+    // host that alternates between two substep counts
+    auto& slot = w->graphs[w->graph_next++ % 6u];
     if (slot.exec) cudaGraphExecDestroy(slot.exec);
     slot.exec = exec;
-    slot.dt_bits = dt_bits;
     slot.substeps = substeps;
     slot.parity = parity;
     slot.warm = warm;
@@ -1385,6 +1435,8 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
     if ((e = cudaMalloc(&w->d_cnt, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMemset(w->d_cnt, 0, sizeof(Counters))) != cudaSuccess) return fail("cudaMemset", e);
     w->ctx.cnt = w->d_cnt;
+    if ((e = cudaMalloc(&w->d_fp, sizeof(FrameParams))) != cudaSuccess) return fail("cudaMalloc", e);
+    w->ctx.fp = w->d_fp;
     int per_sm = 0;
     if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_colour_coop, TPB, 0)) !=
         cudaSuccess)
@@ -1439,6 +1491,7 @@ int32_t sfp_destroy(SfpWorld* w) {
     free_bag(w->pair_allocs);
     free_bag(w->joint_allocs);
     if (w->d_cnt) cudaFree(w->d_cnt);
+    if (w->d_fp) cudaFree(w->d_fp);
     if (w->pin_state) cudaFreeHost(w->pin_state);
     if (w->d_rays) cudaFree(w->d_rays);
     if (w->d_hits) cudaFree(w->d_hits);
@@ -1857,6 +1910,8 @@ int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hit
     // it reuses the broadphase buffers, which are scratch between frames
     Ctx& c = w->ctx;
     const uint32_t gb = blocks_for(w, w->n);
+    const int qinit[4] = {0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000};
+    CU(cudaMemcpyAsync(w->d_cnt->qbox, qinit, sizeof(qinit), cudaMemcpyHostToDevice, st));
     k_query_aabbs<<<gb, TPB, 0, st>>>(c);
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
                       &w->d_cnt->n_entries, st));

@@ -131,3 +131,33 @@ def test_ray_cast_and_box_query_match_oracle(gpu_api, ref_api, scene):
         r.step()
     assert g.download_bodies().tobytes() == r.download_bodies().tobytes()
     assert np.array_equal(g.get_pairs(), r.get_pairs())
+
+
+@pytest.mark.gpu
+def test_long_rays_from_far_away_match_oracle(gpu_api, ref_api):
+    """rays that start kilometres from the scene (tens of thousands of 0.5 m cells away, more
+    with small cells) and rays that miss it: the device walk is confined to the bodies' cell
+    bounding box, so its length does not depend on how long the ray is"""
+    b, j = scenes.mixed_pile(3000)
+    rng = np.random.default_rng(3)
+    n = 400
+    rays = np.zeros(n, dtype=RAY_DTYPE)
+    ang = rng.uniform(0, 2 * np.pi, n)
+    dist = rng.choice([30.0, 900.0, 9000.0, 60000.0], n)
+    tx, ty = rng.uniform(-10, 10, n), rng.uniform(0.0, 6.0, n)   # aim at the pile (most rays)
+    rays["ox"], rays["oy"] = tx + dist * np.cos(ang), ty + dist * np.sin(ang)
+    ln = rng.uniform(0.5, 2.0, n)
+    rays["dx"], rays["dy"] = -np.cos(ang) * ln, -np.sin(ang) * ln
+    rays[:40]["dy"] += 0.7                                        # some miss the scene entirely
+    rays["max_t"] = 1.0e6
+    rays["mask"] = 0xFFFF
+    for cell in (0.5, 0.05):
+        g, r = sf.World(gpu_api, cell_size=cell), sf.World(ref_api, cell_size=cell)
+        for w in (g, r):
+            w.upload_bodies(b)
+        for _ in range(30):
+            g.step()
+            r.step()
+        hg, hr = g.ray_cast(rays), r.ray_cast(rays)
+        assert (hr["body"] != NONE).sum() > 200
+        assert hg.tobytes() == hr.tobytes()
