@@ -791,13 +791,20 @@ SFP_HD uint32_t pair_type_key(f4 shape_a, f4 shape_b) {
 }
 
 /* bounding-circle reject: most candidate pairs of a frame are not touching in a given substep,
- * and this costs a dozen flops instead of a SAT */
-SFP_HD bool narrowphase_far(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float margin) {
+ * and this costs a dozen flops instead of a SAT.  The reach of a pair (sum of the two bounding
+ * radii plus the margin) does not change within a frame: the device computes it once per frame
+ * per pair (narrowphase_reach) and tests with narrowphase_far_reach; same operations, same bits. */
+SFP_HD float narrowphase_reach(f4 shape_a, f4 shape_b, float margin) {
     float ba = sqrtf(shape_a.x * shape_a.x + shape_a.y * shape_a.y) + shape_a.z;
     float bb = sqrtf(shape_b.x * shape_b.x + shape_b.y * shape_b.y) + shape_b.z;
+    return (ba + bb) + margin;
+}
+SFP_HD bool narrowphase_far_reach(f4 pose_a, f4 pose_b, float reach) {
     float dx = pose_b.x - pose_a.x, dy = pose_b.y - pose_a.y;
-    float reach = (ba + bb) + margin;
     return dx * dx + dy * dy >= reach * reach;
+}
+SFP_HD bool narrowphase_far(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float margin) {
+    return narrowphase_far_reach(pose_a, pose_b, narrowphase_reach(shape_a, shape_b, margin));
 }
 SFP_HD ContactRec empty_contact() {
     ContactRec c;
@@ -807,19 +814,27 @@ SFP_HD ContactRec empty_contact() {
     return c;
 }
 
-/* the contact record of a pair that passed narrowphase_far() */
+/* material of a pair (mu_s, mu_d, e): mean friction, larger restitution */
+SFP_HD void pair_material(f4 mat_a, f4 mat_b, float* mu_s, float* mu_d, float* e) {
+    *mu_s = 0.5f * (mat_a.x + mat_b.x);
+    *mu_d = 0.5f * (mat_a.y + mat_b.y);
+    *e = fmaxf(mat_a.z, mat_b.z);
+}
+
+/* the contact record of a pair that passed narrowphase_far(), from the pair's material */
 template <bool POLYS>
-SFP_HD ContactRec narrowphase_near(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
-                                   f4 shape_b, f4 mat_b, float margin, const f4* table) {
+SFP_HD ContactRec narrowphase_near_mat(f4 pose_a, f4 vel_a, f4 shape_a, f4 pose_b, f4 vel_b,
+                                       f4 shape_b, float mu_s, float mu_d, float e, float margin,
+                                       const f4* table) {
     ContactRec c;
     Manifold m = collide<POLYS>(pose_a, shape_a, pose_b, shape_b, margin, table);
     v2 qa = mk(pose_a.z, pose_a.w), qb = mk(pose_b.z, pose_b.w);
     v2 dab = mk(pose_b.x - pose_a.x, pose_b.y - pose_a.y);
     c.a.x = m.n.x;
     c.a.y = m.n.y;
-    c.a.z = 0.5f * (mat_a.x + mat_b.x);
-    c.a.w = 0.5f * (mat_a.y + mat_b.y);
-    c.b.x = fmaxf(mat_a.z, mat_b.z);
+    c.a.z = mu_s;
+    c.a.w = mu_d;
+    c.b.x = e;
     c.b.y = u2f((uint32_t)m.count);
     float vn[2];
     f4 pp[2];
@@ -846,6 +861,15 @@ SFP_HD ContactRec narrowphase_near(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4
     c.s.z = 0.0f;
     c.s.w = 0.0f;
     return c;
+}
+
+template <bool POLYS>
+SFP_HD ContactRec narrowphase_near(f4 pose_a, f4 vel_a, f4 shape_a, f4 mat_a, f4 pose_b, f4 vel_b,
+                                   f4 shape_b, f4 mat_b, float margin, const f4* table) {
+    float mu_s, mu_d, e;
+    pair_material(mat_a, mat_b, &mu_s, &mu_d, &e);
+    return narrowphase_near_mat<POLYS>(pose_a, vel_a, shape_a, pose_b, vel_b, shape_b, mu_s, mu_d, e,
+                                       margin, table);
 }
 
 template <bool POLYS>

@@ -1,12 +1,15 @@
-"""Small driver for profiling the single-world kernels: settle, then 3 more frames."""
+"""Small driver for profiling the single-world kernels: settle, then 3 more frames.
+  python scripts/prof_world.py [workload] [settle_frames] [flags]   (flags 2: one kernel per stage)"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import starframe_b200 as sf
 from bench import make_scene
 name = sys.argv[1] if len(sys.argv) > 1 else "pile100k"
 settle = int(sys.argv[2]) if len(sys.argv) > 2 else 240
+flags = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 b, j = make_scene(name)
-w = sf.World(sf.product_api()); w.upload_bodies(b); w.set_joints(j)
+w = sf.World(sf.product_api(), flags=flags); w.upload_bodies(b); w.set_joints(j)
 for _ in range(settle + 3): w.step()
 w.sync()
-print(name, "frame ms", w.last_step_ms(), w.stats()["n_pairs"])
+st = w.stats()
+print(name, "frame ms", w.last_step_ms(), "pairs", st["n_pairs"], "entries", st["n_entries"], "contacts", st["n_contacts"])

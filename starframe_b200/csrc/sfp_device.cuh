@@ -111,6 +111,10 @@ struct Ctx {
     float4 *janc, *jpar;
     // contacts (per colour-sorted pair)
     float4 *ca, *cb, *cp0, *cp1, *cs, *lam;
+    // per sorted pair, constant within a frame (written by stage_gather, read by every substep's
+    // narrowphase with coalesced loads instead of four gathers): the two shapes, and
+    // (mu_s, mu_d, e, reach of the bounding-circle test).  Null: gather from the bodies.
+    float4 *psa, *psb, *pmt;
     Counters* cnt;
     // parameters
     float gx, gy, inv_cell, aabb_margin, vel_expand, contact_margin;
@@ -524,6 +528,18 @@ __device__ __forceinline__ void serial_sort_pairs(const Ctx& c, uint32_t ncol) {
             if (xa > ya || (xa == ya && xb > yb)) {
                 c.pairs[first + i] = y;
                 c.pairs[first + i + 1u] = x;
+                if (c.psa) {  // the pairs' per-frame narrowphase constants move with them
+                    const uint32_t u = first + i, v = u + 1u;
+                    float4 t = c.psa[u];
+                    c.psa[u] = c.psa[v];
+                    c.psa[v] = t;
+                    t = c.psb[u];
+                    c.psb[u] = c.psb[v];
+                    c.psb[v] = t;
+                    t = c.pmt[u];
+                    c.pmt[u] = c.pmt[v];
+                    c.pmt[v] = t;
+                }
             }
         }
         __syncthreads();
@@ -642,7 +658,18 @@ __device__ __forceinline__ void group_offsets(const uint32_t* sorted, uint32_t n
 
 __device__ __forceinline__ void stage_gather(const Ctx& c, uint32_t tid, uint32_t nth) {
     const uint32_t P = c.cnt->n_pairs;
-    for (uint32_t i = tid; i < P; i += nth) c.pairs[i] = c.pairs_raw[c.pperm[i]];
+    for (uint32_t i = tid; i < P; i += nth) {
+        const uint2 p = c.pairs_raw[c.pperm[i]];
+        c.pairs[i] = p;
+        if (c.psa) {  // the narrowphase's per-frame constants of this pair
+            const f4 sa = ld4(c.shape, p.x), sb = ld4(c.shape, p.y);
+            float mu_s, mu_d, e;
+            sfp::pair_material(ld4(c.mat, p.x), ld4(c.mat, p.y), &mu_s, &mu_d, &e);
+            st4(c.psa, i, sa);
+            st4(c.psb, i, sb);
+            c.pmt[i] = make_float4(mu_s, mu_d, e, sfp::narrowphase_reach(sa, sb, c.contact_margin));
+        }
+    }
     group_offsets<false>(c.pcol_sorted, P, c.n_tiles, c.goff, c.cnt->pair_col_off, tid, nth);
     for (uint32_t i = tid; i < c.nj; i += nth) {
         uint32_t s = c.jperm[i];
@@ -704,7 +731,7 @@ __device__ __forceinline__ void flow_mark_noop(const Ctx& c, uint32_t k, uint2 p
     }
 }
 
-template <bool POLYS, bool MARK = false>
+template <bool POLYS, bool MARK = false, bool STAGED = false>
 __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, uint32_t nth) {
     // Per block-sized chunk of pairs: (1) every thread tests its pair's bounding circles; a pair
     // that is out of reach gets its empty record at once.  (2) The SAT for the pairs in reach.
@@ -734,8 +761,11 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
         }
         if (k < P) {
             uint2 p = c.pairs[k];
-            near = !sfp::narrowphase_far(ld4(c.pose, p.x), ld4(c.shape, p.x), ld4(c.pose, p.y),
-                                         ld4(c.shape, p.y), c.contact_margin);
+            if (STAGED)
+                near = !sfp::narrowphase_far_reach(ld4(c.pose, p.x), ld4(c.pose, p.y), c.pmt[k].w);
+            else
+                near = !sfp::narrowphase_far(ld4(c.pose, p.x), ld4(c.shape, p.x), ld4(c.pose, p.y),
+                                             ld4(c.shape, p.y), c.contact_margin);
             if (!near) {
                 c.cb[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 if (MARK) flow_mark_noop(c, k, p, true);
@@ -755,10 +785,19 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
         }
         if (k2 != NONE) {
             uint2 p = c.pairs[k2];
-            sfp::ContactRec r = sfp::narrowphase_near<POLYS>(
-                ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x), ld4(c.mat, p.x), ld4(c.pose, p.y),
-                ld4(c.vel, p.y), ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin,
-                reinterpret_cast<const sfp::f4*>(c.polytab));
+            sfp::ContactRec r;
+            if (STAGED) {
+                const float4 m = c.pmt[k2];
+                r = sfp::narrowphase_near_mat<POLYS>(
+                    ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.psa, k2), ld4(c.pose, p.y), ld4(c.vel, p.y),
+                    ld4(c.psb, k2), m.x, m.y, m.z, c.contact_margin,
+                    reinterpret_cast<const sfp::f4*>(c.polytab));
+            } else {
+                r = sfp::narrowphase_near<POLYS>(
+                    ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x), ld4(c.mat, p.x), ld4(c.pose, p.y),
+                    ld4(c.vel, p.y), ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin,
+                    reinterpret_cast<const sfp::f4*>(c.polytab));
+            }
             uint32_t cnt = sfp::f2u(r.b.y);
             st4(c.cb, k2, r.b);
             if (MARK && cnt == 0u) flow_mark_noop(c, k2, p, true);

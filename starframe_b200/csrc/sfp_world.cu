@@ -29,6 +29,11 @@ using namespace sfpk;
 namespace {
 
 constexpr int TPB = 256;
+#ifdef SFP_NO_STAGED
+constexpr bool NP_STAGED = false;
+#else
+constexpr bool NP_STAGED = true;
+#endif
 
 __device__ __forceinline__ uint32_t gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
 __device__ __forceinline__ uint32_t gnth() { return gridDim.x * blockDim.x; }
@@ -64,7 +69,7 @@ __global__ void __launch_bounds__(TPB) k_integrate(Ctx c, float h) {
 }
 template <bool POLYS>
 __global__ void __launch_bounds__(TPB) k_narrowphase(Ctx c) {
-    stage_narrowphase<POLYS>(c, gtid(), gnth());
+    stage_narrowphase<POLYS, false, NP_STAGED>(c, gtid(), gnth());
 }
 __global__ void __launch_bounds__(TPB) k_solve_pos(Ctx c, uint32_t colour, float inv_h2) {
     stage_solve_pos(c, colour, inv_h2, gtid(), gnth());
@@ -541,7 +546,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS) k_substeps_coop(C
         stage_integrate(c, h, tid, nth);
         grid.sync();
         lap(4);
-        stage_narrowphase<POLYS>(c, tid, nth);
+        stage_narrowphase<POLYS, false, NP_STAGED>(c, tid, nth);
         grid.sync();
         lap(5);
         if (TILES) {
@@ -733,7 +738,7 @@ __global__ void __launch_bounds__(SFP_SUB_TPB, SFP_SUB_BLOCKS)
         stage_integrate(c, h, tid, nth);
         grid.sync();
         lap(4);
-        stage_narrowphase<POLYS, true>(c, tid, nth);
+        stage_narrowphase<POLYS, true, NP_STAGED>(c, tid, nth);
         grid.sync();
         lap(5);
         flow_solve_pos(c, s_fo, s_joff, s_poff, inv_h2, gwarp, nwarps, lane);
@@ -891,6 +896,9 @@ int alloc_pair_arrays(SfpWorld* w, uint32_t ce, uint32_t cp) {
     TRY(alloc_dev(w, &c.cp1, cp, bag));
     TRY(alloc_dev(w, &c.cs, cp, bag));
     TRY(alloc_dev(w, &c.lam, cp, bag));
+    TRY(alloc_dev(w, &c.psa, cp, bag));
+    TRY(alloc_dev(w, &c.psb, cp, bag));
+    TRY(alloc_dev(w, &c.pmt, cp, bag));
     TRY(alloc_dev(w, &w->d_evt_flag, cp + 1, bag));
     TRY(alloc_dev(w, &w->d_evt_off, cp + 1, bag));
     TRY(alloc_dev(w, &w->d_events, cp, bag));
