@@ -254,13 +254,15 @@ class Api:
 
 
 def step_small_noalloc(api: "Api", bodies: np.ndarray, frames: int = 1, dt: float = 1.0 / 60.0,
-                       substeps: int = 8, params: np.ndarray | None = None) -> np.ndarray:
+                       substeps: int = 8, params: np.ndarray | None = None, **overrides) -> np.ndarray:
     """sfp_step_small_noalloc: one small world stepped inside the library's fixed scratch
     array — for hosts that may not allocate device memory while running (include/sfp.h)."""
     b = np.ascontiguousarray(bodies, dtype=BODY_DESC_DTYPE)
     out = np.zeros(b.shape[0], dtype=BODY_STATE_DTYPE)
     err = C.create_string_buffer(512)
-    p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1)
+    p = api.default_params() if params is None else np.array(params, dtype=PARAMS_DTYPE).reshape(1).copy()
+    for k, v in overrides.items():
+        p[k] = v
     rc = api.fn("step_small_noalloc")(_ptr(p), _ptr(b), b.shape[0], dt, substeps, frames,
                                       _ptr(out), err, 512)
     if rc != SFP_OK:

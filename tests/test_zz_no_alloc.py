@@ -74,3 +74,33 @@ def test_no_alloc_entry_refuses_worlds_beyond_its_array(gpu_api):
     got = _ffi.step_small_noalloc(gpu_api, ok, frames=5)
     want, _ = reference_result(gpu_api, ok, 5)
     assert_bit_identical(got, want)
+
+
+def test_no_alloc_entry_and_batch_entry_overflow_at_the_same_point(gpu_api):
+    """The two entry points give a world the same pair capacity (12 n + 256), so a small dense
+    world that has more candidate pairs than that is refused by BOTH, and one just under the
+    limit is stepped by both with identical bits."""
+    def blob(n_side, margin):
+        b = scenes.empty_bodies(n_side * n_side)
+        k = np.arange(n_side * n_side)
+        b["x"] = 0.2 * (k % n_side) + 0.003 * scenes.uniform(7, 1, len(k))
+        b["y"] = 0.12 + 0.2 * (k // n_side) + 0.003 * scenes.uniform(7, 2, len(k))
+        b["shape"], b["radius"] = 0, 0.09
+        return np.concatenate([b, scenes.static_rect(2.0, -0.5, 5.0, 0.5)]), margin
+
+    # ~22 candidate pairs per body with the wide margin: 13 k pairs for 626 bodies > 12 n + 256
+    dense, margin = blob(25, 0.26)
+    with pytest.raises(sf.SfpError) as e1:
+        _ffi.step_small_noalloc(gpu_api, dense, frames=2, aabb_margin=margin)
+    assert e1.value.code == _ffi.SFP_E_CAPACITY
+    batch = sf.Batch(gpu_api, 1, len(dense), aabb_margin=margin)
+    batch.upload(dense)
+    batch.step()
+    with pytest.raises(sf.SfpError) as e2:
+        batch.stats()
+    assert e2.value.code == _ffi.SFP_E_CAPACITY
+    # the default margin: a handful of pairs per body, both succeed and agree
+    loose, _ = blob(25, 0.02)
+    got = _ffi.step_small_noalloc(gpu_api, loose, frames=20)
+    want, _ = reference_result(gpu_api, loose, 20)
+    assert_bit_identical(got, want)
