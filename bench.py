@@ -117,12 +117,17 @@ class ClockSampler:
                         "and one right after it"}
 
 
-def ncu_traffic(workload):
-    """DRAM bytes per launch of the dominant kernel, from the committed ncu capture (or None)"""
+def ncu_traffic(workload, worlds=None):
+    """DRAM bytes per launch of the dominant kernel, from the committed ncu capture (or None);
+    the batched kernel's capture is scaled to the number of worlds this launch steps"""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     try:
         with open(p) as f:
-            return json.load(f).get(workload, {}).get("bytes_per_launch")
+            e = json.load(f).get(workload, {})
+        b = e.get("bytes_per_launch")
+        if b is not None and worlds and e.get("worlds_per_launch"):
+            b = b * worlds / e["worlds_per_launch"]
+        return b
     except Exception:
         return None
 
@@ -549,7 +554,7 @@ def run_worlds(args, rank, world_size):
                    "collective": "statistics only (all_reduce of 3 floats after the timed region)"},
         "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one CTA per world, whole frame)",
                      "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                     "peak_source": peak_src, "traffic": ncu_traffic("worlds512"),
+                     "peak_source": peak_src, "traffic": ncu_traffic("worlds512", nw),
                      "peak_nominal": 8000.0, "frac_nominal": ach / 8000.0,
                      "algorithmic_bytes_per_launch": bytes_step,
                      "note": "traffic < algorithmic bytes: the per-substep re-reads the algorithmic "
