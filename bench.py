@@ -190,6 +190,8 @@ def make_scene(workload: str):
         return scenes.ropes()
     if workload == "stack100":
         return scenes.stack100()
+    if workload.startswith("polys"):  # a mixed pile in which half of the bodies are general polygons
+        return scenes.polygon_pile(int(workload[5:] or 100_000))
     if workload.startswith("shelves"):
         return scenes.shelves(int(workload[7:] or 4_000_000))
     if workload.startswith("pile"):
@@ -324,7 +326,7 @@ def run_single(args, rank, world_size):
         # the other single-GPU configs of BASELINE.json, measured the same way (short runs);
         # they are parity-test cases first, these lines are context for the headline
         del w
-        out["other_configs"] = {name: quick_config(name, args) for name in ("circles10k", "ropes2k")}
+        out["other_configs"] = {name: quick_config(name, args) for name in ("circles10k", "ropes2k", "polys100000")}
         out["other_configs"]["worlds512_8192_1gpu"] = quick_worlds(args)
         # the same pile uploaded in a random body order (the library re-sorts internally)
         out["shuffled_order"] = quick_config(args.workload, args, shuffle=True)
@@ -341,10 +343,14 @@ def quick_config(name, args, frames=30, shuffle=False):
 
     import starframe_b200 as sf
 
-    bodies, joints = make_scene(name)
+    scene = make_scene(name)
+    bodies, joints = scene[0], scene[1]
+    polys = scene[2] if len(scene) > 2 else None
     if shuffle:
         bodies, joints = shuffle_scene(bodies, joints)
     w = sf.World(sf.product_api(), device=torch.cuda.current_device())
+    if polys is not None:
+        w.set_polygons(polys)
     w.upload_bodies(bodies)
     w.set_joints(joints)
     for _ in range(args.settle):

@@ -7,9 +7,12 @@ import starframe_b200 as sf
 from bench import make_scene
 name = sys.argv[1] if len(sys.argv) > 1 else "pile100k"
 flags = int(sys.argv[2]) if len(sys.argv) > 2 else 0
-b, j = make_scene(name)
+scene = make_scene(name)
+b, j = scene[0], scene[1]
 api = sf.product_api()
-w = sf.World(api, flags=flags); w.upload_bodies(b); w.set_joints(j)
+w = sf.World(api, flags=flags)
+if len(scene) > 2: w.set_polygons(scene[2])
+w.upload_bodies(b); w.set_joints(j)
 for _ in range(240): w.step()
 w.sync()
 acc = {}
@@ -21,4 +24,4 @@ out = np.zeros(12, dtype=np.uint64); fn(w.h, out.ctypes.data_as(C.c_void_p))
 names = {4: "integrate", 5: "narrow", 6: "pos", 7: "derive", 8: "vel", 9: "tails", 10: "tile_pos", 11: "tile_vel"}
 st = w.stats()
 print(os.path.basename(os.environ.get("SFP_B200_LIB", "default")), name, "flags", flags, {k: round(v, 4) for k, v in acc.items()},
-      "overflow", st["overflow"], {names[k]: round(float(out[k]) / 1e3) for k in names}, flush=True)
+      "overflow", st["overflow"], "pairs/body", round(st["n_pairs"] / len(b), 2), "contacts/body", round(st["n_contacts"] / len(b), 2), "colours", st["n_colours"], {names[k]: round(float(out[k]) / 1e3) for k in names}, flush=True)

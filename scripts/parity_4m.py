@@ -1,15 +1,19 @@
 """One-off: the 4 M-body scale point, frames from a settled state, CUDA vs the CPU oracle (all
 host threads) — pair set, counts and every state bit.  Too slow for the test suite (the oracle
-needs ~20 s per frame at this size)."""
+needs ~20 s per frame at this size).  Optional third argument "shuffle": the bodies are uploaded
+in a random order."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["SFP_REF_THREADS"] = str(os.cpu_count())
 import numpy as np
 import starframe_b200 as sf
-from bench import make_scene
+from bench import make_scene, shuffle_scene
 from oracle import loader
 b, j = make_scene(sys.argv[1] if len(sys.argv) > 1 else "shelves4000000")
 frames = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+if len(sys.argv) > 3 and sys.argv[3] == "shuffle":
+    b, j = shuffle_scene(b, j)
+    print("bodies uploaded in a random order")
 settle = sf.World(sf.product_api())
 settle.upload_bodies(b)
 for _ in range(200):
