@@ -27,6 +27,7 @@ pub const SFP_FLAG_BROADPHASE_EVERY_SUBSTEP: u32 = 1;
 pub const SFP_FLAG_MULTI_KERNEL: u32 = 2;
 pub const SFP_FLAG_FLOW_SOLVE: u32 = 4;
 pub const SFP_FLAG_TILES: u32 = 8;
+pub const SFP_FLAG_BATCH_WHOLE_WORLDS: u32 = 16;
 
 #[repr(C)]
 #[derive(Clone, Copy)]

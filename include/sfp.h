@@ -92,9 +92,15 @@ enum {
                                                persistent cooperative substep kernel (debug) */
     SFP_FLAG_TILES = 8u,                    /* solve order: tile-interior constraints first,
                                                then the boundary ones (sfp_math.h, "Tiles")  */
-    SFP_FLAG_FLOW_SOLVE = 4u                /* CUDA: per-body dependency masks instead of a
+    SFP_FLAG_FLOW_SOLVE = 4u,               /* CUDA: per-body dependency masks instead of a
                                                grid-wide barrier after every colour (same
                                                results, measured slower; an experiment)      */
+    SFP_FLAG_BATCH_WHOLE_WORLDS = 16u       /* batches: always one CTA per world, start to end.
+                                               Default: a batch with more worlds than CTAs fit
+                                               on the GPU at once runs that many CTAs, which
+                                               take worlds from a queue — most of them whole,
+                                               the last one to two per CTA a stage at a time,
+                                               so that all CTAs end together (same results)   */
 };
 
 /* ---- parameters ------------------------------------------------------------------- */

@@ -29,6 +29,7 @@ FLAG_BROADPHASE_EVERY_SUBSTEP = 1
 FLAG_MULTI_KERNEL = 2
 FLAG_FLOW_SOLVE = 4
 FLAG_TILES = 8
+FLAG_BATCH_WHOLE_WORLDS = 16
 
 # numpy mirrors of the PODs (sizes asserted against the C side's static_asserts)
 PARAMS_DTYPE = np.dtype(

@@ -50,7 +50,12 @@ struct BatchCtx {
     Counters* counters;    // [n_worlds]
     uint32_t* scratch;     // [n_worlds][bpw] per-body pair counts / offsets
     uint32_t tab_slots;    // colour-table slots per world (power of two)
-    uint32_t world_base;   // first world of this launch (blockIdx.x counts from it)
+    uint32_t world_base;   // first world of this launch
+    uint32_t n_launch;     // worlds of this launch: [world_base, world_base + n_launch)
+    uint32_t n_whole;      // the first n_whole of them are handed out whole (k_batch_frame)
+    struct BatchQueue* queue;  // this launch's queue, or null: CTA i runs world world_base + i
+    uint32_t* ring;        // [n_launch - n_whole] ring of worlds between two stages
+    uint32_t* progress;    // [n_worlds] stages done of a world that is handed out by the stage
     uint32_t joint_cap;    // joint slots per world (0: the batch has no joints)
     const uint32_t* n_joints;  // [n_worlds] joints in use per world, or null
 };
@@ -228,26 +233,39 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
 // FULL: the variant that can collide general polygons and solve joints (more registers and
 // code: two CTAs per SM); the host launches it only for batches that hold a polygon body or
 // a joint, so that plain worlds keep the lean kernel
-template <bool SMEM, bool FULL = false>
-__global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
-    k_batch_frame(BatchCtx b, float dt, uint32_t substeps, float rest_threshold) {
+// stages [sa, se) of world w's frame (stage 0: pairs and colours; stage s >= 1: substep s)
+template <bool SMEM, bool FULL>
+__device__ __forceinline__ void batch_world_stages(const BatchCtx& b, uint32_t w, uint32_t sa, uint32_t se,
+                                                float dt, uint32_t substeps, float rest_threshold) {
     extern __shared__ float4 dyn[];
     __shared__ uint32_t smem9[9];
-    const uint32_t w = blockIdx.x + b.world_base;
-    if (w >= b.n_worlds) return;
+    // colour order as a list, and a per-thread shared-memory slot into which the contact record
+    // of this thread's first item of the NEXT colour is copied asynchronously (cp.async, no
+    // registers held across the barrier): after the barrier only shared-memory reads remain
+    // before the solve, instead of two dependent L2 / HBM round trips.
+    __shared__ uint8_t s_order[SFP_MAX_COLOURS];
+    __shared__ uint32_t s_nord;
+    __shared__ float4 s_rec[4][BTPB];
+    __shared__ float4 s_lam[BTPB];
+    __shared__ uint2 s_pair[BTPB];
+    const uint32_t tid = threadIdx.x, nth = blockDim.x;
+    const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
+    auto next_bit = [](unsigned long long m, int after) {
+        unsigned long long r = (after >= 63) ? 0ull : (m & (~0ull << (after + 1)));
+        return r ? (__ffsll((long long)r) - 1) : 64;
+    };
     Ctx c = world_view(b, w);
     if (!FULL) c.nj = 0;  // compile-time: the lean variant carries no joint code
-    const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
-    uint32_t* cnt_off = b.scratch + (size_t)w * b.bpw;
+    const uint32_t n = c.n;
     float4 *g_pose = c.pose, *g_vel = c.vel;
     long long t_prev = clock64();
     unsigned long long cyc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 #define LAP(slot)                          \
-    do {                                   \
-        long long t_now = clock64();       \
-        cyc[slot] += (unsigned long long)(t_now - t_prev); \
-        t_prev = t_now;                    \
-    } while (0)
+do {                                   \
+    long long t_now = clock64();       \
+    cyc[slot] += (unsigned long long)(t_now - t_prev); \
+    t_prev = t_now;                    \
+} while (0)
     if (SMEM) {
         float4* s_pose = dyn;
         float4* s_vel = dyn + n;
@@ -256,8 +274,8 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
         float2* s_minv = reinterpret_cast<float2*>(dyn + 4 * (size_t)n);
         unsigned long long* s_mask = reinterpret_cast<unsigned long long*>(s_minv + n);
         for (uint32_t i = tid; i < n; i += nth) {
-            s_pose[i] = g_pose[i];
-            s_vel[i] = g_vel[i];
+            s_pose[i] = __ldcg(&g_pose[i]);
+            s_vel[i] = __ldcg(&g_vel[i]);
             s_minv[i] = c.minv[i];
         }
         c.pose = s_pose;
@@ -273,31 +291,35 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
     }
     LAP(0);
 
-    batch_broadphase(c, cnt_off, dt, smem9);
-    LAP(1);
+    if (sa == 0u) {
+        batch_broadphase(c, nullptr, dt, smem9);
+        LAP(1);
 
-    // colouring: same rounds as stage_colour_* in the single-world path
-    stage_colour_init(c, tid, nth);
-    for (uint32_t k = tid; k <= c.tab_mask; k += nth) c.tab_new[k] = 0ull;
-    __syncthreads();
-    if (c.warm) {
-        stage_colour_warm(c, tid, nth);
+        // colouring: same rounds as stage_colour_* in the single-world path
+        stage_colour_init(c, tid, nth);
+        for (uint32_t k = tid; k <= c.tab_mask; k += nth) c.tab_new[k] = 0ull;
+        __syncthreads();
+        if (c.warm) {
+            stage_colour_warm(c, tid, nth);
+            __syncthreads();
+        }
+        uint32_t round = 0;
+        for (; round < (uint32_t)MAX_ROUNDS; ++round) {
+            stage_colour_bid(c, round, tid, nth);
+            __syncthreads();
+            stage_colour_take(c, round, tid, nth);
+            __syncthreads();
+            if (c.cnt->round_flags[round] == 0u) break;
+        }
+        if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
+        stage_colour_record(c, tid, nth);
+        __syncthreads();
+        LAP(2);
+        batch_bucket(c, smem9);
+        LAP(3);
+        if (c.cnt->n_colours > SFP_SERIAL_COLOUR) serial_sort_pairs(c, c.cnt->n_colours);
         __syncthreads();
     }
-    uint32_t round = 0;
-    for (; round < (uint32_t)MAX_ROUNDS; ++round) {
-        stage_colour_bid(c, round, tid, nth);
-        __syncthreads();
-        stage_colour_take(c, round, tid, nth);
-        __syncthreads();
-        if (c.cnt->round_flags[round] == 0u) break;
-    }
-    if (round == (uint32_t)MAX_ROUNDS && tid == 0) atomicOr(&c.cnt->overflow, 8u);
-    stage_colour_record(c, tid, nth);
-    __syncthreads();
-    LAP(2);
-    batch_bucket(c, smem9);
-    LAP(3);
 
     const uint32_t ncol = c.cnt->n_colours;
     // solve order: big colours ascending, then small colours ascending (SFP_TAIL_ITEMS)
@@ -305,22 +327,6 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
     const unsigned long long big = big_colour_mask(c, ncol);
     const unsigned long long small = all & ~big & ~(1ull << SFP_SERIAL_COLOUR);
     const bool serial = ncol > SFP_SERIAL_COLOUR;
-    if (serial) serial_sort_pairs(c, ncol);
-    __syncthreads();
-    auto next_bit = [](unsigned long long m, int after) {
-        unsigned long long r = (after >= 63) ? 0ull : (m & (~0ull << (after + 1)));
-        return r ? (__ffsll((long long)r) - 1) : 64;
-    };
-    const float h = dt / (float)substeps, inv_h = 1.0f / h, inv_h2 = inv_h * inv_h;
-    // colour order as a list, and a per-thread shared-memory slot into which the contact record
-    // of this thread's first item of the NEXT colour is copied asynchronously (cp.async, no
-    // registers held across the barrier): after the barrier only shared-memory reads remain
-    // before the solve, instead of two dependent L2 / HBM round trips.
-    __shared__ uint8_t s_order[SFP_MAX_COLOURS];
-    __shared__ uint32_t s_nord;
-    __shared__ float4 s_rec[4][BTPB];
-    __shared__ float4 s_lam[BTPB];
-    __shared__ uint2 s_pair[BTPB];
     if (tid == 0) {
         uint32_t k = 0;
         for (int pass = 0; pass < 2; ++pass) {
@@ -359,7 +365,7 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
         r.q1.x = q1.x, r.q1.y = q1.y, r.q1.z = q1.z, r.q1.w = q1.w;
         return r;
     };
-    for (uint32_t s = 0; s < substeps; ++s) {
+    for (uint32_t s = (sa ? sa : 1u); s < se; ++s) {
         stage_integrate(c, h, tid, nth);
         __syncthreads();
         LAP(4);
@@ -409,16 +415,128 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
         }
         LAP(8);
     }
-    if (SMEM) {
+    if (SMEM && se > 1u) {
         for (uint32_t i = tid; i < n; i += nth) {
             g_pose[i] = c.pose[i];
             g_vel[i] = c.vel[i];
         }
     }
     LAP(0);
-    if (tid == 0)
-        for (int k = 0; k < 10; ++k) c.cnt->stage_cycles[k] = cyc[k];
+    if (tid == 0) {
+        if (sa == 0u)
+            for (int k = 0; k < 10; ++k) c.cnt->stage_cycles[k] = cyc[k];
+        else
+            for (int k = 0; k < 10; ++k) c.cnt->stage_cycles[k] += cyc[k];
+    }
 #undef LAP
+}
+
+// Scheduling of a launch's worlds over its CTAs.  A world's frame is a chain of substeps + 1
+// stages: stage 0 finds and colours the pairs, stage s >= 1 is substep s.
+//   queue == null: CTA i runs world i, start to end (as many CTAs as worlds).
+//   otherwise the launch has as many CTAs as are resident at once, and they share two lists:
+//   (a) the first n_whole worlds are handed out whole, one at a time, to whichever CTA is free
+//       (an atomic counter): the world's state stays in that CTA's shared memory for the frame;
+//   (b) the other worlds — between one and two per CTA — are handed out ONE STAGE at a time,
+//       first come first served, through a ring of world indices in global memory: after a
+//       stage the CTA writes the state back, notes the world's progress and appends the world
+//       to the ring; whoever takes it next reloads the state.  These worlds therefore advance
+//       together and end together, whatever the speed of the SMs that serve them, so the
+//       launch has no ragged last wave: CTAs that leave (a) early simply take more of (b).
+// A CTA only ever waits for a ring slot that a RUNNING CTA is about to fill (see the comments
+// at the two waits), so the scheme needs the CTAs that hold tasks to be running — which they
+// are — and not the whole grid to be resident.
+struct BatchQueue {
+    uint32_t next_whole;  // (a): next world to hand out
+    uint32_t head;        // (b): tasks handed out
+    uint32_t tail;        // (b): ring slots filled
+    uint32_t exits;       // CTAs that found nothing left; the last one zeroes the queue
+};
+
+template <bool SMEM, bool FULL = false>
+__global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
+    k_batch_frame(BatchCtx b, float dt, uint32_t substeps, float rest_threshold) {
+    // thread 0 finds the next task; nothing but the loop itself is live across the stages
+    __shared__ uint32_t s_seg[4];  // world, first stage, end stage (0: no task left), staged?
+    for (uint32_t it = 0;; ++it) {
+        if (threadIdx.x == 0) {
+            const uint32_t per = substeps + 1u;
+            uint32_t w = 0u, sa = 0u, se = 0u, staged = 0u;
+            BatchQueue* q = b.queue;
+            if (!q) {
+                if (it == 0u) w = blockIdx.x, se = per;
+            } else {
+                const uint32_t n_staged = b.n_launch - b.n_whole;
+                uint32_t i = (it == 0u || s_seg[3] == 0u) ? atomicAdd(&q->next_whole, 1u) : b.n_whole;
+                if (i < b.n_whole) {
+                    w = i, se = per;
+                } else {
+                    const uint32_t t = atomicAdd(&q->head, 1u);
+                    staged = 1u;
+                    if (t < n_staged) {
+                        w = b.n_whole + t, se = 1u;  // the world's stage 0
+                    } else if (t < n_staged * per) {
+                        // Task t continues the world in ring slot t - n_staged.  That slot is
+                        // filled by the (t - n_staged + 1)-th stage that ends with stages to
+                        // go; tasks 0..t-1 are all handed out, and at most n_staged - 1 of them
+                        // can be the last stage of their world while task t exists, so that
+                        // stage is among them: it has ended or is running.
+                        volatile uint32_t* slot = b.ring + (t - n_staged) % n_staged;
+                        uint32_t v;
+                        while ((v = *slot) == 0u) __nanosleep(100);
+                        *slot = 0u;
+                        __threadfence();
+                        w = v - 1u;
+                        sa = *(volatile uint32_t*)(b.progress + b.world_base + w);
+                        se = sa + 1u;
+                    }
+                }
+                if (se == 0u && atomicAdd(&q->exits, 1u) == gridDim.x - 1u) {
+                    // every CTA has taken its last look at the queue: leave it ready for the
+                    // next launch (the ring and the progress notes are already back to zero)
+                    q->next_whole = 0u, q->head = 0u, q->tail = 0u, q->exits = 0u;
+                }
+            }
+            s_seg[0] = w + b.world_base;
+            s_seg[1] = sa;
+            s_seg[2] = se;
+            s_seg[3] = staged;
+        }
+        __syncthreads();
+        const uint32_t w = s_seg[0], sa = s_seg[1], se = s_seg[2];
+#ifdef SFP_CUT_PROBE
+        if (threadIdx.x == 0 && (it == 0u || se == 0u)) {
+            unsigned long long t;
+            unsigned smid;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            reinterpret_cast<unsigned long long*>(b.scratch)[2 * blockIdx.x + (se == 0u ? 1 : 0)] = t;
+            reinterpret_cast<uint32_t*>(b.scratch)[4 * 8192 + blockIdx.x] = smid;
+        }
+#endif
+        if (se == 0u) break;
+        batch_world_stages<SMEM, FULL>(b, w, sa, se, dt, substeps, rest_threshold);
+        // shared memory is reused by the next task; a world that goes back to the ring is
+        // published after everything this CTA wrote for it
+        __syncthreads();
+        if (threadIdx.x == 0 && s_seg[3] != 0u) {
+            const uint32_t w_ = s_seg[0], se_ = s_seg[2];
+            if (se_ != substeps + 1u) {
+                const uint32_t n_staged = b.n_launch - b.n_whole;
+                *(volatile uint32_t*)(b.progress + w_) = se_;
+                __threadfence();
+                // The slot's previous occupant (one lap of the ring earlier) belongs to task
+                // `pos`, which has been handed out — pos + 1 stages have ended, so at least as
+                // many tasks were taken — and whose CTA clears the slot as soon as it reads it.
+                const uint32_t pos = atomicAdd(&b.queue->tail, 1u);
+                volatile uint32_t* slot = b.ring + pos % n_staged;
+                while (*slot != 0u) __nanosleep(100);
+                *slot = (w_ - b.world_base) + 1u;
+            } else {
+                *(volatile uint32_t*)(b.progress + w_) = 0u;  // ready for the next frame
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) k_batch_pack(const float4* __restrict__ pose,
@@ -524,6 +642,9 @@ struct SfpBatch {
     uint32_t joint_cap = 0;              // joint slots per world
     std::vector<uint32_t> n_joints;      // per world
     std::vector<void*> joint_allocs;
+    uint32_t resident[2] = {0u, 0u};     // frame-kernel CTAs resident at once (lean, full)
+    uint32_t* d_ring = nullptr;          // [n_worlds] rings of the launches (k_batch_frame)
+    BatchQueue* d_queue = nullptr;       // [4] one per concurrent launch
     std::string err;
     int32_t sticky = SFP_OK;
 };
@@ -612,6 +733,9 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     A(c.lam, np);
     A(b->ctx.counters, n_worlds);
     A(b->ctx.scratch, nb);
+    A(b->ctx.progress, n_worlds);
+    A(b->d_ring, n_worlds);
+    A(b->d_queue, 4);
     uint32_t slots = 256;
     while (slots < 2u * b->pair_cap) slots <<= 1;
     A(b->d_tab[0], (size_t)n_worlds * slots);
@@ -804,18 +928,56 @@ int32_t sfp_batch_set_joints(SfpBatch* b, const SfpJointDesc* joints, uint32_t j
 }
 
 namespace {
-// worlds [w0, w0 + nw) of the batch, one CTA each, on `st`
+// CTAs of the frame kernel that are resident at once on this batch's device
+uint32_t batch_resident_ctas(SfpBatch* b, bool full) {
+    uint32_t& cached = b->resident[full ? 1 : 0];
+    if (cached) return cached;
+    int per_sm = 0, sms = 0;
+    cudaError_t e;
+    if (b->smem_bytes)
+        e = full ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_frame<true, true>, BTPB, b->smem_bytes)
+                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_frame<true, false>, BTPB, b->smem_bytes);
+    else
+        e = full ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_frame<false, true>, BTPB, 0)
+                 : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_batch_frame<false, false>, BTPB, 0);
+    if (e != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device) != cudaSuccess ||
+        per_sm <= 0 || sms <= 0) {
+        cudaGetLastError();
+        return 0u;  // unknown: one CTA per world
+    }
+    cached = (uint32_t)per_sm * (uint32_t)sms;
+    return cached;
+}
+
+// worlds [w0, w0 + nw) of the batch on `st`, as launch number `slot` of up to `share` that run
+// side by side (each then counts on its share of the device's resident CTAs).  Up to that many
+// worlds: one CTA per world.  More: exactly that many CTAs and the two lists of k_batch_frame.
 void launch_batch_frame(SfpBatch* b, cudaStream_t st, uint32_t w0, uint32_t nw, float dt,
-                        uint32_t substeps, float rt) {
+                        uint32_t substeps, float rt, uint32_t share = 1u, uint32_t slot = 0u) {
     BatchCtx ctx = b->ctx;
     ctx.world_base = w0;
+    ctx.n_launch = nw;
+    ctx.n_whole = nw;
+    ctx.queue = nullptr;
+    ctx.ring = b->d_ring + w0;
     const bool full = b->has_polygons || b->joint_cap != 0u;
+    uint32_t grid = nw;
+    const uint32_t resident = batch_resident_ctas(b, full);
+    if (resident && slot < 4u && !(b->p.flags & SFP_FLAG_BATCH_WHOLE_WORLDS)) {
+        uint32_t mine = resident;
+        if (share > 1u && nw < 2u * resident) mine = std::max(1u, resident / share);
+        if (nw > mine) {
+            grid = mine;
+            ctx.queue = b->d_queue + slot;
+            ctx.n_whole = nw - std::min(nw, grid + nw % grid);
+        }
+    }
     if (b->smem_bytes) {
-        if (full) k_batch_frame<true, true><<<nw, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
-        else k_batch_frame<true, false><<<nw, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
+        if (full) k_batch_frame<true, true><<<grid, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
+        else k_batch_frame<true, false><<<grid, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
     } else {
-        if (full) k_batch_frame<false, true><<<nw, BTPB, 0, st>>>(ctx, dt, substeps, rt);
-        else k_batch_frame<false, false><<<nw, BTPB, 0, st>>>(ctx, dt, substeps, rt);
+        if (full) k_batch_frame<false, true><<<grid, BTPB, 0, st>>>(ctx, dt, substeps, rt);
+        else k_batch_frame<false, false><<<grid, BTPB, 0, st>>>(ctx, dt, substeps, rt);
     }
 }
 }  // namespace
@@ -841,6 +1003,14 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     b->body_substeps += (uint64_t)b->n_worlds * b->bpw * substeps;
     return SFP_OK;
 }
+
+#ifdef SFP_CUT_PROBE
+__attribute__((visibility("default"))) int32_t sfp_debug_batch_scratch(SfpBatch* b, void* out, size_t bytes) {
+    cudaSetDevice(b->device);
+    cudaStreamSynchronize(b->stream);
+    return cudaMemcpy(out, b->ctx.scratch, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 int32_t sfp_batch_sync(SfpBatch* b) {
     if (!b) return SFP_E_INVALID;
@@ -912,7 +1082,7 @@ int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBodyState* o
                                 cudaMemcpyHostToDevice, st));
             k_batch_unpack<<<blocks, 256, 0, st>>>(b->d_state + o, b->ctx.base.minv + o,
                                                    b->ctx.base.pose + o, b->ctx.base.vel + o, m);
-            launch_batch_frame(b, st, w0, nw, dt, substeps, 2.0f * g * h);
+            launch_batch_frame(b, st, w0, nw, dt, substeps, 2.0f * g * h, slices, k);
             k_batch_pack<<<blocks, 256, 0, st>>>(b->ctx.base.pose + o, b->ctx.base.vel + o,
                                                  b->d_state + o, m);
             BCU(cudaGetLastError());
@@ -1214,6 +1384,11 @@ int32_t sfp_step_small_noalloc(const SfpParams* params, const SfpBodyDesc* bodie
     ctx.bpw = n;
     ctx.pair_cap = pair_cap;
     ctx.n_worlds = 1;
+    ctx.n_launch = 1;  // one CTA runs the whole world
+    ctx.n_whole = 1;
+    ctx.queue = nullptr;
+    ctx.ring = nullptr;
+    ctx.progress = nullptr;
     ctx.counters = reinterpret_cast<Counters*>(base + NA_OFF_CNT);
     ctx.scratch = reinterpret_cast<uint32_t*>(base + NA_OFF_CNTOFF);
     ctx.tab_slots = NA_TAB_SLOTS;

@@ -62,6 +62,47 @@ def test_batch_many_worlds_spot_check(gpu_api, ref_api):
         same(out[w], r.download_bodies())
 
 
+@pytest.mark.parametrize("nw,bpw,substeps", [(700, 64, 8), (1000, 48, 3), (445, 64, 1), (2100, 32, 5)])
+def test_batch_queue_schedule_equals_one_cta_per_world(gpu_api, nw, bpw, substeps):
+    """More worlds than resident CTAs: the frame kernel's CTAs take worlds from a queue, the last
+    one to two worlds per CTA one stage at a time with the state handed from CTA to CTA through
+    global memory.  EVERY world must end in the bits it gets with one CTA per world
+    (SFP_FLAG_BATCH_WHOLE_WORLDS), state and statistics, after frames enough for contacts, warm
+    colourings and recolourings."""
+    bodies = scenes.worlds(nw, bpw)
+    outs, stats = [], []
+    for flags in (0, sf.FLAG_BATCH_WHOLE_WORLDS):
+        batch = sf.Batch(gpu_api, nw, bpw, flags=flags)
+        batch.upload(bodies)
+        for _ in range(24):
+            batch.step(substeps=substeps)
+        outs.append(batch.download())
+        stats.append(batch.stats())
+        del batch
+    same(outs[0].reshape(-1), outs[1].reshape(-1))
+    for k in ("n_pairs", "n_contacts", "n_manifolds", "n_colours", "colour_rounds", "overflow"):
+        assert np.array_equal(stats[0][k], stats[1][k]), k
+    assert stats[0]["n_contacts"].sum() > 0
+
+
+def test_batch_queue_sliced_host_path_matches_whole_worlds(gpu_api):
+    """the sliced sfp_batch_step_host path with slices larger than their share of the GPU"""
+    nw, bpw, frames = 1200, 32, 12
+    bodies = scenes.worlds(nw, bpw)
+    outs = []
+    for flags in (0, sf.FLAG_BATCH_WHOLE_WORLDS):
+        batch = sf.Batch(gpu_api, nw, bpw, flags=flags)
+        batch.upload(bodies)
+        bufs = [gpu_api.alloc_host_states(nw * bpw), gpu_api.alloc_host_states(nw * bpw)]
+        bufs[0][:] = batch.download().reshape(-1)
+        for f in range(frames):
+            batch.step_host(bufs[f & 1], out=bufs[(f + 1) & 1])
+        outs.append(np.array(bufs[frames & 1]))
+        del batch
+    same(outs[0], outs[1])
+    assert np.array_equal(outs[0]["angle"].view(np.uint32), outs[1]["angle"].view(np.uint32))
+
+
 def test_batch_partition_is_world_index_independent(gpu_api):
     """a rank that owns worlds [k, k+m) computes what a rank owning [0, n) computes for them
     (this is the multi-GPU sharding: no data-path exchange, so no collective to test)"""
@@ -213,6 +254,26 @@ def test_batch_joints_match_oracle(gpu_api, ref_api):
     out = batch.download()
     for w in range(nw):
         same(out[w], refs[w].download_bodies())
+
+
+def test_batch_queue_schedule_with_joints(gpu_api):
+    """the joint-and-polygon variant of the frame kernel (fewer resident CTAs) through the queue"""
+    b4, j4, c4 = rope_worlds(4)
+    rep = 90
+    bodies, joints, counts = np.tile(b4, (rep, 1)), np.tile(j4, (rep, 1)), np.tile(c4, rep)
+    nw = 4 * rep
+    outs = []
+    for flags in (0, sf.FLAG_BATCH_WHOLE_WORLDS):
+        batch = sf.Batch(gpu_api, nw, bodies.shape[1], flags=flags)
+        batch.upload(bodies)
+        batch.set_joints(joints, counts)
+        for _ in range(30):
+            batch.step()
+        outs.append(batch.download())
+        del batch
+    same(outs[0].reshape(-1), outs[1].reshape(-1))
+    for w in range(4, nw):  # the tiled worlds are copies of the first four
+        same(outs[0][w], outs[0][w % 4])
 
 
 def test_batch_set_joints_rejects_bad_arguments(gpu_api):
