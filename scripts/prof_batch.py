@@ -1,12 +1,18 @@
-"""Small driver for profiling the batched kernel: 1024 worlds x 512 bodies, settle, 3 more frames."""
+"""Small driver for profiling the batched frame kernel: settle, then 3 more frames.
+  python scripts/prof_batch.py [n_worlds] [settle_frames] [flags]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
 import starframe_b200 as sf
 from starframe_b200 import scenes
-nw = 1024
-b = sf.Batch(sf.product_api(), nw, 512)
-b.upload(scenes.worlds(64, 512).repeat(nw // 64, axis=0))
-for _ in range(243):
-    b.step()
+nw = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
+settle = int(sys.argv[2]) if len(sys.argv) > 2 else 120
+flags = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+bodies = scenes.worlds(min(nw, 64), 512)
+bodies = np.concatenate([bodies] * ((nw + len(bodies) - 1) // len(bodies)), axis=0)[:nw]
+b = sf.Batch(sf.product_api(), nw, 512, flags=flags)
+b.upload(bodies)
+for _ in range(settle + 3): b.step()
 b.sync()
-print("frame ms", b.last_step_ms())
+st = b.stats()
+print("worlds", nw, "frame ms", b.last_step_ms(), "pairs/world", st["n_pairs"].mean(), "colours", st["n_colours"].mean())

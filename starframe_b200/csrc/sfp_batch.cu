@@ -949,11 +949,14 @@ uint32_t batch_resident_ctas(SfpBatch* b, bool full) {
     return cached;
 }
 
-// worlds [w0, w0 + nw) of the batch on `st`, as launch number `slot` of up to `share` that run
-// side by side (each then counts on its share of the device's resident CTAs).  Up to that many
-// worlds: one CTA per world.  More: exactly that many CTAs and the two lists of k_batch_frame.
+// worlds [w0, w0 + nw) of the batch on `st`, as launch number `slot` of those that may run side by
+// side.  Up to as many worlds as CTAs are resident: one CTA per world.  More: exactly that many
+// CTAs and the two lists of k_batch_frame.  `closing`: this launch is the last of a pipeline of
+// slices and starts while earlier slices still hold most of the SMs — then ALL its worlds go by
+// the stage, so that the CTAs that get an SM late still find work to share and the whole
+// pipeline, not just this slice, ends evenly.
 void launch_batch_frame(SfpBatch* b, cudaStream_t st, uint32_t w0, uint32_t nw, float dt,
-                        uint32_t substeps, float rt, uint32_t share = 1u, uint32_t slot = 0u) {
+                        uint32_t substeps, float rt, uint32_t slot = 0u, bool closing = false) {
     BatchCtx ctx = b->ctx;
     ctx.world_base = w0;
     ctx.n_launch = nw;
@@ -964,12 +967,15 @@ void launch_batch_frame(SfpBatch* b, cudaStream_t st, uint32_t w0, uint32_t nw, 
     uint32_t grid = nw;
     const uint32_t resident = batch_resident_ctas(b, full);
     if (resident && slot < 4u && !(b->p.flags & SFP_FLAG_BATCH_WHOLE_WORLDS)) {
-        uint32_t mine = resident;
-        if (share > 1u && nw < 2u * resident) mine = std::max(1u, resident / share);
-        if (nw > mine) {
-            grid = mine;
+        if (nw > resident) {
+            grid = resident;
             ctx.queue = b->d_queue + slot;
             ctx.n_whole = nw - std::min(nw, grid + nw % grid);
+        }
+        if (closing && nw <= 2u * resident) {
+            grid = std::min(nw, resident);
+            ctx.queue = b->d_queue + slot;
+            ctx.n_whole = 0u;
         }
     }
     if (b->smem_bytes) {
@@ -1070,25 +1076,27 @@ int32_t sfp_batch_step_host(SfpBatch* b, const SfpBodyState* in, SfpBodyState* o
         b->colour_age += 1;
         BCU(cudaEventRecord(b->ev0, b->stream));
         for (int k = 0; k < 3; ++k) BCU(cudaStreamWaitEvent(b->aux[k], b->ev0, 0));
-        const uint32_t slices = 4, per = (b->n_worlds + slices - 1u) / slices;
+        // four streams; eight slices once a slice is still a few hundred worlds (what stays
+        // exposed is the first slice's upload and the last one's download)
+        const uint32_t slices = b->n_worlds >= 2048u ? 8u : 4u, per = (b->n_worlds + slices - 1u) / slices;
         for (uint32_t k = 0; k < slices; ++k) {
             const uint32_t w0 = k * per;
             if (w0 >= b->n_worlds) break;
             const uint32_t nw = std::min(per, b->n_worlds - w0);
             const size_t o = (size_t)w0 * b->bpw, m = (size_t)nw * b->bpw;
-            cudaStream_t st = (k == 0) ? b->stream : b->aux[(k - 1u) % 3u];
+            cudaStream_t st = (k % 4u == 0u) ? b->stream : b->aux[k % 4u - 1u];
             const unsigned blocks = (unsigned)std::min<size_t>((m + 255) / 256, 148 * 4);
             BCU(cudaMemcpyAsync(b->d_state + o, in + o, sizeof(SfpBodyState) * m,
                                 cudaMemcpyHostToDevice, st));
             k_batch_unpack<<<blocks, 256, 0, st>>>(b->d_state + o, b->ctx.base.minv + o,
                                                    b->ctx.base.pose + o, b->ctx.base.vel + o, m);
-            launch_batch_frame(b, st, w0, nw, dt, substeps, 2.0f * g * h, slices, k);
+            launch_batch_frame(b, st, w0, nw, dt, substeps, 2.0f * g * h, k % 4u, w0 + nw == b->n_worlds);
             k_batch_pack<<<blocks, 256, 0, st>>>(b->ctx.base.pose + o, b->ctx.base.vel + o,
                                                  b->d_state + o, m);
             BCU(cudaGetLastError());
             BCU(cudaMemcpyAsync(out + o, b->d_state + o, sizeof(SfpBodyState) * m,
                                 cudaMemcpyDeviceToHost, st));
-            if (k > 0) BCU(cudaEventRecord(b->aux_done[(k - 1u) % 3u], st));
+            if (k % 4u != 0u) BCU(cudaEventRecord(b->aux_done[k % 4u - 1u], st));
         }
         for (int k = 0; k < 3; ++k) BCU(cudaStreamWaitEvent(b->stream, b->aux_done[k], 0));
         BCU(cudaEventRecord(b->ev1, b->stream));

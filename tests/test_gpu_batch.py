@@ -85,9 +85,11 @@ def test_batch_queue_schedule_equals_one_cta_per_world(gpu_api, nw, bpw, substep
     assert stats[0]["n_contacts"].sum() > 0
 
 
-def test_batch_queue_sliced_host_path_matches_whole_worlds(gpu_api):
-    """the sliced sfp_batch_step_host path with slices larger than their share of the GPU"""
-    nw, bpw, frames = 1200, 32, 12
+@pytest.mark.parametrize("nw", [1200, 2100])
+def test_batch_queue_sliced_host_path_matches_whole_worlds(gpu_api, nw):
+    """the sliced sfp_batch_step_host path (four slices, eight from 2048 worlds; the last slice
+    goes through the queue by the stage)"""
+    bpw, frames = 32, 12
     bodies = scenes.worlds(nw, bpw)
     outs = []
     for flags in (0, sf.FLAG_BATCH_WHOLE_WORLDS):
