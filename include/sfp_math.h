@@ -245,15 +245,43 @@ SFP_HD void state_unpack(StateRec r, f2 minv, f4* pose, f4* vel) {
  * by vel_expand*dt*v only on the side the body is moving towards.  (A symmetric speed-based
  * expansion makes every body of a free-falling pile a candidate partner of dozens of
  * neighbours, which costs pairs and, worse, constraint colours.) */
-SFP_HD f4 body_aabb(f4 pose, f4 vel, f4 shape, float margin, float vel_expand, float dt) {
+SFP_HD f4 body_aabb(f4 pose, f4 vel, f4 shape, float margin, float vel_expand, float dt,
+                    const f4* table = nullptr) {
+    float k = vel_expand * dt;
+    float sx = k * vel.x, sy = k * vel.y;
+    f4 r;
+    if (table != nullptr && (f2u(shape.w) & 3u) == 3u) {
+        /* general polygon with its vertex table at hand (sfp_math.h "shape.w bits"): the box of
+         * the rotated vertices.  Without the table — callers that only need SOME bound — the
+         * polygon falls through to the box of its bounding circle below. */
+        const f4* rec = table + (size_t)(f2u(shape.w) >> 8) * 8u;
+        const int count = (int)((f2u(shape.w) >> 2) & 15u);
+        float lox = 3.0e38f, loy = 3.0e38f, hix = -3.0e38f, hiy = -3.0e38f;
+        for (int j = 0; j < 4; ++j) {
+            f4 vv = rec[j];
+            if (2 * j < count) {
+                float ox = pose.z * vv.x - pose.w * vv.y, oy = pose.w * vv.x + pose.z * vv.y;
+                lox = fminf(lox, ox), hix = fmaxf(hix, ox);
+                loy = fminf(loy, oy), hiy = fmaxf(hiy, oy);
+            }
+            if (2 * j + 1 < count) {
+                float ox = pose.z * vv.z - pose.w * vv.w, oy = pose.w * vv.z + pose.z * vv.w;
+                lox = fminf(lox, ox), hix = fmaxf(hix, ox);
+                loy = fminf(loy, oy), hiy = fmaxf(hiy, oy);
+            }
+        }
+        float e = shape.z + margin + k * (fabsf(vel.z) * shape.x); /* shape.x: the core's radius */
+        r.x = (pose.x + lox - e) + fminf(sx, 0.0f);
+        r.y = (pose.y + loy - e) + fminf(sy, 0.0f);
+        r.z = (pose.x + hix + e) + fmaxf(sx, 0.0f);
+        r.w = (pose.y + hiy + e) + fmaxf(sy, 0.0f);
+        return r;
+    }
     float ac = fabsf(pose.z), as = fabsf(pose.w);
     float ex = ac * shape.x + as * shape.y + shape.z;
     float ey = as * shape.x + ac * shape.y + shape.z;
     float bound = sqrtf(shape.x * shape.x + shape.y * shape.y); /* core only: r is spin-invariant */
-    float k = vel_expand * dt;
     float e = margin + k * (fabsf(vel.z) * bound);
-    float sx = k * vel.x, sy = k * vel.y;
-    f4 r;
     r.x = (pose.x - ex - e) + fminf(sx, 0.0f);
     r.y = (pose.y - ey - e) + fminf(sy, 0.0f);
     r.z = (pose.x + ex + e) + fmaxf(sx, 0.0f);
@@ -1380,10 +1408,10 @@ SFP_HD bool ray_collider_near(v2 o, v2 d, float tmax, f4 pose, f4 shape, const f
 }
 
 /* tight AABB of a collider at its current pose (no margin, no sweep) */
-SFP_HD f4 tight_aabb(f4 pose, f4 shape) {
+SFP_HD f4 tight_aabb(f4 pose, f4 shape, const f4* table = nullptr) {
     f4 zero;
     zero.x = zero.y = zero.z = zero.w = 0.0f;
-    return body_aabb(pose, zero, shape, 0.0f, 0.0f, 0.0f);
+    return body_aabb(pose, zero, shape, 0.0f, 0.0f, 0.0f, table);
 }
 
 /* ------------------------------------------------------------------------------------- */

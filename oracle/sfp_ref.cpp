@@ -178,7 +178,8 @@ void parallel_for(SfpWorld& w, int T, size_t n, const F& f) {
 void compute_aabbs(const SfpWorld& w, float dt, std::vector<f4>& aabb) {
     aabb.resize(w.n);
     for (uint32_t i = 0; i < w.n; ++i)
-        aabb[i] = body_aabb(w.pose[i], w.vel[i], w.shape[i], w.p.aabb_margin, w.p.vel_expand, dt);
+        aabb[i] = body_aabb(w.pose[i], w.vel[i], w.shape[i], w.p.aabb_margin, w.p.vel_expand, dt,
+                            w.polys.recs.empty() ? nullptr : w.polys.recs.data());
 }
 
 /* A2: every body is entered into each cell its expanded AABB touches; inside a cell every two
@@ -786,7 +787,9 @@ int32_t sfp_ref_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, floa
     uint32_t cnt = 0;
     for (uint32_t i = 0; i < w->n; ++i) {
         if (((f2u(w->mat[i].w) & 0xffffu) & mask) == 0u) continue;
-        if (!aabb_overlap(tight_aabb(w->pose[i], w->shape[i]), box)) continue;
+        if (!aabb_overlap(tight_aabb(w->pose[i], w->shape[i],
+                                     w->polys.recs.empty() ? nullptr : w->polys.recs.data()), box))
+            continue;
         if (cnt < cap) out[cnt] = i;
         ++cnt;
     }

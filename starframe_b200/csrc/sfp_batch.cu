@@ -108,7 +108,7 @@ __device__ void batch_broadphase(const Ctx& c, uint32_t* cnt_off, float dt, uint
     const uint32_t tid = threadIdx.x, nth = blockDim.x, n = c.n;
     for (uint32_t i = tid; i < n; i += nth) {
         f4 bb = sfp::body_aabb(ld4(c.pose, i), ld4(c.vel, i), ld4(c.shape, i), c.aabb_margin,
-                               c.vel_expand, dt);
+                               c.vel_expand, dt, reinterpret_cast<const sfp::f4*>(c.polytab));
         int x0, y0, x1, y1;
         if (!sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1)) atomicOr(&c.cnt->overflow, 16u);
         st4(c.aabb, i, bb);

@@ -159,7 +159,8 @@ __device__ __forceinline__ void stage_aabb_count(const Ctx& c, float dt, uint32_
     for (uint32_t i = tid; i < c.n; i += nth) {
         f4 pose = ld4(c.pose, i), vel = ld4(c.vel, i), shape = ld4(c.shape, i);
         f2 mi = ld2(c.minv, i);
-        f4 bb = sfp::body_aabb(pose, vel, shape, c.aabb_margin, c.vel_expand, dt);
+        f4 bb = sfp::body_aabb(pose, vel, shape, c.aabb_margin, c.vel_expand, dt,
+                               reinterpret_cast<const sfp::f4*>(c.polytab));
         int x0, y0, x1, y1;
         if (!sfp::cell_range(bb, c.inv_cell, &x0, &y0, &x1, &y1)) atomicOr(&c.cnt->overflow, 16u);
         st4(c.aabb, i, bb);

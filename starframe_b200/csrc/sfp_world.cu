@@ -289,7 +289,8 @@ __global__ void __launch_bounds__(TPB) k_box_flags(Ctx c, float4 box, uint32_t m
     for (uint32_t e = gtid(); e < c.n; e += gnth()) {  // e: the caller's index
         const uint32_t i = c.inv[e];
         bool in = (((sfp::f2u(c.mat[i].w) & 0xffffu) & mask) != 0u) &&
-                  sfp::aabb_overlap(sfp::tight_aabb(ld4(c.pose, i), ld4(c.shape, i)), bx);
+                  sfp::aabb_overlap(sfp::tight_aabb(ld4(c.pose, i), ld4(c.shape, i),
+                                                    reinterpret_cast<const sfp::f4*>(c.polytab)), bx);
         flags[e] = in ? 1u : 0u;
     }
 }
