@@ -220,6 +220,8 @@ extern "C" {
     pub fn sfp_ray_cast(w: *mut SfpWorld, rays: *const SfpRay, m: u32, hits: *mut SfpRayHit) -> i32;
     pub fn sfp_query_aabb(w: *mut SfpWorld, lo_x: f32, lo_y: f32, hi_x: f32, hi_y: f32, mask: u32,
                           out: *mut u32, cap: u32, n_out: *mut u32) -> i32;
+    pub fn sfp_query_shape(w: *mut SfpWorld, probe: *const SfpBodyDesc, mask: u32, out: *mut u32,
+                           cap: u32, n_out: *mut u32) -> i32;
     pub fn sfp_update_bodies(w: *mut SfpWorld, idx: *const u32, states: *const SfpBodyState,
                              m: u32) -> i32;
     pub fn sfp_step_host(w: *mut SfpWorld, input: *const SfpBodyState, out: *mut SfpBodyState,

@@ -275,10 +275,16 @@ SFP_API int32_t sfp_get_contact_events(SfpWorld* w, SfpContactEvent* out, uint32
  * unavailable).  Both work on the CURRENT body state.
  * sfp_ray_cast: m rays at once, one device thread per ray walking the spatial hash (rebuilt for
  * the current poses); closest hit per ray, ties to the lower body index.
- * sfp_query_aabb: indices (ascending) of the bodies whose tight AABB overlaps the box. */
+ * sfp_query_aabb: indices (ascending) of the bodies whose tight AABB overlaps the box.
+ * sfp_query_shape: indices (ascending) of the bodies whose COLLIDER overlaps the probe collider,
+ * by the narrowphase itself (zero margin: a point of negative separation).  The probe is given
+ * like a body — shape, x, y, angle, hx, hy, radius; a polygon probe indexes the world's polygon
+ * table; every other field is ignored.  A circle of radius 0 is a point query (mouse picking). */
 SFP_API int32_t sfp_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits);
 SFP_API int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y,
                                uint32_t mask, uint32_t* out, uint32_t cap, uint32_t* n_out);
+SFP_API int32_t sfp_query_shape(SfpWorld* w, const SfpBodyDesc* probe, uint32_t mask, uint32_t* out,
+                                uint32_t cap, uint32_t* n_out);
 
 /* Replaces: game code moving individual bodies between steps (teleports, kinematic control).
  * Overwrites pose and velocity of the m bodies idx[0..m) with states[0..m); everything else
@@ -421,6 +427,8 @@ SFP_API int32_t sfp_ref_get_contact_events(SfpWorld* w, SfpContactEvent* out, ui
 SFP_API int32_t sfp_ref_ray_cast(SfpWorld* w, const SfpRay* rays, uint32_t m, SfpRayHit* hits);
 SFP_API int32_t sfp_ref_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi_y,
                                    uint32_t mask, uint32_t* out, uint32_t cap, uint32_t* n_out);
+SFP_API int32_t sfp_ref_query_shape(SfpWorld* w, const SfpBodyDesc* probe, uint32_t mask,
+                                    uint32_t* out, uint32_t cap, uint32_t* n_out);
 SFP_API int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
                                       uint32_t m);
 SFP_API const char* sfp_ref_last_error(SfpWorld* w);

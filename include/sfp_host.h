@@ -198,6 +198,21 @@ inline void body_from_desc(const SfpBodyDesc& d, f4* pose, f4* vel, f2* minv, f4
     mat->w = u2f((uint32_t)d.category | ((uint32_t)d.mask << 16));
 }
 
+/* probe collider of sfp_query_shape: pose and shape of `d` as a body would get them; only the
+ * geometry fields are looked at (the probe is treated as static: no mass, no material) */
+inline bool probe_from_desc(const SfpBodyDesc& d, const PolyTable* polys, f4* pose, f4* shape) {
+    SfpBodyDesc q = d;
+    q.flags = SFP_BODY_STATIC;
+    q.vx = q.vy = q.omega = 0.0f;
+    q.density = 1.0f;
+    q.mu_s = q.mu_d = q.restitution = 0.0f;
+    if (!desc_valid(q, polys)) return false;
+    f4 vel, mat;
+    f2 minv;
+    body_from_desc(q, pose, &vel, &minv, shape, &mat, polys);
+    return true;
+}
+
 /* Does the collider, as uploaded, fit the broadphase grid?  A body whose box (tight box +
  * aabb_margin) covers more than SFP_MAX_CELLS_PER_BODY cells, or 4096 or more cells along one
  * axis, would be left out of the broadphase (cell_range() refuses it: it would produce no pairs

@@ -796,6 +796,16 @@ SFP_HD Manifold collide(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, float marg
     return collide_cores<4>(xa, qa, shape_a, xb, qb, shape_b, margin, table);
 }
 
+/* Do two colliders overlap?  The narrowphase with a zero margin: true when it reports a point of
+ * negative separation (what the solver would push apart).  A circle of radius 0 is a point. */
+SFP_HD bool colliders_overlap(f4 pose_a, f4 shape_a, f4 pose_b, f4 shape_b, const f4* table) {
+    float ba = sqrtf(shape_a.x * shape_a.x + shape_a.y * shape_a.y) + shape_a.z;
+    float bb = sqrtf(shape_b.x * shape_b.x + shape_b.y * shape_b.y) + shape_b.z;
+    float dx = pose_b.x - pose_a.x, dy = pose_b.y - pose_a.y, reach = ba + bb;
+    if (dx * dx + dy * dy >= reach * reach) return false;
+    return collide<true>(pose_a, shape_a, pose_b, shape_b, 0.0f, table).count > 0;
+}
+
 /* ------------------------------------------------------------------------------------- */
 /* Contact record (per candidate pair; 5 x 16 B)                                         */
 /* ------------------------------------------------------------------------------------- */

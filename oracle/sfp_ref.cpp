@@ -797,6 +797,23 @@ int32_t sfp_ref_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, floa
     return SFP_OK;
 }
 
+int32_t sfp_ref_query_shape(SfpWorld* w, const SfpBodyDesc* probe, uint32_t mask, uint32_t* out,
+                            uint32_t cap, uint32_t* n_out) {
+    if (!w || !probe || !n_out || (cap && !out)) return SFP_E_INVALID;
+    f4 pp, ps;
+    if (!probe_from_desc(*probe, &w->polys, &pp, &ps)) return SFP_E_INVALID;
+    const f4* table = w->polys.recs.empty() ? nullptr : w->polys.recs.data();
+    uint32_t cnt = 0;
+    for (uint32_t i = 0; i < w->n; ++i) {
+        if (((f2u(w->mat[i].w) & 0xffffu) & mask) == 0u) continue;
+        if (!colliders_overlap(w->pose[i], w->shape[i], pp, ps, table)) continue;
+        if (cnt < cap) out[cnt] = i;
+        ++cnt;
+    }
+    *n_out = cnt;
+    return SFP_OK;
+}
+
 int32_t sfp_ref_update_bodies(SfpWorld* w, const uint32_t* idx, const SfpBodyState* states,
                               uint32_t m) {
     if (!w || (m && (!idx || !states))) return SFP_E_INVALID;

@@ -109,7 +109,7 @@ PRODUCT_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
     "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host",
+    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "query_shape", "step_host",
     "alloc_host_states", "free_host_states",
     "batch_create", "batch_destroy", "batch_upload", "batch_step", "batch_sync",
     "batch_download", "batch_step_host", "batch_set_joints", "batch_set_polygons", "batch_stats", "batch_last_error", "last_step_ms", "batch_last_step_ms",
@@ -123,8 +123,8 @@ ORACLE_SYMBOLS = [
     "default_params", "create", "destroy", "upload_bodies", "set_joints", "set_polygons", "step",
     "sync",
     "download_bodies", "get_pairs", "get_contacts", "get_colours", "get_stats", "last_error",
-    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "step_host", "last_step_ms",
-    "backend", "brute_pairs",
+    "get_contact_events", "update_bodies", "ray_cast", "query_aabb", "query_shape", "step_host",
+    "last_step_ms", "backend", "brute_pairs",
 ]
 
 
@@ -182,6 +182,7 @@ class Api:
             "update_bodies": [vp, vp, vp, u32],
             "ray_cast": [vp, vp, u32, vp],
             "query_aabb": [vp, f32, f32, f32, f32, u32, vp, u32, C.POINTER(u32)],
+            "query_shape": [vp, vp, u32, vp, u32, C.POINTER(u32)],
             "alloc_host_states": [u32, C.POINTER(vp)],
             "free_host_states": [vp],
             "get_colours": [vp, vp, u32, vp, u32],
@@ -382,6 +383,22 @@ class World:
         self._check(self.api.fn("query_aabb")(self.h, lo[0], lo[1], hi[0], hi[1], mask, _ptr(out),
                                               out.shape[0], C.byref(n)), "query_aabb")
         return out[: n.value].copy()
+
+    def query_shape(self, probe: np.ndarray, mask: int = 0xFFFF) -> np.ndarray:
+        """bodies whose collider overlaps the probe collider (one BODY_DESC record: shape, x, y,
+        angle, hx, hy, radius)"""
+        q = np.ascontiguousarray(probe, dtype=BODY_DESC_DTYPE).reshape(1)
+        n = C.c_uint32(0)
+        out = np.zeros(max(self.n, 1), dtype=np.uint32)
+        self._check(self.api.fn("query_shape")(self.h, _ptr(q), mask, _ptr(out), out.shape[0],
+                                               C.byref(n)), "query_shape")
+        return out[: n.value].copy()
+
+    def query_point(self, x: float, y: float, mask: int = 0xFFFF) -> np.ndarray:
+        """bodies whose collider contains the point: a circle probe of radius 0"""
+        q = np.zeros(1, dtype=BODY_DESC_DTYPE)
+        q["x"], q["y"] = x, y
+        return self.query_shape(q, mask)
 
     def update_bodies(self, idx: np.ndarray, states: np.ndarray):
         i = np.ascontiguousarray(idx, dtype=np.uint32)

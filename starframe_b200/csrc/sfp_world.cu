@@ -294,6 +294,19 @@ __global__ void __launch_bounds__(TPB) k_box_flags(Ctx c, float4 box, uint32_t m
         flags[e] = in ? 1u : 0u;
     }
 }
+__global__ void __launch_bounds__(TPB) k_shape_flags(Ctx c, float4 probe_pose, float4 probe_shape,
+                                                     uint32_t mask, uint32_t* __restrict__ flags) {
+    f4 pp, ps;
+    pp.x = probe_pose.x, pp.y = probe_pose.y, pp.z = probe_pose.z, pp.w = probe_pose.w;
+    ps.x = probe_shape.x, ps.y = probe_shape.y, ps.z = probe_shape.z, ps.w = probe_shape.w;
+    for (uint32_t e = gtid(); e < c.n; e += gnth()) {  // e: the caller's index
+        const uint32_t i = c.inv[e];
+        bool in = (((sfp::f2u(c.mat[i].w) & 0xffffu) & mask) != 0u) &&
+                  sfp::colliders_overlap(ld4(c.pose, i), ld4(c.shape, i), pp, ps,
+                                         reinterpret_cast<const sfp::f4*>(c.polytab));
+        flags[e] = in ? 1u : 0u;
+    }
+}
 __global__ void __launch_bounds__(TPB) k_box_write(Ctx c, const uint32_t* __restrict__ off,
                                                    uint32_t* __restrict__ out) {
     for (uint32_t i = gtid(); i < c.n; i += gnth())
@@ -1954,6 +1967,33 @@ int32_t sfp_query_aabb(SfpWorld* w, float lo_x, float lo_y, float hi_x, float hi
     cudaStream_t st = w->stream;
     const uint32_t gb = blocks_for(w, w->n);
     k_box_flags<<<gb, TPB, 0, st>>>(w->ctx, make_float4(lo_x, lo_y, hi_x, hi_y), mask, w->d_evt_flag);
+    CU(scan_exclusive(w->d_evt_flag, w->d_evt_off, &w->d_cnt->n_bodies, w->cap_bodies,
+                      w->d_scan_tiles, w->d_evt_flag + w->cap_pairs, st));
+    k_box_write<<<gb, TPB, 0, st>>>(w->ctx, w->d_evt_off, w->d_idx);
+    CU(cudaGetLastError());
+    uint32_t total = 0;
+    CU(cudaMemcpyAsync(&total, w->d_evt_flag + w->cap_pairs, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    *n_out = total;
+    const uint32_t mm = std::min(total, cap);
+    if (mm) CU(cudaMemcpy(out, w->d_idx, sizeof(uint32_t) * mm, cudaMemcpyDeviceToHost));
+    return SFP_OK;
+}
+
+int32_t sfp_query_shape(SfpWorld* w, const SfpBodyDesc* probe, uint32_t mask, uint32_t* out,
+                        uint32_t cap, uint32_t* n_out) {
+    if (!w || !probe || !n_out || (cap && !out)) return SFP_E_INVALID;
+    if (w->sticky != SFP_OK) return w->sticky;
+    *n_out = 0;
+    sfp::f4 pp, ps;
+    if (!sfp::probe_from_desc(*probe, &w->polys, &pp, &ps)) return SFP_E_INVALID;
+    if (w->n == 0) return SFP_OK;
+    CU(cudaSetDevice(w->device));
+    TRY(settle(w));
+    cudaStream_t st = w->stream;
+    const uint32_t gb = blocks_for(w, w->n);
+    k_shape_flags<<<gb, TPB, 0, st>>>(w->ctx, make_float4(pp.x, pp.y, pp.z, pp.w),
+                                      make_float4(ps.x, ps.y, ps.z, ps.w), mask, w->d_evt_flag);
     CU(scan_exclusive(w->d_evt_flag, w->d_evt_off, &w->d_cnt->n_bodies, w->cap_bodies,
                       w->d_scan_tiles, w->d_evt_flag + w->cap_pairs, st));
     k_box_write<<<gb, TPB, 0, st>>>(w->ctx, w->d_evt_off, w->d_idx);

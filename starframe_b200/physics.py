@@ -241,6 +241,24 @@ class Physics:
         self._flush()
         return self._world.query_aabb(lo, hi, mask)
 
+    def query_point(self, x: float, y: float, mask: int = 0xFFFF) -> np.ndarray:
+        """indices of the bodies whose collider contains the point (picking)"""
+        self._flush()
+        return self._world.query_point(x, y, mask)
+
+    def query_shape(self, collider: "Collider", x: float, y: float, angle: float = 0.0,
+                    mask: int = 0xFFFF) -> np.ndarray:
+        """indices of the bodies whose collider overlaps `collider` placed at (x, y, angle)"""
+        if collider.points is not None:
+            raise ValueError("query_shape: general-polygon probes go through World.query_shape "
+                             "with an index into the world's polygon table")
+        self._flush()
+        from ._ffi import BODY_DESC_DTYPE
+        q = np.zeros(1, dtype=BODY_DESC_DTYPE)
+        q["shape"], q["hx"], q["hy"], q["radius"] = collider.shape, collider.hx, collider.hy, collider.radius
+        q["x"], q["y"], q["angle"] = x, y, angle
+        return self._world.query_shape(q, mask)
+
     def set_body_states(self, idx, states: np.ndarray):
         """teleport / kinematic control of individual bodies between ticks"""
         self._flush()

@@ -165,6 +165,20 @@ def test_polygon_pile_gpu_matches_oracle(gpu_api, ref_api):
         for f in FIELDS:
             assert np.array_equal(a[f].view(np.uint32), c[f].view(np.uint32)), (block, f)
         assert g.ray_cast(rays).tobytes() == r.ray_cast(rays).tobytes()
+        # box, point and shape queries: the polygons answer by their vertices; probe 3 + k is
+        # itself a general polygon (an index into the world's table)
+        found = 0
+        for k in range(24):
+            x, y = float(rng.uniform(-8, 8)), float(rng.uniform(0.2, 8.0))
+            assert np.array_equal(g.query_aabb((x, y), (x + 1.0, y + 0.6)), r.query_aabb((x, y), (x + 1.0, y + 0.6)))
+            assert np.array_equal(g.query_point(x, y), r.query_point(x, y))
+            q = np.zeros(1, dtype=_ffi.BODY_DESC_DTYPE)
+            q["x"], q["y"], q["angle"], q["radius"] = x, y, float(rng.uniform(-3, 3)), 0.05
+            q["shape"] = SHAPE_POLYGON | ((k % len(table)) << 8)
+            a, c = g.query_shape(q), r.query_shape(q)
+            assert np.array_equal(a, c)
+            found += len(c)
+        assert found > 10
     assert g.get_contacts().tobytes() == r.get_contacts().tobytes()
     assert sg["n_contacts"] > 1500
 

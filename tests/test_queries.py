@@ -1,4 +1,4 @@
-"""Spatial queries: ray casts and AABB queries.  CPU tier: closed-form
+"""Spatial queries: ray casts, AABB, shape and point queries.  CPU tier: closed-form
 answers on the oracle.  GPU tier: the device's hash walk returns exactly what the oracle's brute
 force over all bodies returns."""
 import math
@@ -87,6 +87,77 @@ def test_query_aabb_known_answers(ref_api):
     assert w.query_aabb((-5, -5), (5, 5), mask=2).tolist() == [2]
 
 
+def probe(shape, x, y, angle=0.0, hx=0.0, hy=0.0, r=0.0):
+    q = np.zeros(1, dtype=_ffi.BODY_DESC_DTYPE)
+    q["shape"], q["x"], q["y"], q["angle"], q["hx"], q["hy"], q["radius"] = shape, x, y, angle, hx, hy, r
+    return q
+
+
+def test_query_shape_and_point_known_answers(ref_api):
+    bodies = np.concatenate([
+        body(SHAPE_CIRCLE, 0.0, 0.0, r=1.0),                                    # 0
+        body(SHAPE_RECT, 3.0, 0.0, angle=math.pi / 4, hx=1.0, hy=1.0),          # 1 diamond, tip at x = 1.586
+        body(SHAPE_CAPSULE, 0.0, 4.0, hx=1.0, r=0.25, category=2),              # 2 from (-1,4) to (1,4)
+        body(SHAPE_RECT, 10.0, 0.0, hx=1.0, hy=0.5, r=0.25),                    # 3 rounded box
+    ])
+    w = world(ref_api, bodies)
+    # points
+    assert w.query_point(0.5, 0.5).tolist() == [0]
+    assert w.query_point(0.8, 0.8).tolist() == []              # 1.131 from the centre
+    assert w.query_point(1.7, 0.0).tolist() == [1]             # inside the diamond's tip
+    assert w.query_point(1.7, 0.2).tolist() == []              # beside the tip (|dy| < x - 1.586 fails)
+    assert w.query_point(1.1, 4.15).tolist() == [2]            # in the cap: 0.18 from (1, 4)
+    assert w.query_point(1.2, 4.2).tolist() == []              # outside it: 0.283 > 0.25
+    assert w.query_point(1.1, 4.15, mask=1).tolist() == []     # the capsule is on layer 2
+    assert w.query_point(11.15, 0.65).tolist() == [3]          # in the rounded corner: 0.212 from (11, .5)
+    assert w.query_point(11.2, 0.7).tolist() == []             # outside it: 0.283
+    # shapes
+    assert w.query_shape(probe(SHAPE_CIRCLE, 1.3, 0.0, r=0.35)).tolist() == [0, 1]   # bridges the gap
+    assert w.query_shape(probe(SHAPE_CIRCLE, 1.3, 0.0, r=0.25)).tolist() == []       # fits into it
+    assert w.query_shape(probe(SHAPE_RECT, 0.0, 2.4, hx=1.5, hy=1.3)).tolist() == []     # y 1.1 .. 3.7, x up to 1.5
+    assert w.query_shape(probe(SHAPE_RECT, 0.0, 2.4, hx=1.5, hy=1.45)).tolist() == [0, 2]
+    assert w.query_shape(probe(SHAPE_CAPSULE, 5.0, 0.0, angle=math.pi / 2, hx=3.0, r=0.1)).tolist() == []
+    assert w.query_shape(probe(SHAPE_CAPSULE, 6.5, 0.0, hx=2.4, r=0.2)).tolist() == [1, 3]
+    # a bad probe is refused
+    bad = probe(SHAPE_CIRCLE, 0.0, 0.0, r=-1.0)
+    with pytest.raises(sf.SfpError):
+        w.query_shape(bad)
+
+
+def test_query_shape_against_independent_geometry(ref_api):
+    """the overlap answer against separations computed WITHOUT the shared math header (float64
+    support functions, tests/indep_geometry.py); probes whose separation is within 1e-4 of zero are
+    left out"""
+    import indep_geometry as ig
+    rng = np.random.default_rng(21)
+    b, _ = scenes.random_soup(160, 9, extent=6.0)
+    b["angle"] = rng.uniform(-3.0, 3.0, len(b))
+    w = world(ref_api, b)
+    checked = hits = 0
+    for k in range(60):
+        shape = int(rng.integers(0, 3))
+        hx = float(rng.uniform(0.1, 0.8)) if shape != SHAPE_CIRCLE else 0.0
+        hy = float(rng.uniform(0.1, 0.5)) if shape == SHAPE_RECT else 0.0
+        r = float(rng.uniform(0.0, 0.3)) if shape != SHAPE_CIRCLE else float(rng.uniform(0.0, 0.5))
+        x, y, ang = float(rng.uniform(-6, 6)), float(rng.uniform(-6, 6)), float(rng.uniform(-3, 3))
+        got = set(w.query_shape(probe(shape, x, y, ang, hx, hy, r)).tolist())
+        VP = ig.to_world(ig.core_vertices(shape, hx, hy), x, y, ang)
+        for i in range(len(b)):
+            VB = ig.to_world(ig.core_vertices(int(b["shape"][i]), float(b["hx"][i]), float(b["hy"][i])),
+                             float(b["x"][i]), float(b["y"][i]), float(b["angle"][i]))
+            reach = np.hypot(b["hx"][i], b["hy"][i]) + b["radius"][i] + np.hypot(hx, hy) + r
+            if np.hypot(b["x"][i] - x, b["y"][i] - y) > reach + 0.5:
+                assert i not in got
+                continue
+            sep, _ = ig.separation(VB, float(b["radius"][i]), VP, r)
+            if abs(sep) < 1e-4:
+                continue
+            checked += 1
+            hits += sep < 0
+            assert (i in got) == (sep < 0), (k, i, sep)
+    assert checked > 300 and hits > 40
+
+
 def random_rays(n, seed, extent_x, extent_y):
     rng = np.random.default_rng(seed)
     r = np.zeros(n, dtype=RAY_DTYPE)
@@ -125,6 +196,19 @@ def test_ray_cast_and_box_query_match_oracle(gpu_api, ref_api, scene):
         assert hg.tobytes() == hr.tobytes()
         for lo, hi in (((-3.0, 0.0), (2.0, 4.0)), ((-50.0, -5.0), (50.0, 0.4)), ((5.0, 5.0), (5.1, 5.1))):
             assert np.array_equal(g.query_aabb(lo, hi), r.query_aabb(lo, hi))
+        rng = np.random.default_rng(frames)
+        found = 0
+        for k in range(40):
+            shape = int(rng.integers(0, 3))
+            q = probe(shape, rng.uniform(-ex / 2, ex / 2), rng.uniform(0.0, 6.0), rng.uniform(-3, 3),
+                      rng.uniform(0.1, 1.0) if shape else 0.0, rng.uniform(0.1, 0.6) if shape == 2 else 0.0,
+                      rng.uniform(0.0, 0.4))
+            a, c = g.query_shape(q, 0xFFFF if k % 4 else 1), r.query_shape(q, 0xFFFF if k % 4 else 1)
+            assert np.array_equal(a, c)
+            found += len(c)
+            assert np.array_equal(g.query_point(float(q["x"][0]), float(q["y"][0])),
+                                  r.query_point(float(q["x"][0]), float(q["y"][0])))
+        assert found > 20
     # a query must not disturb the simulation: keep stepping, still bit-identical
     for _ in range(10):
         g.step()
