@@ -16,3 +16,12 @@ for _ in range(settle + 3): b.step()
 b.sync()
 st = b.stats()
 print("worlds", nw, "frame ms", b.last_step_ms(), "pairs/world", st["n_pairs"].mean(), "colours", st["n_colours"].mean())
+import ctypes as C
+fn = b.api.lib.sfp_batch_debug_stage_cycles
+fn.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+names = ["load/store", "broadphase", "colouring", "bucket", "integrate", "narrowphase", "pos solve", "derive", "vel solve", "-"]
+for w in (0, nw // 2):
+    out = np.zeros(10, dtype=np.uint64)
+    fn(b.h, w, out.ctypes.data_as(C.c_void_p))
+    tot = float(out.sum())
+    print("world", w, "cycles", int(tot), {n: f"{100 * float(v) / tot:.1f}%" for n, v in zip(names, out) if v})

@@ -56,6 +56,7 @@ struct BatchCtx {
     struct BatchQueue* queue;  // this launch's queue, or null: CTA i runs world world_base + i
     uint32_t* ring;        // [n_launch - n_whole] ring of worlds between two stages
     uint32_t* progress;    // [n_worlds] stages done of a world that is handed out by the stage
+    uint32_t np_list;      // 1: the dynamic shared memory holds the narrowphase list (pair_cap x u16) after the bodies
     uint32_t joint_cap;    // joint slots per world (0: the batch has no joints)
     const uint32_t* n_joints;  // [n_worlds] joints in use per world, or null
 };
@@ -83,6 +84,7 @@ __device__ __forceinline__ Ctx world_view(const BatchCtx& b, uint32_t w) {
     c.cp1 += po;
     c.cs += po;
     c.lam += po;
+    if (c.np_order) c.np_order += po;
     c.tab_old += (size_t)w * b.tab_slots;
     c.tab_new += (size_t)w * b.tab_slots;
     c.cnt = b.counters + w;
@@ -178,18 +180,18 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
     for (uint32_t k = tid; k < P; k += nth) atomicAdd(&bins[c.pcol[k] & (BUCKET_BINS - 1)], 1u);
     __syncthreads();
     // exclusive scan of the bins: BUCKET_BINS / nth consecutive bins per thread
-    constexpr int PER = BUCKET_BINS / BTPB;
+    constexpr int PER = (BUCKET_BINS + BTPB - 1) / BTPB;
     uint32_t v[PER], sum = 0;
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-        v[j] = bins[tid * PER + j];
+        v[j] = (tid * PER + j < (uint32_t)BUCKET_BINS) ? bins[tid * PER + j] : 0u;
         sum += v[j];
     }
     uint32_t total;
     uint32_t ex = block_excl_scan(sum, &total, smem9);
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-        bins[tid * PER + j] = ex;
+        if (tid * PER + j < (uint32_t)BUCKET_BINS) bins[tid * PER + j] = ex;
         ex += v[j];
     }
     __syncthreads();
@@ -220,6 +222,123 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
         c.pairs[pos] = c.pairs_raw[k];
     }
     __syncthreads();
+    // Narrowphase order: the same positions grouped by class alone.  A (colour, class) bucket
+    // of a 512-body world holds a few dozen pairs, so in position order nearly every warp
+    // would run two of the three narrowphase routines.  bins[key] is now the END of bucket
+    // key; obase[key] = where the bucket starts in class-major order.
+    if (c.np_order != nullptr) {
+        __shared__ uint32_t obase[BUCKET_BINS];
+        constexpr uint32_t NCLS = 1u << SFP_TYPE_BITS;
+        if (tid < NCLS) {
+            uint32_t run = 0;  // pairs of the lower classes
+            for (uint32_t cl = 0; cl < tid; ++cl)
+                for (uint32_t col = 0; col < SFP_MAX_COLOURS; ++col) {
+                    const uint32_t key = (col << SFP_TYPE_BITS) | cl;
+                    run += bins[key] - (key ? bins[key - 1] : 0u);
+                }
+            if (tid > 0u) c.cnt->np_cls_off[tid - 1u] = run;
+            for (uint32_t col = 0; col < SFP_MAX_COLOURS; ++col) {
+                const uint32_t key = (col << SFP_TYPE_BITS) | tid;
+                obase[key] = run;
+                run += bins[key] - (key ? bins[key - 1] : 0u);
+            }
+        }
+        __syncthreads();
+        const uint32_t lane = tid & 31u, warp = tid >> 5, nwarp = nth >> 5;
+        for (uint32_t key = warp; key < (uint32_t)BUCKET_BINS; key += nwarp) {
+            const uint32_t start = key ? bins[key - 1] : 0u, size = bins[key] - start;
+            for (uint32_t j = lane; j < size; j += 32u) c.np_order[obase[key] + j] = start + j;
+        }
+        __syncthreads();
+    }
+}
+
+// Narrowphase of one batched world, one substep.  Pass 1: every candidate pair (visited in class
+// order, c.np_order) tests its bounding circles; a pair out of reach gets its empty record, a
+// pair in reach is appended to its class's list in shared memory (s_list is laid out like
+// np_order: class cl's list starts at its class offset, and holds at most the class's pairs).
+// Pass 2: the SAT over the lists, densely — a thread takes the items tid, tid + nth, ... of the
+// concatenated lists, so all warps but those on a class boundary run ONE routine with all lanes
+// busy, and the pass takes ceil(pairs in reach / threads) rounds instead of one per 256
+// candidates.  Which thread handles which pair changes nothing in the records.
+template <bool POLYS>
+__device__ __forceinline__ void batch_narrowphase(const Ctx& c, uint16_t* s_list, uint32_t tid,
+                                                  uint32_t nth) {
+    constexpr uint32_t NCLS = 1u << SFP_TYPE_BITS;
+    __shared__ uint32_t s_cur[NCLS];
+    const uint32_t P = c.cnt->n_pairs;
+    const uint32_t off1 = c.cnt->np_cls_off[0], off2 = c.cnt->np_cls_off[1], off3 = c.cnt->np_cls_off[2];
+    const uint32_t lane = tid & 31u;
+    if (tid < NCLS) s_cur[tid] = 0u;
+    __syncthreads();
+    for (uint32_t base = 0; base < P; base += nth) {
+        const uint32_t i = base + tid;
+        bool near = false;
+        uint32_t k = 0u, cls = 0u;
+        if (i < P) {
+            k = c.np_order[i];
+            cls = (i >= off1 ? 1u : 0u) + (i >= off2 ? 1u : 0u) + (i >= off3 ? 1u : 0u);
+            uint2 p = c.pairs[k];
+            near = !sfp::narrowphase_far(ld4(c.pose, p.x), ld4(c.shape, p.x), ld4(c.pose, p.y),
+                                         ld4(c.shape, p.y), c.contact_margin);
+            if (!near) c.cb[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+        // a warp's 32 positions are consecutive in class order: one class, two on a boundary
+#pragma unroll
+        for (uint32_t cl = 0; cl < NCLS; ++cl) {
+            const uint32_t m = __ballot_sync(0xffffffffu, near && cls == cl);
+            if (m) {
+                uint32_t at = 0;
+                if (lane == 0) at = atomicAdd(&s_cur[cl], (uint32_t)__popc(m));
+                at = __shfl_sync(0xffffffffu, at, 0);
+                if (near && cls == cl) {
+                    const uint32_t o = cl == 0u ? 0u : (cl == 1u ? off1 : (cl == 2u ? off2 : off3));
+                    s_list[o + at + __popc(m & ((1u << lane) - 1u))] = (uint16_t)k;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t n0 = s_cur[0], n1 = n0 + s_cur[1], n2 = n1 + s_cur[2], n3 = n2 + s_cur[3];
+    uint32_t npts = 0, nman = 0;
+    float maxpen = 0.0f;
+    for (uint32_t idx = tid; idx < n3; idx += nth) {
+        uint32_t at;
+        if (idx < n0) at = idx;
+        else if (idx < n1) at = off1 + (idx - n0);
+        else if (idx < n2) at = off2 + (idx - n1);
+        else at = off3 + (idx - n2);
+        const uint32_t k2 = s_list[at];
+        uint2 p = c.pairs[k2];
+        sfp::ContactRec r = sfp::narrowphase_near<POLYS>(
+            ld4(c.pose, p.x), ld4(c.vel, p.x), ld4(c.shape, p.x), ld4(c.mat, p.x), ld4(c.pose, p.y),
+            ld4(c.vel, p.y), ld4(c.shape, p.y), ld4(c.mat, p.y), c.contact_margin,
+            reinterpret_cast<const sfp::f4*>(c.polytab));
+        uint32_t cnt = sfp::f2u(r.b.y);
+        st4(c.cb, k2, r.b);
+        if (cnt) {  // an empty manifold is fully described by count == 0
+            st4(c.ca, k2, r.a);
+            st4(c.cp0, k2, r.p0);
+            st4(c.cp1, k2, r.p1);
+            st4(c.cs, k2, r.s);
+        }
+        npts += cnt;
+        nman += cnt ? 1u : 0u;
+        if (cnt > 0) maxpen = fmaxf(maxpen, -r.s.x);
+        if (cnt > 1) maxpen = fmaxf(maxpen, -r.s.y);
+    }
+    // warp-aggregated integer statistics (order-independent)
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        npts += __shfl_xor_sync(0xffffffffu, npts, d);
+        nman += __shfl_xor_sync(0xffffffffu, nman, d);
+        maxpen = fmaxf(maxpen, __shfl_xor_sync(0xffffffffu, maxpen, d));
+    }
+    if (lane == 0 && (npts | nman)) {
+        atomicAdd(&c.cnt->n_contacts, npts);
+        atomicAdd(&c.cnt->n_manifolds, nman);
+        atomicMax(&c.cnt->maxpen_bits, sfp::f2u(maxpen));
+    }
 }
 
 // Shared-memory layout of one world (bytes per body): pose 16 | vel 16 | X 16 | meta 16 |
@@ -227,8 +346,13 @@ __device__ void batch_bucket(const Ctx& c, uint32_t* smem9) {
 // arrays during colouring, the substep record `prev` during the substeps.  Everything the
 // solver gathers by body index therefore lives in this SM's shared memory; only the per-pair
 // contact records (read and written by the pair's own thread, coalesced) stay in global memory.
+// CTAs per SM.  Measured on 8192 worlds of 512 bodies: one 29.5 ms, TWO 19.7 ms, three 21.0 ms
+// (256 threads each), four of 128 threads 24.3 ms.  Three need 80 registers (spills), and — the
+// larger effect — every resident CTA is in a different phase of the frame, the kernel's hot code
+// is ~70 KB against a 32 KB instruction cache level, and ncu shows "no instruction" as the
+// largest stall of the working warps (profiles/r2_ncu_batch.md).
 #ifndef SFP_BCTAS
-#define SFP_BCTAS 3
+#define SFP_BCTAS 2
 #endif
 // FULL: the variant that can collide general polygons and solve joints (more registers and
 // code: two CTAs per SM); the host launches it only for batches that hold a polygon body or
@@ -369,7 +493,10 @@ do {                                   \
         stage_integrate(c, h, tid, nth);
         __syncthreads();
         LAP(4);
-        stage_narrowphase<FULL>(c, tid, nth);
+        if (SMEM && b.np_list)
+            batch_narrowphase<FULL>(c, reinterpret_cast<uint16_t*>(dyn + 5 * (size_t)n), tid, nth);
+        else
+            stage_narrowphase<FULL, false, false, true>(c, tid, nth);
         __syncthreads();
         LAP(5);
         {
@@ -731,6 +858,7 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     A(c.cp1, np);
     A(c.cs, np);
     A(c.lam, np);
+    A(c.np_order, np);
     A(b->ctx.counters, n_worlds);
     A(b->ctx.scratch, nb);
     A(b->ctx.progress, n_worlds);
@@ -762,6 +890,12 @@ int32_t sfp_batch_create(const SfpParams* params, uint32_t n_worlds, uint32_t bo
     b->ctx.n_worlds = n_worlds;
     {
         size_t need = (size_t)bodies_per_world * 80u;
+        // + the narrowphase list (batch_narrowphase): one u16 per candidate pair
+        const size_t with_list = need + (((size_t)b->pair_cap * 2u + 15u) & ~(size_t)15u);
+        if (b->pair_cap <= 65535u && with_list <= 100u * 1024u) {
+            need = with_list;
+            b->ctx.np_list = 1u;
+        }
         if (need <= 200u * 1024u) {
             if (raise_batch_smem_limit(b->device, need) != cudaSuccess) return die(SFP_E_CUDA);
             b->smem_bytes = need;

@@ -41,7 +41,7 @@ struct Counters {
     uint32_t n_unc;  // length of Ctx::unc (pairs still uncoloured after the warm start)
     uint32_t n_colours_int;  // interior colours in use (tiles; n_colours counts the boundary ones)
     uint32_t frames_done;    // frames whose substep kernel ran to the end (capacity recovery)
-    uint32_t pad_[3];
+    uint32_t np_cls_off[3];  // batched worlds: where classes 1, 2, 3 start in Ctx::np_order
     int qbox[4];             // spatial queries: cell bounding box of all bodies (x0, y0, x1, y1)
     uint32_t pair_col_off[SFP_MAX_COLOURS + 1];
     uint32_t joint_col_off[SFP_MAX_COLOURS + 1];
@@ -79,6 +79,7 @@ struct Ctx {
     uint32_t *ekey0, *eval0, *ekey1, *eval1;
     uint32_t *pcnt, *poff;
     uint2* pairs_raw;
+    uint32_t* np_order;  // batched worlds: pair positions in narrowphase-class order (sfp_batch.cu), or null
     unsigned long long* pprio;  // per raw pair: its colouring priority (from the caller's indices); null: computed on the fly
     // tiles (sfp_math.h, "Tiles"): after the re-sort the dynamic bodies are the indices [0, n_dyn)
     // and tile t is the range [t * tile_b, (t + 1) * tile_b).  tile_b == 0: tiles off, every
@@ -732,7 +733,11 @@ __device__ __forceinline__ void flow_mark_noop(const Ctx& c, uint32_t k, uint2 p
     }
 }
 
-template <bool POLYS, bool MARK = false, bool STAGED = false>
+// ORDERED: pair positions are visited through c.np_order (a permutation of 0..P-1 that groups
+// the pairs by narrowphase class), so that the pairs of a warp run the same routine even when
+// the (colour, class) buckets are only a few dozen pairs long; which thread handles which pair
+// changes nothing in the records.
+template <bool POLYS, bool MARK = false, bool STAGED = false, bool ORDERED = false>
 __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, uint32_t nth) {
     // Per block-sized chunk of pairs: (1) every thread tests its pair's bounding circles; a pair
     // that is out of reach gets its empty record at once.  (2) The SAT for the pairs in reach.
@@ -753,8 +758,10 @@ __device__ __forceinline__ void stage_narrowphase(const Ctx& c, uint32_t tid, ui
     const uint32_t NONE = 0xffffffffu;
     uint32_t npts = 0, nman = 0;
     float maxpen = 0.0f;
+    const uint32_t* order = ORDERED ? c.np_order : nullptr;
     for (uint32_t base = tid - threadIdx.x; base < P; base += nth) {
-        const uint32_t k = base + threadIdx.x;
+        uint32_t k = base + threadIdx.x;
+        if (ORDERED && order != nullptr && k < P) k = order[k];
         bool near = false;
         if (compact) {
             if (threadIdx.x == 0) s_n = 0u;
