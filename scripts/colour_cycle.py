@@ -4,9 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import starframe_b200 as sf
 from bench import make_scene
-b, j = make_scene(sys.argv[1] if len(sys.argv) > 1 else "pile100k")
+scene = make_scene(sys.argv[1] if len(sys.argv) > 1 else "pile100k")
+b, j = scene[0], scene[1]
 api = sf.product_api()
-w = sf.World(api); w.upload_bodies(b); w.set_joints(j)
+w = sf.World(api)
+if len(scene) > 2: w.set_polygons(scene[2])
+w.upload_bodies(b); w.set_joints(j)
 fs = api.lib.sfp_debug_stage_ns; fs.argtypes = [C.c_void_p, C.c_void_p]; fs.restype = C.c_int32
 for f in range(300):
     w.step()

@@ -7,8 +7,11 @@ from bench import make_scene
 name = sys.argv[1] if len(sys.argv) > 1 else "pile100k"
 settle = int(sys.argv[2]) if len(sys.argv) > 2 else 240
 flags = int(sys.argv[3]) if len(sys.argv) > 3 else 0
-b, j = make_scene(name)
-w = sf.World(sf.product_api(), flags=flags); w.upload_bodies(b); w.set_joints(j)
+scene = make_scene(name)
+b, j = scene[0], scene[1]
+w = sf.World(sf.product_api(), flags=flags)
+if len(scene) > 2: w.set_polygons(scene[2])
+w.upload_bodies(b); w.set_joints(j)
 for _ in range(settle + 3): w.step()
 w.sync()
 st = w.stats()
