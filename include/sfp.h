@@ -99,7 +99,7 @@ enum {
                                                Default: a batch with more worlds than CTAs fit
                                                on the GPU at once runs that many CTAs, which
                                                take worlds from a queue — most of them whole,
-                                               the last one to two per CTA a stage at a time,
+                                               the last one per CTA a stage at a time,
                                                so that all CTAs end together (same results)   */
 };
 

@@ -65,7 +65,7 @@ def test_batch_many_worlds_spot_check(gpu_api, ref_api):
 @pytest.mark.parametrize("nw,bpw,substeps", [(700, 64, 8), (1000, 48, 3), (445, 64, 1), (2100, 32, 5)])
 def test_batch_queue_schedule_equals_one_cta_per_world(gpu_api, nw, bpw, substeps):
     """More worlds than resident CTAs: the frame kernel's CTAs take worlds from a queue, the last
-    one to two worlds per CTA one stage at a time with the state handed from CTA to CTA through
+    world per CTA one stage at a time with the state handed from CTA to CTA through
     global memory.  EVERY world must end in the bits it gets with one CTA per world
     (SFP_FLAG_BATCH_WHOLE_WORLDS), state and statistics, after frames enough for contacts, warm
     colourings and recolourings."""
