@@ -1117,6 +1117,7 @@ void launch_batch_frame(SfpBatch* b, cudaStream_t st, uint32_t w0, uint32_t nw, 
             ctx.n_whole = 0u;
         }
     }
+    if (ctx.queue && nw - ctx.n_whole < grid) grid = nw - ctx.n_whole;  // a ring slot per CTA
     if (b->smem_bytes) {
         if (full) k_batch_frame<true, true><<<grid, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
         else k_batch_frame<true, false><<<grid, BTPB, b->smem_bytes, st>>>(ctx, dt, substeps, rt);
