@@ -558,7 +558,7 @@ def run_worlds(args, rank, world_size):
                    "contacts_per_body": tot[1] / tot[2],
                    "l2": f"per-GPU state {n * 88 / 1e6:.0f} MB + contacts exceeds L2; no flush",
                    "collective": "statistics only (all_reduce of 3 floats after the timed region)"},
-        "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one CTA per world, whole frame)",
+        "roofline": {"bound": "hbm", "kernel": "k_batch_frame (one launch per frame; a CTA runs a world's frame or, for the last worlds, single stages from a queue)",
                      "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                      "peak_source": peak_src, "traffic": ncu_traffic("worlds512", nw),
                      "peak_nominal": 8000.0, "frac_nominal": ach / 8000.0,

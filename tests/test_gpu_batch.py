@@ -87,8 +87,8 @@ def test_batch_queue_schedule_equals_one_cta_per_world(gpu_api, nw, bpw, substep
 
 @pytest.mark.parametrize("nw", [1200, 2100])
 def test_batch_queue_sliced_host_path_matches_whole_worlds(gpu_api, nw):
-    """the sliced sfp_batch_step_host path (four slices, eight from 2048 worlds; the last slice
-    goes through the queue by the stage)"""
+    """the sliced sfp_batch_step_host path (four slices, the outer two small; the last slice goes
+    through the queue by the stage)"""
     bpw, frames = 32, 12
     bodies = scenes.worlds(nw, bpw)
     outs = []
