@@ -445,6 +445,22 @@ do {                                   \
         __syncthreads();
     }
 
+    // The substeps read the world's counters — above all the colour offsets, twice per colour
+    // and pass — from a copy in shared memory: in global memory every first touch of a line
+    // is an L2 round trip on the critical path of its colour, and a world that goes through
+    // the queue by the stage starts every stage with a cold L1.  What the substeps change
+    // (the head of the struct: contact statistics, overflow flags; the stage times) is written
+    // back at the end.
+    __shared__ Counters s_cnt;
+    Counters* const g_cnt = c.cnt;
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(g_cnt);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&s_cnt);
+        for (uint32_t i = tid; i < (uint32_t)(sizeof(Counters) / 4u); i += nth) dst[i] = __ldcg(src + i);
+    }
+    __syncthreads();
+    c.cnt = &s_cnt;
+
     const uint32_t ncol = c.cnt->n_colours;
     // solve order: big colours ascending, then small colours ascending (SFP_TAIL_ITEMS)
     const unsigned long long all = (ncol >= 64u) ? ~0ull : ((1ull << ncol) - 1ull);
@@ -556,6 +572,16 @@ do {                                   \
             for (int k = 0; k < 10; ++k) c.cnt->stage_cycles[k] += cyc[k];
     }
 #undef LAP
+    __syncthreads();
+    {
+        constexpr uint32_t HEAD = (uint32_t)(offsetof(Counters, pair_col_off) / 4u);
+        constexpr uint32_t CYC0 = (uint32_t)(offsetof(Counters, stage_cycles) / 4u);
+        constexpr uint32_t CYC1 = (uint32_t)(sizeof(Counters) / 4u);
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&s_cnt);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(g_cnt);
+        if (tid < HEAD) dst[tid] = src[tid];
+        if (CYC0 + tid < CYC1) dst[CYC0 + tid] = src[CYC0 + tid];
+    }
 }
 
 // Scheduling of a launch's worlds over its CTAs.  A world's frame is a chain of substeps + 1
