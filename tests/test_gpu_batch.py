@@ -105,6 +105,54 @@ def test_batch_queue_sliced_host_path_matches_whole_worlds(gpu_api, nw):
     assert np.array_equal(outs[0]["angle"].view(np.uint32), outs[1]["angle"].view(np.uint32))
 
 
+def test_batch_broadphase_sweep_with_many_wide_bodies(gpu_api, ref_api):
+    """the per-world broadphase sorts the boxes along x and keeps bodies wider than 8 cells in a list
+    of 32 that is tested against everybody: worlds with MORE than 32 such bodies (long bars, some
+    static, some falling), an odd body count, and bodies sharing their low edge exactly"""
+    nw, n = 5, 131
+    worlds = []
+    for w in range(nw):
+        b, _ = scenes.random_soup(n, 300 + w, extent=5.0)
+        rng = np.random.default_rng(w)
+        bars = np.arange(0, 44)                      # 44 bars, 6 to 9 m long: all "wide"
+        b["shape"][bars] = sf._ffi.SHAPE_RECT
+        b["hx"][bars] = rng.uniform(3.0, 4.5, len(bars))
+        b["hy"][bars] = 0.05
+        b["radius"][bars] = 0.0
+        b["angle"][bars] = rng.uniform(-0.2, 0.2, len(bars))
+        b["y"][bars] = 0.5 + 0.35 * bars
+        b["x"][bars] = rng.uniform(-1.0, 1.0, len(bars))
+        b["flags"][bars[::3]] |= sf._ffi.BODY_STATIC
+        same_edge = np.arange(60, 80)                # 20 circles with the same low edge
+        b["shape"][same_edge] = sf._ffi.SHAPE_CIRCLE
+        b["hx"][same_edge] = 0.0
+        b["hy"][same_edge] = 0.0
+        b["radius"][same_edge] = 0.1
+        b["x"][same_edge] = 2.0
+        b["vx"][same_edge] = 0.0
+        b["omega"][same_edge] = 0.0
+        worlds.append(b)
+    bodies = np.stack(worlds)
+    batch = sf.Batch(gpu_api, nw, n)
+    batch.upload(bodies)
+    refs = []
+    for w in range(nw):
+        r = sf.World(ref_api)
+        r.upload_bodies(bodies[w])
+        refs.append(r)
+    for f in range(25):
+        batch.step()
+        for r in refs:
+            r.step()
+    out, st = batch.download(), batch.stats()
+    for w in range(nw):
+        rs = refs[w].stats()
+        for k in ("n_pairs", "n_contacts", "n_colours"):
+            assert st[k][w] == rs[k], (w, k, st[k][w], rs[k])
+        same(out[w], refs[w].download_bodies())
+    assert st["n_pairs"].min() > 150
+
+
 def test_batch_partition_is_world_index_independent(gpu_api):
     """a rank that owns worlds [k, k+m) computes what a rank owning [0, n) computes for them
     (this is the multi-GPU sharding: no data-path exchange, so no collective to test)"""
