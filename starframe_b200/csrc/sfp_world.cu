@@ -800,6 +800,8 @@ struct SfpWorld {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_bp = nullptr, ev_col = nullptr;
+    cudaStream_t side = nullptr;                  // frame work that only the colouring waits for
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool timed = false;
     uint32_t launches = 0;
     uint32_t n = 0, nj = 0;
@@ -1073,10 +1075,23 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
     // the frames whose colouring starts from scratch also renew the body order
     if ((w->colour_age % SFP_RECOLOUR_PERIOD) == 0u) TRY(resort_bodies(w));
     const bool mark = !(w->p.flags & SFP_FLAG_BROADPHASE_EVERY_SUBSTEP);
-    if (mark) {  // the state this frame starts from, for the capacity recovery
-        k_snapshot<<<gb, TPB, 0, st>>>(c, w->d_pose_bak, w->d_vel_bak);
+    // warm start: read last frame's table, build this frame's in the other one
+    c.warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
+    c.tab_old = w->d_tab[(w->colour_age + 1u) & 1u];
+    c.tab_new = w->d_tab[w->colour_age & 1u];
+    w->colour_age += 1;
+    // The snapshot for the capacity recovery and the clearing of this frame's colour table feed
+    // nothing before the colouring: they run on a side stream (a parallel branch of the captured
+    // graph) beside the broadphase kernels, which are each too short to fill the device.
+    CU(cudaEventRecord(w->ev_fork, st));
+    CU(cudaStreamWaitEvent(w->side, w->ev_fork, 0));
+    if (mark) {  // the state this frame starts from
+        k_snapshot<<<gb, TPB, 0, w->side>>>(c, w->d_pose_bak, w->d_vel_bak);
         w->launches += 1;
     }
+    k_clear_table<<<blocks_for(w, w->tab_slots), TPB, 0, w->side>>>(c, c.tab_new, w->tab_slots);
+    w->launches += 1;
+    CU(cudaEventRecord(w->ev_join, w->side));
     k_aabb_count<<<gb, TPB, 0, st>>>(c);  // (dt from the frame's parameter block)
     CU(scan_exclusive(c.cell_cnt, c.cell_off, &w->d_cnt->n_bodies, w->cap_bodies, w->d_scan_tiles,
                       &w->d_cnt->n_entries, st));
@@ -1092,13 +1107,7 @@ int broadphase_and_colour(SfpWorld* w, float dt) {
                    (radix_blocks(w->cap_entries) > RADIX_INLINE_BLOCKS ? SFP_KEY_PASSES : 0);
     if (mark) CU(cudaEventRecordWithFlags(w->ev_bp, st, w->capturing ? cudaEventRecordExternal : 0));
 
-    // warm start: read last frame's table, build this frame's in the other one
-    c.warm = (w->colour_age % SFP_RECOLOUR_PERIOD) != 0u ? 1u : 0u;
-    c.tab_old = w->d_tab[(w->colour_age + 1u) & 1u];
-    c.tab_new = w->d_tab[w->colour_age & 1u];
-    w->colour_age += 1;
-    k_clear_table<<<blocks_for(w, w->tab_slots), TPB, 0, st>>>(c, c.tab_new, w->tab_slots);
-    w->launches += 1;
+    CU(cudaStreamWaitEvent(st, w->ev_join, 0));
     if (!multi) {
         // a grid barrier costs 1.2 us with 2-3 CTAs per SM and ~3 us with 8, and the kernel is a
         // dozen barriers around loops that are short for a 100 k-body world (measured: 3 CTAs
@@ -1454,6 +1463,11 @@ int32_t sfp_create(const SfpParams* params, SfpWorld** out) {
     if ((e = cudaEventCreate(&w->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&w->ev_bp)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&w->ev_col)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&w->ev_join, cudaEventDisableTiming)) != cudaSuccess)
+        return fail("cudaEventCreate", e);
     if ((e = cudaMalloc(&w->d_cnt, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMemset(w->d_cnt, 0, sizeof(Counters))) != cudaSuccess) return fail("cudaMemset", e);
     w->ctx.cnt = w->d_cnt;
@@ -1522,6 +1536,9 @@ int32_t sfp_destroy(SfpWorld* w) {
     if (w->ev1) cudaEventDestroy(w->ev1);
     if (w->ev_bp) cudaEventDestroy(w->ev_bp);
     if (w->ev_col) cudaEventDestroy(w->ev_col);
+    if (w->ev_fork) cudaEventDestroy(w->ev_fork);
+    if (w->ev_join) cudaEventDestroy(w->ev_join);
+    if (w->side) cudaStreamDestroy(w->side);
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
     return SFP_OK;
