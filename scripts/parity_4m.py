@@ -1,4 +1,4 @@
-"""One-off: the 4 M-body scale point, frames from a settled state, CUDA vs the CPU oracle (all
+"""One-off: a large scene (default: the 4 M-body scale point; polysN: a polygon pile), frames from a settled state, CUDA vs the CPU oracle (all
 host threads) — pair set, counts and every state bit.  Too slow for the test suite (the oracle
 needs ~20 s per frame at this size).  Optional third argument "shuffle": the bodies are uploaded
 in a random order."""
@@ -9,12 +9,15 @@ import numpy as np
 import starframe_b200 as sf
 from bench import make_scene, shuffle_scene
 from oracle import loader
-b, j = make_scene(sys.argv[1] if len(sys.argv) > 1 else "shelves4000000")
+scene = make_scene(sys.argv[1] if len(sys.argv) > 1 else "shelves4000000")
+b, j = scene[0], scene[1]
+polys = scene[2] if len(scene) > 2 else None
 frames = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 if len(sys.argv) > 3 and sys.argv[3] == "shuffle":
     b, j = shuffle_scene(b, j)
     print("bodies uploaded in a random order")
 settle = sf.World(sf.product_api())
+if polys is not None: settle.set_polygons(polys)
 settle.upload_bodies(b)
 for _ in range(200):
     settle.step()
@@ -22,6 +25,7 @@ st = settle.download_bodies()
 del settle
 g, r = sf.World(sf.product_api()), sf.World(loader.api())
 for w in (g, r):
+    if polys is not None: w.set_polygons(polys)
     w.upload_bodies(b)
 t0 = time.time()
 sg_, sr_ = st, st
