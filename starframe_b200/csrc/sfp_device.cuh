@@ -297,6 +297,10 @@ __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
         int4 ma = c.meta[a];
         uint32_t k = 0;
         uint32_t o = WRITE ? c.poff[e] : 0u;
+        // the write pass knows from the count pass how many partners this entry has: none (close
+        // to half of the entries of a pile) needs no scan, and the scan stops at the last one
+        const uint32_t want = WRITE ? c.pcnt[e] : 0xffffffffu;
+        if (WRITE && want == 0u) continue;
         for (uint32_t f = e + 1; f < E; f += 4u) {
             uint32_t kf[4], bf[4];
 #pragma unroll
@@ -334,7 +338,7 @@ __device__ __forceinline__ void stage_pairs(const Ctx& c, const uint32_t* ekey,
                     ++k;
                 }
             }
-            if (!same[3]) break;
+            if (!same[3] || k >= want) break;
         }
         if (!WRITE) c.pcnt[e] = k;
     }
