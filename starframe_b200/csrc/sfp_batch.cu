@@ -1,18 +1,20 @@
-// sfp_batch.cu — batched independent worlds (BASELINE.json config 5): ONE thread block per world
-// runs that world's WHOLE frame — broadphase, colouring, all substeps — in a single launch.
+// sfp_batch.cu — batched independent worlds (BASELINE.json config 5): a thread block runs a world's
+// WHOLE frame — broadphase, colouring, all substeps — and one launch runs the frame of all worlds.
 //
 // Why a different shape from sfp_world.cu: a 512-body world is far too small to fill a B200, and
 // its ~350 dependent phases per frame would each cost a grid-wide barrier.  Inside one CTA the
 // same phases are separated by __syncthreads() (tens of ns) and the world's state (45 KB of
-// bodies, a few hundred KB of contacts) stays in that SM's L1 / the L2.  The grid is the world
-// list: 148 SMs x BATCH_CTAS_PER_SM worlds in flight, the rest queue behind them.
+// bodies in shared memory, a few hundred KB of contacts) stays in that SM / the L2.  Two CTAs
+// are resident per SM (SFP_BCTAS); a batch with more worlds than resident CTAs launches exactly
+// that many, which take worlds from a queue in device memory (k_batch_frame, BatchQueue).
 //
 // The stages are the SAME __device__ functions as the single-world path (sfp_device.cuh), called
 // with (tid, nth) = (threadIdx.x, blockDim.x) on a per-world view of the buffers, so a world
 // stepped in a batch is bit-identical to the same world stepped alone, and to the oracle.  Only
-// the broadphase differs in structure: with 512 bodies an all-pairs AABB sweep (131k tests) is
-// cheaper than hashing and yields exactly the same pair SET, which is all that matters
-// downstream (the colouring depends on the set, not on the order).
+// the broadphase differs in structure: with 512 bodies a sweep along x over boxes sorted in
+// shared memory is cheaper than hashing and yields exactly the same pair SET, which is all that
+// matters downstream (the colouring depends on the set, not on the order); and the narrowphase
+// visits the pairs grouped by class through shared-memory lists (batch_narrowphase).
 //
 // Reference: none for batching — north_star: "batched independent worlds are partitioned across
 // the 8 GPUs of one box, with NCCL used only to gather statistics".
