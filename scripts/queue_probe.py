@@ -1,4 +1,4 @@
-"""Per-CTA start / end times of one frame of the queue schedule (needs a library built with -DSFP_CUT_PROBE,
+"""Per-CTA start / end times of one frame of the queue schedule (needs a library built with -DSFP_QUEUE_PROBE,
 SFP_B200_LIB=var/libsfp_probe.so): how evenly do the CTAs finish?"""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -18,8 +18,10 @@ b.sync()
 b.step(); b.sync()
 raw = np.zeros(4 * 8192 + 1024, dtype=np.uint32)
 fn(b.h, raw.ctypes.data_as(C.c_void_p), raw.nbytes)
-t = raw[:4 * 8192].view(np.uint64).reshape(-1, 2)[:444].astype(np.int64)
-sm = raw[4 * 8192:4 * 8192 + 444]
+t = raw[:4 * 8192].view(np.uint64).reshape(-1, 2).astype(np.int64)
+ncta = int(np.count_nonzero(t[:, 1]))   # CTAs of the launch (they all record their end)
+t = t[:ncta]
+sm = raw[4 * 8192:4 * 8192 + ncta]
 t0 = t[:, 0].min()
 start, end = (t[:, 0] - t0) / 1e3, (t[:, 1] - t0) / 1e3
 dur = end - start

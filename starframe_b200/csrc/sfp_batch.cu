@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(BTPB, FULL ? 2 : SFP_BCTAS)
         }
         __syncthreads();
         const uint32_t w = s_seg[0], sa = s_seg[1], se = s_seg[2];
-#ifdef SFP_CUT_PROBE
+#ifdef SFP_QUEUE_PROBE
         if (threadIdx.x == 0 && (it == 0u || se == 0u)) {
             unsigned long long t;
             unsigned smid;
@@ -1254,7 +1254,7 @@ int32_t sfp_batch_step(SfpBatch* b, float dt, uint32_t substeps) {
     return SFP_OK;
 }
 
-#ifdef SFP_CUT_PROBE
+#ifdef SFP_QUEUE_PROBE
 __attribute__((visibility("default"))) int32_t sfp_debug_batch_scratch(SfpBatch* b, void* out, size_t bytes) {
     cudaSetDevice(b->device);
     cudaStreamSynchronize(b->stream);
