@@ -358,6 +358,15 @@ impl Physics {
         check(unsafe { sfp_ray_cast(self.world, rays.as_ptr(), rays.len() as u32, hits.as_mut_ptr()) },
               self.world)
     }
+
+    /// bodies whose collider overlaps `probe` (shape, x, y, angle, hx, hy, radius of a desc; the
+    /// narrowphase with zero margin decides); a circle of radius 0 is a point query
+    pub fn query_shape(&mut self, probe: &SfpBodyDesc, mask: u32, out: &mut Vec<u32>) -> Result<(), PhysicsError> {
+        let mut n = 0u32;
+        check(unsafe { sfp_query_shape(self.world, probe, mask, std::ptr::null_mut(), 0, &mut n) }, self.world)?;
+        out.resize(n as usize, 0);
+        check(unsafe { sfp_query_shape(self.world, probe, mask, out.as_mut_ptr(), n, &mut n) }, self.world)
+    }
 }
 
 impl Drop for Physics {
