@@ -127,6 +127,33 @@ class Physics {
             check(SFP_FN(ray_cast)(w_, rays.data(), (uint32_t)rays.size(), hits.data()), "ray_cast");
         return hits;
     }
+    /* bodies whose tight box overlaps [lo, hi] */
+    std::vector<uint32_t> query_aabb(float lo_x, float lo_y, float hi_x, float hi_y, uint32_t mask = 0xffff) {
+        flush();
+        std::vector<uint32_t> out(bodies_.size() + 1);
+        uint32_t n = 0;
+        check(SFP_FN(query_aabb)(w_, lo_x, lo_y, hi_x, hi_y, mask, out.data(), (uint32_t)out.size(), &n),
+              "query_aabb");
+        out.resize(n);
+        return out;
+    }
+    /* bodies whose collider overlaps `c` placed at (x, y, angle): the narrowphase with zero margin */
+    std::vector<uint32_t> query_shape(const Collider& c, float x, float y, float angle = 0.0f,
+                                      uint32_t mask = 0xffff) {
+        flush();
+        SfpBodyDesc q = {};
+        q.shape = c.shape, q.hx = c.hx, q.hy = c.hy, q.radius = c.radius;
+        q.x = x, q.y = y, q.angle = angle;
+        std::vector<uint32_t> out(bodies_.size() + 1);
+        uint32_t n = 0;
+        check(SFP_FN(query_shape)(w_, &q, mask, out.data(), (uint32_t)out.size(), &n), "query_shape");
+        out.resize(n);
+        return out;
+    }
+    /* bodies whose collider contains the point (picking) */
+    std::vector<uint32_t> query_point(float x, float y, uint32_t mask = 0xffff) {
+        return query_shape(Collider::new_circle(0.0f), x, y, 0.0f, mask);
+    }
     /* teleport / kinematic control of individual bodies between ticks */
     void set_body_states(const std::vector<uint32_t>& idx, const std::vector<SfpBodyState>& states) {
         flush();

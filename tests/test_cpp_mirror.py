@@ -35,6 +35,16 @@ int main() {
     ray.ox = 4.f, ray.oy = 5.f, ray.dx = 0.f, ray.dy = -1.f, ray.max_t = 10.f, ray.mask = 0xffffffffu;
     auto hit = ph.ray_cast({ray});
     if (!ball_on_ground || hit[0].body != nut) return 2;
+    // picking: the point at the nut's centre is inside the nut only; a wide flat probe on the ground
+    // line touches the ground and what rests on it
+    auto s_now = ph.body_states();
+    auto pick = ph.query_point(s_now[nut].x, s_now[nut].y);
+    if (pick.size() != 1 || pick[0] != nut) return 4;
+    auto under = ph.query_shape(Collider::new_rect(20.f, 0.2f), 0.f, 0.05f);
+    bool has_ground = false, has_ball = false;
+    for (uint32_t i : under) has_ground |= (i == 0u), has_ball |= (i == ball);
+    if (!has_ground || !has_ball) return 5;
+    if (ph.query_aabb(-50.f, -5.f, 50.f, 50.f).size() != s_now.size()) return 6;
     auto s0 = ph.body_states();
     std::vector<SfpBodyState> s1;
     ph.tick_host(s0, s1);
