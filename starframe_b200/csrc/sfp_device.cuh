@@ -39,6 +39,7 @@ struct Counters {
     uint32_t overflow;
     uint32_t n_contacts, n_manifolds, maxpen_bits;
     uint32_t n_unc;  // length of Ctx::unc (pairs still uncoloured after the warm start)
+    uint32_t n_unc2; // length of Ctx::unc2 (the list the odd rounds read; see stage_colour_take)
     uint32_t n_colours_int;  // interior colours in use (tiles; n_colours counts the boundary ones)
     uint32_t frames_done;    // frames whose substep kernel ran to the end (capacity recovery)
     uint32_t np_cls_off[3];  // batched worlds: where classes 1, 2, 3 start in Ctx::np_order
@@ -99,6 +100,7 @@ struct Ctx {
     // pairs that the warm start left uncoloured, in any order (null: the rounds walk all pairs);
     // after a warm start that is a few per cent of the pairs
     uint32_t* unc;
+    uint32_t* unc2;  // second list: a round reads one and appends the pairs it leaves uncoloured to the other
     uint32_t *pcol_sorted, *pperm, *jcol_sorted, *jperm;
     // colour tables (sfp_math.h, SFP_CTAB_*): last frame's (read) and this frame's (built)
     unsigned long long *tab_old, *tab_new;
@@ -561,9 +563,13 @@ __device__ __forceinline__ void colour_bid_one(const Ctx& c, unsigned long long*
 __device__ __forceinline__ void stage_colour_bid(const Ctx& c, uint32_t round, uint32_t tid,
                                                  uint32_t nth) {
     unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
-    const uint32_t P = c.unc ? c.cnt->n_unc : c.cnt->n_pairs;
+    // the list of this round (even rounds: unc, odd rounds: unc2); the take stage of this round
+    // fills the other one, whose counter is reset here
+    const uint32_t* list = c.unc ? ((round & 1u) ? c.unc2 : c.unc) : nullptr;
+    const uint32_t P = c.unc ? ((round & 1u) ? c.cnt->n_unc2 : c.cnt->n_unc) : c.cnt->n_pairs;
+    if (c.unc && tid == 0) *((round & 1u) ? &c.cnt->n_unc : &c.cnt->n_unc2) = 0u;
     for (uint32_t i = tid; i < P; i += nth) {
-        const uint32_t k = c.unc ? c.unc[i] : i;
+        const uint32_t k = list ? list[i] : i;
         if (c.pcol[k] == UNCOLOURED) {
             uint2 p = c.pairs_raw[k];
             colour_bid_one(c, claim, p.x, p.y,
@@ -610,19 +616,43 @@ __device__ __forceinline__ void stage_colour_take(const Ctx& c, uint32_t round, 
                                                   uint32_t nth) {
     unsigned long long* claim = (round & 1u) ? c.claim1 : c.claim0;
     unsigned long long* next_claim = (round & 1u) ? c.claim0 : c.claim1;
-    const uint32_t P = c.unc ? c.cnt->n_unc : c.cnt->n_pairs;
+    // With lists: the pairs this round leaves uncoloured go on the OTHER list, which the next
+    // round reads — a colouring from scratch takes ~33 rounds for a 100 k-body pile and used to
+    // walk all 340 k pairs in every one of them (0.86 ms every SFP_RECOLOUR_PERIOD-th frame; 0.67 now).
+    // The order of a list means nothing: a round treats every pair on it independently.
+    const uint32_t* list = c.unc ? ((round & 1u) ? c.unc2 : c.unc) : nullptr;
+    uint32_t* next_list = (round & 1u) ? c.unc : c.unc2;
+    uint32_t* next_n = (round & 1u) ? &c.cnt->n_unc : &c.cnt->n_unc2;
+    const uint32_t P = c.unc ? ((round & 1u) ? c.cnt->n_unc2 : c.cnt->n_unc) : c.cnt->n_pairs;
+    const uint32_t lane = threadIdx.x & 31u;
     ColourCount ncol;
-    for (uint32_t i = tid; i < P; i += nth) {
-        const uint32_t k = c.unc ? c.unc[i] : i;
-        if (c.pcol[k] == UNCOLOURED) {
-            uint2 p = c.pairs_raw[k];
-            uint32_t col = colour_take_one(
-                c, claim, next_claim, p.x, p.y,
-                c.pprio ? c.pprio[k] : sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)), round, &ncol);
-            // sort key: colour in the high bits, narrowphase class in the low ones (coherence
-            // inside a colour bucket)
-            if (col != UNCOLOURED) col = pair_sort_key(c, col, p);
-            c.pcol[k] = col;
+    // (whole warps walk the loop together: the append is warp-aggregated)
+    for (uint32_t base = tid - lane; base < P; base += nth) {
+        const uint32_t i = base + lane;
+        bool left = false;
+        uint32_t k = 0u;
+        if (i < P) {
+            k = list ? list[i] : i;
+            if (c.pcol[k] == UNCOLOURED) {
+                uint2 p = c.pairs_raw[k];
+                uint32_t col = colour_take_one(
+                    c, claim, next_claim, p.x, p.y,
+                    c.pprio ? c.pprio[k] : sfp::pair_priority(ext_id(c, p.x), ext_id(c, p.y)), round, &ncol);
+                // sort key: colour in the high bits, narrowphase class in the low ones (coherence
+                // inside a colour bucket)
+                left = col == UNCOLOURED;
+                if (!left) col = pair_sort_key(c, col, p);
+                c.pcol[k] = col;
+            }
+        }
+        if (list) {
+            const uint32_t m = __ballot_sync(0xffffffffu, left);
+            if (m) {
+                uint32_t at = 0;
+                if (lane == 0) at = atomicAdd(next_n, (uint32_t)__popc(m));
+                at = __shfl_sync(0xffffffffu, at, 0);
+                if (left) next_list[at + __popc(m & ((1u << lane) - 1u))] = k;
+            }
         }
     }
     for (uint32_t k = tid; k < c.nj; k += nth)

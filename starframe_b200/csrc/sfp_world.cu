@@ -902,6 +902,7 @@ int alloc_pair_arrays(SfpWorld* w, uint32_t ce, uint32_t cp) {
     TRY(alloc_dev(w, &c.pprio, cp, bag));
     TRY(alloc_dev(w, &c.pcol, cp, bag));
     TRY(alloc_dev(w, &c.unc, cp, bag));
+    TRY(alloc_dev(w, &c.unc2, cp, bag));
     TRY(alloc_dev(w, &c.pcol_sorted, cp, bag));
     TRY(alloc_dev(w, &c.pperm, cp, bag));
     TRY(alloc_dev(w, &w->d_pkeyB, cp, bag));

@@ -93,6 +93,32 @@ def test_multi_kernel_mode_matches(gpu_api, ref_api):
     run_and_compare(g, r, 5)
 
 
+@pytest.mark.parametrize("scene", ["pile", "ropes"])
+def test_across_recolourings_and_resorts(gpu_api, ref_api, scene):
+    """100 frames: every 32nd frame (SFP_RECOLOUR_PERIOD) both sides colour from scratch and the
+    device renews its body order; compared around those frames and at the end, bodies uploaded in
+    a random order so that the re-sorts really move them"""
+    if scene == "pile":
+        b, j = scenes.mixed_pile(700)
+    else:
+        b, j = scenes.ropes(n_ropes=16, links=20, n_free=200)
+    perm = np.random.default_rng(5).permutation(len(b))
+    inv = np.empty_like(perm)
+    inv[perm] = np.arange(len(b))
+    b = b[perm]
+    if len(j):
+        j = j.copy()
+        j["body_a"], j["body_b"] = inv[j["body_a"]], inv[j["body_b"]]
+    g, r = make_worlds(gpu_api, ref_api, b, j)
+    for f in range(100):
+        g.step()
+        r.step()
+        if f in (30, 31, 32, 33, 63, 64, 65, 96, 99):
+            assert_same_discrete(g, r)
+            assert_same_state(g, r)
+    assert g.stats()["n_contacts"] > 300
+
+
 def test_circles_container_small(gpu_api, ref_api):
     b, j = scenes.circles_container(2000)
     g, r = make_worlds(gpu_api, ref_api, b, j)
